@@ -1,0 +1,187 @@
+"""Pins the CPU oracle (oracle/gp_oracle.py) against independent re-derivations.
+
+The reference has no tests or golden vectors (parity unpinned), so the oracle is
+checked against: torch autograd of the same loss (what gpmpc/gp.py:61-63 does), the literal
+explicit-inverse formulas of gpmpc/gp.py:46,85, an 80-bit long-double loop implementation, central
+finite differences, analytic known-answer cases, and the committed fixtures in tests/golden/.
+"""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gp_oracle as o
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _problem(n, d, q, seed=0):
+    p = o.synthetic_problem(n, d, q, p=1, seed=seed)
+    return p["X"], p["Y"][:, 0], p["Z"], p["ell"], p["sf2"], p["noise"]
+
+
+@pytest.mark.parametrize("n,d", [(15, 1), (45, 3), (200, 5), (64, 16)])
+def test_kernel_formulations_agree(n, d):
+    X, y, Z, ell, sf2, noise = _problem(n, d, 33)
+    a = o.se_kernel(Z, X, ell, sf2)
+    b = o.se_kernel_gpytorch(Z, X, ell, sf2)
+    assert o.rel_err(a, b) < 1e-13
+    # literal covSE_single formula, one pair at a time (gpmpc/gp.py:12-14)
+    i, j = 3, 7
+    ref = sf2 * math.exp(-0.5 * float((((Z[i] - X[j]) ** 2) / ell**2).sum()))
+    assert abs(float(a[i, j]) - ref) < 1e-15
+
+
+@pytest.mark.parametrize("n,d,ard", [(30, 1, False), (45, 3, False), (200, 5, True), (120, 16, True)])
+def test_closed_form_gradient_matches_autograd(n, d, ard):
+    X, y, *_ = _problem(n, d, 1, seed=3)
+    g = torch.Generator().manual_seed(5)
+    rn = torch.randn(1, generator=g, dtype=torch.float64) - 2.0
+    rs = torch.randn((), generator=g, dtype=torch.float64)
+    rl = torch.randn(1, d if ard else 1, generator=g, dtype=torch.float64) + 1.0
+    l1, gn1, gs1, gl1 = o.loss_and_grad(X, y, rn, rs, rl)
+    l2, gn2, gs2, gl2 = o.loss_autograd(X, y, rn, rs, rl)
+    assert abs(float(l1 - l2)) < 1e-12 * max(1.0, abs(float(l2)))
+    assert o.rel_err(gn1, gn2) < 1e-9
+    assert o.rel_err(gs1, gs2) < 1e-9
+    assert o.rel_err(gl1, gl2) < 1e-9
+
+
+@pytest.mark.parametrize("n,d", [(15, 1), (45, 3), (200, 5)])
+def test_predict_matches_explicit_inverse_and_autograd_jacobian(n, d):
+    X, y, Z, ell, sf2, noise = _problem(n, d, 25, seed=11)
+    st = o.fit_state(X, y, ell, sf2, noise)
+    mean, var, jac = o.predict(Z, X, ell, sf2, st["L"], st["alpha"])
+    m2, v2 = o.predict_explicit_inverse(Z, X, y, ell, sf2, noise)
+    assert o.rel_err(mean, m2) < 1e-9
+    assert o.rel_err(var, v2) < 1e-9
+    # Jacobian vs autograd of the mean
+    Zg = Z.clone().requires_grad_(True)
+    k = sf2 * torch.exp(-0.5 * (((Zg[:, None, :] - X[None, :, :]) / ell) ** 2).sum(-1))
+    (k @ st["alpha"]).sum().backward()
+    assert o.rel_err(jac, Zg.grad) < 1e-12
+    # ... and vs central finite differences
+    h = 1e-6
+    for j in range(d):
+        e = torch.zeros(d, dtype=torch.float64)
+        e[j] = h
+        mp, _, _ = o.predict(Z + e, X, ell, sf2, st["L"], st["alpha"], want_var=False, want_jac=False)
+        mm, _, _ = o.predict(Z - e, X, ell, sf2, st["L"], st["alpha"], want_var=False, want_jac=False)
+        assert o.rel_err((mp - mm) / (2 * h), jac[:, j]) < 1e-6
+
+
+def _longdouble_gp(X, y, Z, ell, sf2, noise):
+    """Naive loops in numpy long double (80-bit on x86): Cholesky, solves, mean, variance, MLL."""
+    ld = np.longdouble
+    X = X.numpy().astype(ld); y = y.numpy().astype(ld); Z = Z.numpy().astype(ld)
+    ell = np.asarray(ell, dtype=ld); sf2 = ld(sf2); noise = ld(noise)
+    n = X.shape[0]
+    def kern(a, b):
+        return sf2 * np.exp(ld(-0.5) * (((a - b) / ell) ** 2).sum())
+    K = np.array([[kern(X[i], X[j]) for j in range(n)] for i in range(n)], dtype=ld) + noise * np.eye(n, dtype=ld)
+    L = np.zeros((n, n), dtype=ld)
+    for j in range(n):
+        s = K[j, j] - (L[j, :j] ** 2).sum()
+        L[j, j] = np.sqrt(s)
+        for i in range(j + 1, n):
+            L[i, j] = (K[i, j] - (L[i, :j] * L[j, :j]).sum()) / L[j, j]
+    def fwd(b):
+        x = np.zeros(n, dtype=ld)
+        for i in range(n):
+            x[i] = (b[i] - (L[i, :i] * x[:i]).sum()) / L[i, i]
+        return x
+    def bwd(b):
+        x = np.zeros(n, dtype=ld)
+        for i in reversed(range(n)):
+            x[i] = (b[i] - (L[i + 1:, i] * x[i + 1:]).sum()) / L[i, i]
+        return x
+    t = fwd(y); alpha = bwd(t)
+    mll = ld(-0.5) * ((t * t).sum() + 2 * np.log(np.diag(L)).sum() + n * np.log(2 * ld(np.pi)))
+    means, vars_ = [], []
+    for z in Z:
+        k = np.array([kern(z, X[i]) for i in range(n)], dtype=ld)
+        v = fwd(k)
+        means.append((k * alpha).sum()); vars_.append(sf2 - (v * v).sum())
+    return float(mll / n), np.array(means, dtype=np.float64), np.array(vars_, dtype=np.float64)
+
+
+@pytest.mark.parametrize("n,d", [(15, 1), (30, 3), (45, 3)])
+def test_oracle_matches_long_double_loops(n, d):
+    X, y, Z, ell, sf2, noise = _problem(n, d, 8, seed=21)
+    mll_ld, mean_ld, var_ld = _longdouble_gp(X, y, Z, ell.numpy(), sf2, noise)
+    st = o.fit_state(X, y, ell, sf2, noise)
+    mean, var, _ = o.predict(Z, X, ell, sf2, st["L"], st["alpha"])
+    assert abs(float(o.mll_per_n(X, y, ell, sf2, noise)) - mll_ld) < 1e-11 * abs(mll_ld)
+    assert o.rel_err(mean, mean_ld) < 1e-10
+    assert o.rel_err(var, var_ld) < 1e-10
+
+
+def test_known_answers():
+    sf2, noise, ell = 1.7, 0.3, torch.tensor([0.8, 1.1])
+    # N = 1: mean = sf2 k/(sf2+noise) y ; var = sf2 - k^2/(sf2+noise)
+    X = torch.tensor([[0.2, -0.4]], dtype=torch.float64); y = torch.tensor([1.3], dtype=torch.float64)
+    Z = torch.tensor([[0.5, 0.1], [0.2, -0.4]], dtype=torch.float64)
+    st = o.fit_state(X, y, ell, sf2, noise)
+    mean, var, jac = o.predict(Z, X, ell, sf2, st["L"], st["alpha"])
+    k = o.se_kernel(Z, X, ell, sf2)[:, 0]
+    assert torch.allclose(mean, k / (sf2 + noise) * y[0], rtol=1e-14)
+    assert torch.allclose(var, sf2 - k * k / (sf2 + noise), rtol=1e-14)
+    assert torch.allclose(jac[1], torch.zeros(2, dtype=torch.float64), atol=1e-15)  # at the data point
+    # query == training point with tiny noise: mean -> y_i, var_f -> ~0
+    X, yy, _, ell3, _, _ = _problem(20, 3, 1, seed=2)
+    st = o.fit_state(X, yy, ell3, 1.0, 1e-6)
+    mean, var, _ = o.predict(X[:5], X, ell3, 1.0, st["L"], st["alpha"])
+    assert o.rel_err(mean, yy[:5]) < 1e-3 and float(var.abs().max()) < 1e-5
+    # far-away query: mean -> 0, var -> sf2, jac -> 0
+    mean, var, jac = o.predict(torch.full((1, 3), 50.0, dtype=torch.float64), X, ell3, 1.0, st["L"], st["alpha"])
+    assert abs(float(mean)) < 1e-100 and abs(float(var) - 1.0) < 1e-14 and float(jac.abs().max()) < 1e-100
+    # duplicated training rows survive with the noise floor
+    Xd = torch.cat([X, X[:3]]); yd = torch.cat([yy, yy[:3]])
+    st = o.fit_state(Xd, yd, ell3, 1.0, 1e-6)
+    assert torch.isfinite(st["alpha"]).all()
+
+
+def test_defaults_at_raw_zero():
+    noise, sf2, ell = o.constrained(0.0, 0.0, 0.0)
+    assert abs(float(noise) - (math.log(2) + 1e-6)) < 1e-15
+    assert abs(float(sf2) - math.log(2)) < 1e-15 and abs(float(ell) - math.log(2)) < 1e-15
+    y = torch.tensor(0.37, dtype=torch.float64)
+    assert abs(float(o.softplus(o.inv_softplus(y))) - 0.37) < 1e-14
+
+
+def test_fit_loop_decreases_loss_and_stops():
+    X, y, *_ = _problem(30, 3, 1, seed=9)
+    out = o.fit_hyperparameters(X, y, n_train=200, lr=0.05)
+    assert out["losses"][-1] < out["losses"][0]
+    assert len(out["losses"]) <= 200
+    assert out["raw_ell"].shape == (1, 1) and out["raw_noise"].dtype == torch.float32
+
+
+def test_fitc_reduces_to_exact_when_all_points_are_inducing():
+    X, y, Z, ell, sf2, noise = _problem(25, 3, 10, seed=4)
+    w = o.fitc_posterior_mean(X, y, X, ell, sf2, noise)
+    st = o.fit_state(X, y, ell, sf2, noise)
+    assert o.rel_err(w, st["alpha"]) < 1e-6
+
+
+def test_golden_fixtures_reproduce():
+    """tests/golden/*.npz were written by tests/golden/make_golden.py from this oracle; a change in the
+    oracle's arithmetic shows up here."""
+    files = sorted(f for f in os.listdir(GOLD) if f.endswith(".npz"))
+    assert files, "no golden fixtures committed"
+    for f in files:
+        g = np.load(os.path.join(GOLD, f))
+        X, y, Z = (torch.from_numpy(g[k]) for k in ("X", "y", "Z"))
+        ell, sf2, noise = torch.from_numpy(g["ell"]), float(g["sf2"]), float(g["noise"])
+        st = o.fit_state(X, y, ell, sf2, noise)
+        mean, var, jac = o.predict(Z, X, ell, sf2, st["L"], st["alpha"])
+        assert o.rel_err(st["alpha"], g["alpha"]) < 1e-9, f
+        assert o.rel_err(mean, g["mean"]) < 1e-10, f
+        assert o.rel_err(var, g["var"]) < 1e-10, f
+        assert o.rel_err(jac, g["jac"]) < 1e-10, f
+        assert abs(float(o.mll_per_n(X, y, ell, sf2, noise)) - float(g["mll_per_n"])) < 1e-11 * abs(float(g["mll_per_n"])), f
+        loss, gn, gs, gl = o.loss_and_grad(X, y, g["raw_noise"], g["raw_sf2"], g["raw_ell"])
+        assert abs(float(loss) - float(g["loss_raw"])) < 1e-11 * abs(float(g["loss_raw"])), f
+        assert o.rel_err(gl, g["g_raw_ell"]) < 1e-8 and o.rel_err(gn, g["g_raw_noise"]) < 1e-8, f
