@@ -1,0 +1,91 @@
+// Shared helpers for the gp-mpc GP hot path kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <atomic>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "gpmpc_b200 kernels are written for sm_100a (B200) only"
+#endif
+
+namespace gpk {
+
+extern thread_local char g_err[512];
+extern std::atomic<long> g_launches;
+
+int fail(int code, const char* fmt, ...);
+
+// Layout of the per-GP hyper-parameter block in device memory (doubles).
+constexpr int HYP_MAXD = 32;
+constexpr int HYP_CENTER = 0;             // center[32]
+constexpr int HYP_INV_ELL = HYP_MAXD;     // 1/ell[32]
+constexpr int HYP_SF2 = 2 * HYP_MAXD;     // signal variance
+constexpr int HYP_NOISE = 2 * HYP_MAXD + 1;
+constexpr int HYP_STRIDE = 2 * HYP_MAXD + 8;
+
+constexpr int TILE = 128;                 // every padded matrix dimension is a multiple of this
+
+#define GPK_ARG(cond, msg)                                                      \
+    do { if (!(cond)) return gpk::fail(-1, "%s: bad argument: %s", __func__, msg); } while (0)
+#define GPK_CUDA(x)                                                             \
+    do { cudaError_t e_ = (x); if (e_ != cudaSuccess)                           \
+        return gpk::fail(-(1000 + (int)e_), "%s: %s -> %s", __func__, #x, cudaGetErrorString(e_)); } while (0)
+#define GPK_LAUNCHED()                                                          \
+    do { gpk::g_launches.fetch_add(1, std::memory_order_relaxed);               \
+         cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess)            \
+        return gpk::fail(-(1000 + (int)e_), "%s: kernel launch -> %s", __func__, cudaGetErrorString(e_)); } while (0)
+#define GPK_TRY(x) do { int r_ = (x); if (r_ != 0) return r_; } while (0)
+
+// ---- small device helpers -----------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+// cp.async (LDGSTS), 16 bytes, L2-only
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_u32(smem)), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+// ---- mbarrier + 1-D bulk TMA copy (cp.async.bulk -> SASS UBLKCP) -----------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra.uni WAIT_DONE;\n"
+        "bra.uni WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity));
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+}  // namespace gpk

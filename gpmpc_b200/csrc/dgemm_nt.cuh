@@ -1,0 +1,198 @@
+// FP64 "NT" GEMM core on the DMMA pipe (mma.sync m8n8k4 f64 -> SASS DMMA.8x8x4; measured 37.1 TFLOP/s
+// on B200, profiles/peaks_micro_r01.json).  tcgen05 has no f64 kind, so this is the tensor path for
+// every fp64 contraction of the GP hot path:
+//     C[i,j] = beta * C[i,j] + alpha * sum_{k in range(i)} A[i,k] * B[j,k]
+// A: M x K row-major, B: N x K row-major (both K-contiguous), C: M x N row-major.
+// All dimensions are multiples of the 128 tile (the host pads every matrix), so there is no edge code.
+//
+// One CTA = one 128x128 tile of C, 8 warps as 2 (M) x 4 (N), warp tile 64x32 = 8x4 DMMA fragments,
+// 64 fp64 accumulators per thread.  K is streamed in blocks of 16 through a 4-stage cp.async ring
+// (40 KB per stage, rows padded to 160 B so the 8-byte fragment loads are bank-conflict free).
+//
+// Triangular operands (used by potrf/trtri/K^-1/variance) only shorten the k-range per tile row:
+//     a_tri == 1 (A lower triangular, diagonal at A[0][0]):  k <  (tile_m + 1) * 128
+//     a_tri == 2 (A upper triangular):                       k >= tile_m * 128
+// c_lower == 1 computes only tiles on or below the diagonal (SYRK-like updates).
+// Epilogue 0 stores C; epilogue 1 (posterior variance) never stores C and instead writes the
+// per-tile column sums of squares  colsq[tile_m][j] = sum_{i in tile} C[i,j]^2.
+#pragma once
+#include "common.cuh"
+
+namespace gpk {
+
+constexpr int G_BM = 128, G_BN = 128, G_BK = 16, G_STAGES = 4, G_THREADS = 256;
+constexpr int G_ROW = G_BK + 4;                         // padded smem row, doubles (160 B)
+constexpr int G_STAGE_ELEMS = (G_BM + G_BN) * G_ROW;    // doubles per stage
+constexpr int G_SMEM_BYTES = G_STAGES * G_STAGE_ELEMS * 8;
+
+struct GemmParams {
+    const double* A;
+    const double* B;
+    double* C;
+    long lda, ldb, ldc;
+    long strideA, strideB, strideC;   // batch strides (elements); grid.z = batch
+    int M, N, K;
+    double alpha, beta;
+    int a_tri;       // 0 full, 1 lower, 2 upper
+    int c_lower;     // 1: skip tiles with tile_m < tile_n
+    int tiles_m, tiles_n;
+    int group_m, group_n;   // super-tile for L2 reuse across the ~148 concurrently resident CTAs
+    double* colsq;          // epilogue 1 output: [tiles_m][ld_colsq]
+    long ld_colsq, stride_colsq;
+};
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+// linear CTA id -> (tile_m, tile_n), super-tiles of group_m x group_n tiles enumerated row-major
+__device__ __forceinline__ void tile_coords(const GemmParams& p, int id, int& tm, int& tn) {
+    const int per_srow = p.group_m * p.tiles_n;
+    const int sr = id / per_srow;
+    const int rem = id - sr * per_srow;
+    const int gm = min(p.group_m, p.tiles_m - sr * p.group_m);
+    const int per_st = gm * p.group_n;
+    const int sc = rem / per_st;
+    const int rem2 = rem - sc * per_st;
+    tm = sr * p.group_m + rem2 % gm;
+    tn = sc * p.group_n + rem2 / gm;
+    if (p.a_tri == 1) tm = p.tiles_m - 1 - tm;   // heaviest rows first for a lower-triangular A
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(G_THREADS, 1) dgemm_nt_kernel(const GemmParams p) {
+    extern __shared__ __align__(16) double smem[];
+
+    int tm, tn;
+    tile_coords(p, blockIdx.x, tm, tn);
+    if (p.c_lower && tm < tn) return;
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = warp >> 2, wn = warp & 3;     // 2 x 4 warps
+
+    const long batch = blockIdx.z;
+    const double* __restrict__ A = p.A + batch * p.strideA + (long)tm * G_BM * p.lda;
+    const double* __restrict__ B = p.B + batch * p.strideB + (long)tn * G_BN * p.ldb;
+
+    int kbeg = 0, kend = p.K;
+    if (p.a_tri == 1) kend = min(p.K, (tm + 1) * G_BM);
+    if (p.a_tri == 2) kbeg = min(p.K, tm * G_BM);
+    const int nk = (kend - kbeg) / G_BK;
+
+    // each thread copies 4 + 4 16-byte chunks per k-block: chunk c -> row c/8, k-chunk c%8
+    auto load_stage = [&](int stage, int kb) {
+        double* As = smem + stage * G_STAGE_ELEMS;
+        double* Bs = As + G_BM * G_ROW;
+        const long k0 = kbeg + (long)kb * G_BK;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int c = tid + i * G_THREADS;
+            const int row = c >> 3, kc = (c & 7) * 2;
+            cp_async16(As + row * G_ROW + kc, A + (long)row * p.lda + k0 + kc);
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int c = tid + i * G_THREADS;
+            const int row = c >> 3, kc = (c & 7) * 2;
+            cp_async16(Bs + row * G_ROW + kc, B + (long)row * p.ldb + k0 + kc);
+        }
+    };
+
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+#pragma unroll
+    for (int s = 0; s < G_STAGES - 1; s++) {
+        if (s < nk) load_stage(s, s);
+        cp_async_commit();
+    }
+
+    const int a_off = (wm * 64 + g) * G_ROW + t;
+    const int b_off = G_BM * G_ROW + (wn * 32 + g) * G_ROW + t;
+
+    for (int kb = 0; kb < nk; kb++) {
+        cp_async_wait<G_STAGES - 2>();
+        __syncthreads();
+        {   // refill the stage consumed in the previous iteration
+            const int nxt = kb + G_STAGES - 1;
+            if (nxt < nk) load_stage(nxt % G_STAGES, nxt);
+            cp_async_commit();
+        }
+        const double* st = smem + (kb % G_STAGES) * G_STAGE_ELEMS;
+#pragma unroll
+        for (int ks = 0; ks < G_BK / 4; ks++) {
+            double a[8], b[4];
+#pragma unroll
+            for (int f = 0; f < 8; f++) a[f] = st[a_off + f * 8 * G_ROW + ks * 4];
+#pragma unroll
+            for (int f = 0; f < 4; f++) b[f] = st[b_off + f * 8 * G_ROW + ks * 4];
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+    }
+    cp_async_wait<0>();
+
+    if constexpr (EPI == 0) {
+        double* __restrict__ C = p.C + batch * p.strideC + ((long)tm * G_BM + wm * 64 + g) * p.ldc +
+                                 (long)tn * G_BN + wn * 32 + 2 * t;
+        const double alpha = p.alpha, beta = p.beta;
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                double2* ptr = reinterpret_cast<double2*>(C + (long)i * 8 * p.ldc + j * 8);
+                double2 v;
+                v.x = alpha * acc[i][j][0];
+                v.y = alpha * acc[i][j][1];
+                if (beta != 0.0) {
+                    const double2 old = *ptr;
+                    v.x += beta * old.x;
+                    v.y += beta * old.y;
+                }
+                *ptr = v;
+            }
+    } else {
+        // column sums of squares over the 128 rows of this tile
+        __syncthreads();                       // all warps are done with the pipeline smem
+        double* red = smem;                    // [2 (wm)][128 columns]
+        const double alpha2 = p.alpha * p.alpha;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                s0 = fma(acc[i][j][0], acc[i][j][0], s0);
+                s1 = fma(acc[i][j][1], acc[i][j][1], s1);
+            }
+            // reduce over g (lane bits 2..4)
+#pragma unroll
+            for (int o = 4; o < 32; o <<= 1) {
+                s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+                s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+            }
+            if (g == 0) {
+                red[wm * G_BN + wn * 32 + j * 8 + 2 * t] = s0;
+                red[wm * G_BN + wn * 32 + j * 8 + 2 * t + 1] = s1;
+            }
+        }
+        __syncthreads();
+        if (tid < G_BN) {
+            double* out = p.colsq + batch * p.stride_colsq + (long)tm * p.ld_colsq + (long)tn * G_BN;
+            out[tid] = alpha2 * (red[tid] + red[G_BN + tid]);
+        }
+    }
+}
+
+// host-side launcher (defined in linalg.cu)
+int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st);
+
+}  // namespace gpk

@@ -1,0 +1,599 @@
+// SIMT kernels of the GP hot path: ARD squared-exponential kernel assembly, the fused posterior
+// mean + input-Jacobian kernel (north-star subsystem a), the variance finalisation and the MLL gradient
+// trace reduction (subsystem c).
+//
+// Math restated from the reference (file:line under /root/reference):
+//   k(a,b) = sf2 * exp(-1/2 sum_j (a_j - b_j)^2 / ell_j^2)                      gpmpc/gp.py:12-14, 17-21
+//   K      = k(X,X) + noise I                                                   gpmpc/gp.py:45
+//   mean   = k(z,X) K^-1 y  = sum_i alpha_i k(z,x_i)                            gpmpc/gp.py:85
+//   jac    = d mean / d z   = sum_i alpha_i k(z,x_i) (x_i - z) / ell^2          CasADi AD of gp.py:12-14 in acados
+// Points are centred by `center` and divided by ell on the fly (what gpytorch's RBFKernel does before its
+// distance computation); r^2 is then expanded as |a|^2 + |b|^2 - 2 a.b so the inner loop is one FMA per
+// dimension.
+#include "common.cuh"
+
+namespace gpk {
+
+// ------------------------------------------------------------------------------------------------
+// cross kernel / training-matrix assembly:  out[r][c] = sf2 exp(-1/2 |a~_r - b~_c|^2)
+//   mode 0: cross kernel K(A, B); rows >= na and columns >= nb are written as 0 (padding)
+//   mode 1: training matrix K(A, A) + noise I, exact diagonal sf2 + noise, identity on the padding
+// ------------------------------------------------------------------------------------------------
+constexpr int CK_T = 64, CK_LD = HYP_MAXD + 1;
+
+template <typename TP_>
+__device__ __forceinline__ void stage_scaled_rows(const TP_* __restrict__ P, long ldp, long n_valid, long row0,
+                                                  int d, int dfill, const double* __restrict__ hyp, double* sm,
+                                                  double* se) {
+    // 64 rows, scaled and centred, into sm[64][CK_LD] (columns d..dfill-1 zeroed); se[r] = -1/2 |row|^2.
+    // 256 threads: 4 threads per row.
+    const int r = threadIdx.x >> 2, q = threadIdx.x & 3;
+    const long gr = row0 + r;
+    double s = 0.0;
+    for (int j = q; j < dfill; j += 4) {
+        double v = 0.0;
+        if (gr < n_valid && j < d) v = ((double)P[gr * ldp + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j];
+        sm[r * CK_LD + j] = v;
+        s = fma(v, v, s);
+    }
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    if (q == 0) se[r] = -0.5 * s;
+}
+
+template <typename TA>
+__global__ void __launch_bounds__(256)
+cross_kernel(const TA* __restrict__ A, long lda, long na, long strideA, const double* __restrict__ B, long ldb,
+             long nb, long strideB, int d, const double* __restrict__ hyp_all, double* __restrict__ out, long ldo,
+             long strideO, int mode) {
+    __shared__ double As[CK_T * CK_LD], Bs[CK_T * CK_LD], ea[CK_T], eb[CK_T];
+    const long batch = blockIdx.z;
+    const double* hyp = hyp_all + batch * HYP_STRIDE;
+    A += batch * strideA;
+    B += batch * strideB;
+    out += batch * strideO;
+    const long row0 = (long)blockIdx.y * CK_T, col0 = (long)blockIdx.x * CK_T;
+    stage_scaled_rows(A, lda, na, row0, d, d, hyp, As, ea);
+    stage_scaled_rows(B, ldb, nb, col0, d, d, hyp, Bs, eb);
+    __syncthreads();
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    double acc[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) acc[r][c] = ea[ty * 4 + r] + eb[tx + 16 * c];
+#pragma unroll 4
+    for (int j = 0; j < d; j++) {
+        double a[4], b[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) a[r] = As[(ty * 4 + r) * CK_LD + j];
+#pragma unroll
+        for (int c = 0; c < 4; c++) b[c] = Bs[(tx + 16 * c) * CK_LD + j];
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) acc[r][c] = fma(a[r], b[c], acc[r][c]);
+    }
+    const double sf2 = hyp[HYP_SF2], noise = hyp[HYP_NOISE];
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const long gr = row0 + ty * 4 + r, gc = col0 + tx + 16 * c;
+            double v;
+            if (gr < na && gc < nb) {
+                v = sf2 * exp(fmin(acc[r][c], 0.0));
+                if (mode == 1 && gr == gc) v = sf2 + noise;
+            } else {
+                v = (mode == 1 && gr == gc) ? 1.0 : 0.0;
+            }
+            out[gr * ldo + gc] = v;
+        }
+}
+
+// ------------------------------------------------------------------------------------------------
+// train pack: per tile of TP points  [x~ (TP x DP)] [e (TP)] [a (TP)]  in the prediction dtype
+//   fp64: e = -1/2 |x~|^2          (natural exponent, exp())
+//   fp32: e = -1/2 |x~|^2 log2(e)  (base-2 exponent, ex2.approx)
+//   a = sf2 * alpha (0 on the padding)
+// ------------------------------------------------------------------------------------------------
+constexpr int TP = 256;
+constexpr double LOG2E = 1.4426950408889634074;
+
+template <typename T>
+__global__ void pack_train_kernel(const double* __restrict__ X, long ldx, long n, int d, int dp,
+                                  const double* __restrict__ alpha, const double* __restrict__ hyp,
+                                  T* __restrict__ pack, long n_tiles) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_tiles * TP) return;
+    const long tile = i / TP;
+    const int r = (int)(i - tile * TP);
+    T* base = pack + tile * (long)TP * (dp + 2);
+    double s = 0.0;
+    for (int j = 0; j < dp; j++) {
+        double v = 0.0;
+        if (i < n && j < d) v = (X[i * ldx + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j];
+        const T vt = (T)v;
+        base[r * dp + j] = vt;
+        s = fma((double)vt, (double)vt, s);      // norm of the value actually used by the kernel
+    }
+    const double scale = sizeof(T) == 4 ? LOG2E : 1.0;
+    base[(long)TP * dp + r] = (T)(-0.5 * s * scale);
+    base[(long)TP * dp + TP + r] = (T)(i < n ? hyp[HYP_SF2] * alpha[i] : 0.0);
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused posterior mean + input-Jacobian (north-star subsystem a)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float kexp(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ double kexp(double x) { return exp(x); }
+
+template <typename T, int DP>
+__device__ __forceinline__ void load_row(const T* __restrict__ p, T (&x)[DP]) {
+    if constexpr ((DP * sizeof(T)) % 16 == 0) {
+        constexpr int V = 16 / sizeof(T);
+        using VT = typename std::conditional<sizeof(T) == 4, float4, double2>::type;
+#pragma unroll
+        for (int v = 0; v < DP / V; v++) {
+            const VT t = reinterpret_cast<const VT*>(p)[v];
+            if constexpr (sizeof(T) == 4) {
+                x[v * 4 + 0] = ((const float4&)t).x; x[v * 4 + 1] = ((const float4&)t).y;
+                x[v * 4 + 2] = ((const float4&)t).z; x[v * 4 + 3] = ((const float4&)t).w;
+            } else {
+                x[v * 2 + 0] = ((const double2&)t).x; x[v * 2 + 1] = ((const double2&)t).y;
+            }
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < DP; j++) x[j] = p[j];
+    }
+}
+
+struct MeanJacArgs {
+    const void* Z; long ldz; long q; long strideZ;   // raw queries (dtype T), shared between GPs when strideZ == 0
+    int d;
+    const double* hyp;                               // [batch][HYP_STRIDE]
+    const void* pack; long stride_pack;              // [batch][n_tiles * TP * (DP + 2)]
+    int n_tiles, tiles_per_split, n_split;
+    void* mean; long stride_mean;                    // [batch][q]
+    void* jac; long ldj; long stride_jac;            // [batch][q][ldj]
+    void* work; long stride_work;                    // [batch][n_split][q][DP + 1] partial sums when n_split > 1
+};
+
+constexpr int MJ_THREADS = 128;
+
+template <typename T, int DP, int RQ>
+__global__ void __launch_bounds__(MJ_THREADS)
+mean_jac_kernel(const MeanJacArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int TILE_ELEMS = TP * (DP + 2);
+    constexpr uint32_t TILE_BYTES = TILE_ELEMS * sizeof(T);
+    T* buf = reinterpret_cast<T*>(smem_raw);                        // 2 tiles
+    __shared__ __align__(8) uint64_t bar[2];
+
+    const int tid = threadIdx.x;
+    const long batch = blockIdx.z;
+    const int split = blockIdx.y;
+    const double* hyp = a.hyp + batch * HYP_STRIDE;
+    const T* __restrict__ Z = reinterpret_cast<const T*>(a.Z) + batch * a.strideZ;
+    const T* __restrict__ pack = reinterpret_cast<const T*>(a.pack) + batch * a.stride_pack;
+
+    const int t_begin = split * a.tiles_per_split;
+    const int t_end = min(a.n_tiles, t_begin + a.tiles_per_split);
+
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (tid == 0 && t_begin < t_end) {
+        mbar_expect_tx(&bar[0], TILE_BYTES);
+        tma_bulk_g2s(buf, pack + (long)t_begin * TILE_ELEMS, TILE_BYTES, &bar[0]);
+    }
+
+    // this thread's RQ queries, centred / scaled; for fp32 the exponent runs in base 2
+    constexpr T ESCALE = sizeof(T) == 4 ? (T)LOG2E : (T)1;
+    T zs[RQ][DP], zl[RQ][DP], ez[RQ], m[RQ], S[RQ][DP];
+    long qi[RQ];
+#pragma unroll
+    for (int r = 0; r < RQ; r++) {
+        qi[r] = ((long)blockIdx.x * RQ + r) * MJ_THREADS + tid;
+        T s = 0;
+#pragma unroll
+        for (int j = 0; j < DP; j++) {
+            T v = 0;
+            if (j < a.d && qi[r] < a.q) v = (T)(((double)Z[qi[r] * a.ldz + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j]);
+            zs[r][j] = v;
+            zl[r][j] = v * ESCALE;
+            s = fma(v, v, s);
+            S[r][j] = 0;
+        }
+        ez[r] = (T)(-0.5) * s * ESCALE;
+        m[r] = 0;
+    }
+
+    for (int t = t_begin; t < t_end; t++) {
+        const int it = t - t_begin, cur = it & 1;
+        if (tid == 0 && t + 1 < t_end) {   // the other buffer was released by the __syncthreads below
+            mbar_expect_tx(&bar[cur ^ 1], TILE_BYTES);
+            tma_bulk_g2s(buf + (cur ^ 1) * TILE_ELEMS, pack + (long)(t + 1) * TILE_ELEMS, TILE_BYTES, &bar[cur ^ 1]);
+        }
+        mbar_wait(&bar[cur], (it >> 1) & 1);
+        const T* xs = buf + cur * TILE_ELEMS;
+        const T* es = xs + TP * DP;
+        const T* as = es + TP;
+#pragma unroll 2
+        for (int i = 0; i < TP; i++) {
+            T x[DP];
+            load_row<T, DP>(xs + i * DP, x);
+            const T e = es[i], al = as[i];
+#pragma unroll
+            for (int r = 0; r < RQ; r++) {
+                T s = e + ez[r];
+#pragma unroll
+                for (int j = 0; j < DP; j++) s = fma(zl[r][j], x[j], s);
+                const T w = kexp(s) * al;
+                m[r] += w;
+#pragma unroll
+                for (int j = 0; j < DP; j++) S[r][j] = fma(w, x[j], S[r][j]);
+            }
+        }
+        __syncthreads();
+    }
+
+    if (a.n_split == 1) {
+        T* mean = reinterpret_cast<T*>(a.mean) + batch * a.stride_mean;
+        T* jac = reinterpret_cast<T*>(a.jac) + batch * a.stride_jac;
+#pragma unroll
+        for (int r = 0; r < RQ; r++) {
+            if (qi[r] >= a.q) continue;
+            mean[qi[r]] = m[r];
+#pragma unroll
+            for (int j = 0; j < DP; j++)
+                if (j < a.d) jac[qi[r] * a.ldj + j] = (T)((double)(S[r][j] - zs[r][j] * m[r]) * hyp[HYP_INV_ELL + j]);
+        }
+    } else {
+        T* work = reinterpret_cast<T*>(a.work) + batch * a.stride_work + (long)split * a.q * (DP + 1);
+#pragma unroll
+        for (int r = 0; r < RQ; r++) {
+            if (qi[r] >= a.q) continue;
+            T* w = work + qi[r] * (DP + 1);
+            w[0] = m[r];
+#pragma unroll
+            for (int j = 0; j < DP; j++) w[1 + j] = S[r][j];
+        }
+    }
+}
+
+// sums the split partials and applies jac_j = (S_j - z~_j mean) / ell_j
+template <typename T, int DP>
+__global__ void mean_jac_finalize_kernel(const MeanJacArgs a) {
+    const long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long batch = blockIdx.z;
+    if (q >= a.q) return;
+    const double* hyp = a.hyp + batch * HYP_STRIDE;
+    const T* Z = reinterpret_cast<const T*>(a.Z) + batch * a.strideZ;
+    const T* work = reinterpret_cast<const T*>(a.work) + batch * a.stride_work;
+    double acc[DP + 1];
+#pragma unroll
+    for (int j = 0; j <= DP; j++) acc[j] = 0.0;
+    for (int s = 0; s < a.n_split; s++) {
+        const T* w = work + ((long)s * a.q + q) * (DP + 1);
+#pragma unroll
+        for (int j = 0; j <= DP; j++) acc[j] += (double)w[j];
+    }
+    reinterpret_cast<T*>(a.mean)[batch * a.stride_mean + q] = (T)acc[0];
+    T* jac = reinterpret_cast<T*>(a.jac) + batch * a.stride_jac + q * a.ldj;
+#pragma unroll
+    for (int j = 0; j < DP; j++)
+        if (j < a.d) {
+            const T zsj = (T)(((double)Z[q * a.ldz + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j]);
+            jac[j] = (T)((acc[1 + j] - (double)zsj * acc[0]) * hyp[HYP_INV_ELL + j]);
+        }
+}
+
+template <typename T, int DP, int RQ>
+static int launch_mean_jac_t(MeanJacArgs a, int batch, cudaStream_t st) {
+    constexpr int smem = 2 * TP * (DP + 2) * (int)sizeof(T);
+    static bool attr_done = false;
+    if (!attr_done) {
+        GPK_CUDA(cudaFuncSetAttribute(mean_jac_kernel<T, DP, RQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        attr_done = true;
+    }
+    const long per_block = (long)MJ_THREADS * RQ;
+    dim3 grid((unsigned)((a.q + per_block - 1) / per_block), (unsigned)a.n_split, (unsigned)batch);
+    mean_jac_kernel<T, DP, RQ><<<grid, MJ_THREADS, smem, st>>>(a);
+    GPK_LAUNCHED();
+    if (a.n_split > 1) {
+        dim3 g2((unsigned)((a.q + 127) / 128), 1, (unsigned)batch);
+        mean_jac_finalize_kernel<T, DP><<<g2, 128, 0, st>>>(a);
+        GPK_LAUNCHED();
+    }
+    return 0;
+}
+
+template <typename T>
+static int launch_mean_jac(const MeanJacArgs& a, int dp, int batch, cudaStream_t st) {
+    constexpr int RQ = sizeof(T) == 4 ? 2 : 1;
+    switch (dp) {
+        case 1: return launch_mean_jac_t<T, 1, RQ>(a, batch, st);
+        case 2: return launch_mean_jac_t<T, 2, RQ>(a, batch, st);
+        case 3: return launch_mean_jac_t<T, 3, RQ>(a, batch, st);
+        case 4: return launch_mean_jac_t<T, 4, RQ>(a, batch, st);
+        case 8: return launch_mean_jac_t<T, 8, RQ>(a, batch, st);
+        case 16: return launch_mean_jac_t<T, 16, RQ>(a, batch, st);
+        case 32: return launch_mean_jac_t<T, 32, 1>(a, batch, st);
+        default: return fail(-1, "mean_jac: unsupported padded dimension %d", dp);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// variance finalisation:  var[q] = sf2 - sum_tm colsq[tm][q]
+// ------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void var_finalize_kernel(const double* __restrict__ colsq, long ld, long stride_colsq, int tiles_m, long q,
+                                    const double* __restrict__ hyp_all, T* __restrict__ var, long stride_var) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long batch = blockIdx.z;
+    if (i >= q) return;
+    const double* c = colsq + batch * stride_colsq + i;
+    double s = 0.0;
+    for (int t = 0; t < tiles_m; t++) s += c[(long)t * ld];
+    var[batch * stride_var + i] = (T)(hyp_all[batch * HYP_STRIDE + HYP_SF2] - s);
+}
+
+// ------------------------------------------------------------------------------------------------
+// MLL gradient trace reduction (north-star subsystem c).  With G = alpha alpha^T - K^-1 and K_f the
+// noise-free kernel, accumulates over rows a in [r0, r1), all columns b < n:
+//   out[0] = sum_a G_aa ;  out[1] = sum_ab G_ab K_f,ab ;  out[2 + j] = sum_ab G_ab K_f,ab (x~_aj - x~_bj)^2
+// K_f is recomputed from X (never read from HBM); K^-1 is streamed once: 8 N^2 bytes per full pass.
+// ------------------------------------------------------------------------------------------------
+template <int DP>
+__global__ void __launch_bounds__(256)
+grad_trace_kernel(const double* __restrict__ X, long ldx, long n, int d, const double* __restrict__ hyp,
+                  const double* __restrict__ Kinv, long ldk, const double* __restrict__ alpha, long r0, long r1,
+                  double* __restrict__ partial) {
+    __shared__ double As[CK_T * CK_LD], Bs[CK_T * CK_LD], ea[CK_T], eb[CK_T], red[8][DP + 2];
+    const long row0 = r0 + (long)blockIdx.y * CK_T, col0 = (long)blockIdx.x * CK_T;
+    stage_scaled_rows(X, ldx, n, row0, d, DP, hyp, As, ea);
+    stage_scaled_rows(X, ldx, n, col0, d, DP, hyp, Bs, eb);
+    __syncthreads();
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const double sf2 = hyp[HYP_SF2];
+    double w[4][4];
+    double acc_tr = 0.0, acc_k = 0.0;
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) w[r][c] = ea[ty * 4 + r] + eb[tx + 16 * c];
+#pragma unroll
+    for (int j = 0; j < DP; j++) {
+        double av[4], bv[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) av[r] = As[(ty * 4 + r) * CK_LD + j];
+#pragma unroll
+        for (int c = 0; c < 4; c++) bv[c] = Bs[(tx + 16 * c) * CK_LD + j];
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) w[r][c] = fma(av[r], bv[c], w[r][c]);
+    }
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const long gr = row0 + ty * 4 + r, gc = col0 + tx + 16 * c;
+            double v = 0.0;
+            if (gr < r1 && gr < n && gc < n) {
+                const double g = alpha[gr] * alpha[gc] - Kinv[gr * ldk + gc];
+                const double kf = gr == gc ? sf2 : sf2 * exp(fmin(w[r][c], 0.0));
+                v = g * kf;
+                if (gr == gc) acc_tr += g;
+            }
+            w[r][c] = v;
+            acc_k += v;
+        }
+    // per-dimension sums are reduced across the warp right away so they never live in registers together
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll 2
+    for (int j = 0; j < DP; j++) {
+        double av[4], bv[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) av[r] = As[(ty * 4 + r) * CK_LD + j];
+#pragma unroll
+        for (int c = 0; c < 4; c++) bv[c] = Bs[(tx + 16 * c) * CK_LD + j];
+        double s = 0.0;
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const double df = av[r] - bv[c];
+                s = fma(w[r][c], df * df, s);
+            }
+        s = warp_sum(s);
+        if (lane == 0) red[warp][2 + j] = s;
+    }
+    acc_tr = warp_sum(acc_tr);
+    acc_k = warp_sum(acc_k);
+    if (lane == 0) {
+        red[warp][0] = acc_tr;
+        red[warp][1] = acc_k;
+    }
+    __syncthreads();
+    if (threadIdx.x < DP + 2) {
+        double s = 0.0;
+#pragma unroll
+        for (int wi = 0; wi < 8; wi++) s += red[wi][threadIdx.x];
+        partial[((long)blockIdx.y * gridDim.x + blockIdx.x) * (DP + 2) + threadIdx.x] = s;
+    }
+}
+
+// out[v] = sum_b partial[b][v]   (one block per value v; deterministic order)
+__global__ void reduce_partials_kernel(const double* __restrict__ partial, long n_blocks, int width,
+                                       double* __restrict__ out) {
+    __shared__ double sh[32];
+    const int v = blockIdx.x;
+    double s = 0.0;
+    for (long b = threadIdx.x; b < n_blocks; b += blockDim.x) s += partial[b * width + v];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        s = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.0;
+        s = warp_sum(s);
+        if (threadIdx.x == 0) out[v] = s;
+    }
+}
+
+static int pad_dim(int d) {
+    if (d <= 4) return d;
+    if (d <= 8) return 8;
+    if (d <= 16) return 16;
+    return 32;
+}
+
+}  // namespace gpk
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+using namespace gpk;
+
+extern "C" {
+
+int gpk_pad_dim(int d) { return (d >= 1 && d <= HYP_MAXD) ? pad_dim(d) : -1; }
+int gpk_hyp_stride(void) { return HYP_STRIDE; }
+int gpk_train_tile(void) { return TP; }
+
+long gpk_pack_train_elems(long n, int d) {
+    if (n <= 0 || d < 1 || d > HYP_MAXD) return -1;
+    const long tiles = (n + TP - 1) / TP;
+    return tiles * TP * (pad_dim(d) + 2);
+}
+
+// K(A,B) [mode 0] or K(A,A) + noise I with identity padding [mode 1] into out (rows_pad x cols_pad, multiples of 64)
+int gpk_cross_kernel(int dtype_a, const void* A, long lda, long na, long strideA, const double* B, long ldb, long nb,
+                     long strideB, int d, const double* hyp, double* out, long ldo, long strideO, long rows_pad,
+                     long cols_pad, int mode, int batch, void* stream) {
+    GPK_ARG(dtype_a == 0 || dtype_a == 1, "dtype_a must be 0 (f32) or 1 (f64)");
+    GPK_ARG(A && B && hyp && out, "null pointer");
+    GPK_ARG(d >= 1 && d <= HYP_MAXD, "d must be in [1, 32]");
+    GPK_ARG(rows_pad % CK_T == 0 && cols_pad % CK_T == 0 && rows_pad >= na && cols_pad >= nb, "padded sizes");
+    GPK_ARG(ldo >= cols_pad && batch >= 1, "ldo / batch");
+    GPK_ARG(mode == 0 || mode == 1, "mode");
+    dim3 grid((unsigned)(cols_pad / CK_T), (unsigned)(rows_pad / CK_T), (unsigned)batch);
+    if (dtype_a == 0)
+        cross_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)A, lda, na, strideA, B, ldb, nb, strideB,
+                                                                    d, hyp, out, ldo, strideO, mode);
+    else
+        cross_kernel<double><<<grid, 256, 0, (cudaStream_t)stream>>>((const double*)A, lda, na, strideA, B, ldb, nb,
+                                                                     strideB, d, hyp, out, ldo, strideO, mode);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+int gpk_pack_train(int dtype, const double* X, long ldx, long n, int d, const double* alpha, const double* hyp,
+                   void* pack, long pack_elems, void* stream) {
+    GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    GPK_ARG(X && alpha && hyp && pack, "null pointer");
+    GPK_ARG(d >= 1 && d <= HYP_MAXD && n > 0, "n / d");
+    GPK_ARG(pack_elems >= gpk_pack_train_elems(n, d), "pack buffer too small");
+    const long tiles = (n + TP - 1) / TP;
+    const int dp = pad_dim(d);
+    const unsigned blocks = (unsigned)((tiles * TP + 255) / 256);
+    if (dtype == 0)
+        pack_train_kernel<float><<<blocks, 256, 0, (cudaStream_t)stream>>>(X, ldx, n, d, dp, alpha, hyp, (float*)pack, tiles);
+    else
+        pack_train_kernel<double><<<blocks, 256, 0, (cudaStream_t)stream>>>(X, ldx, n, d, dp, alpha, hyp, (double*)pack, tiles);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+long gpk_mean_jac_work_bytes(int dtype, long q, long n, int d, int batch) {
+    // upper bound: every train tile its own split
+    const long tiles = (n + TP - 1) / TP;
+    return tiles * q * (pad_dim(d) + 1) * (dtype == 0 ? 4 : 8) * batch;
+}
+
+// fused posterior mean + Jacobian for `batch` GPs of identical shape.
+int gpk_predict_mean_jac(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                         const void* pack, long stride_pack, long n, void* mean, long stride_mean, void* jac,
+                         long ldj, long stride_jac, void* work, long work_bytes, int batch, void* stream) {
+    GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    GPK_ARG(Z && hyp && pack && mean && jac, "null pointer");
+    GPK_ARG(d >= 1 && d <= HYP_MAXD && n > 0 && batch >= 1, "n / d / batch");
+    if (q == 0) return 0;
+    GPK_ARG(q > 0 && ldz >= d && ldj >= d, "q / ldz / ldj");
+    GPK_ARG(((uintptr_t)pack % 16) == 0, "pack must be 16-byte aligned");
+    const int dp = pad_dim(d);
+    const int esz = dtype == 0 ? 4 : 8;
+    MeanJacArgs a{};
+    a.Z = Z; a.ldz = ldz; a.q = q; a.strideZ = strideZ; a.d = d; a.hyp = hyp;
+    a.pack = pack; a.stride_pack = stride_pack;
+    a.n_tiles = (int)((n + TP - 1) / TP);
+    a.mean = mean; a.stride_mean = stride_mean; a.jac = jac; a.ldj = ldj; a.stride_jac = stride_jac;
+    // split the training set over CTAs when the query count alone cannot fill the machine (~2 waves)
+    const long per_block = MJ_THREADS * (dtype == 0 && dp < 32 ? 2 : 1);
+    const long qblocks = (q + per_block - 1) / per_block * batch;
+    int n_split = (int)((148L * 8 + qblocks - 1) / qblocks);
+    if (n_split > a.n_tiles) n_split = a.n_tiles;
+    if (n_split < 1) n_split = 1;
+    const long need = (long)n_split * q * (dp + 1) * esz * batch;
+    if (n_split > 1 && (work == nullptr || work_bytes < need)) {
+        n_split = 1;   // caller gave no scratch: fall back to one CTA row per query block
+    }
+    a.tiles_per_split = (a.n_tiles + n_split - 1) / n_split;
+    a.n_split = (a.n_tiles + a.tiles_per_split - 1) / a.tiles_per_split;
+    a.work = work;
+    a.stride_work = (long)a.n_split * q * (dp + 1);
+    if (dtype == 0) return launch_mean_jac<float>(a, dp, batch, (cudaStream_t)stream);
+    return launch_mean_jac<double>(a, dp, batch, (cudaStream_t)stream);
+}
+
+int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,
+                     const double* hyp, void* var, long stride_var, int batch, void* stream) {
+    GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    GPK_ARG(colsq && hyp && var && tiles_m >= 1 && q > 0, "arguments");
+    dim3 grid((unsigned)((q + 255) / 256), 1, (unsigned)batch);
+    if (dtype == 0)
+        var_finalize_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(colsq, ld, stride_colsq, tiles_m, q, hyp, (float*)var, stride_var);
+    else
+        var_finalize_kernel<double><<<grid, 256, 0, (cudaStream_t)stream>>>(colsq, ld, stride_colsq, tiles_m, q, hyp, (double*)var, stride_var);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+long gpk_grad_trace_work_elems(long n, int d, long r0, long r1) {
+    const long by = (r1 - r0 + CK_T - 1) / CK_T, bx = (n + CK_T - 1) / CK_T;
+    return by * bx * (pad_dim(d) + 2);
+}
+
+// out[0] = tr G over rows [r0,r1), out[1] = sum G*K_f, out[2+j] = sum G*K_f*(x~_aj - x~_bj)^2, j < d
+int gpk_mll_grad_reduce(const double* X, long ldx, long n, int d, const double* hyp, const double* Kinv, long ldk,
+                        const double* alpha, long r0, long r1, double* work, long work_elems, double* out,
+                        void* stream) {
+    GPK_ARG(X && hyp && Kinv && alpha && work && out, "null pointer");
+    GPK_ARG(d >= 1 && d <= HYP_MAXD && n > 0, "n / d");
+    GPK_ARG(0 <= r0 && r0 < r1 && r1 <= n, "row range");
+    GPK_ARG(work_elems >= gpk_grad_trace_work_elems(n, d, r0, r1), "scratch too small");
+    const int dp = pad_dim(d);
+    dim3 grid((unsigned)((n + CK_T - 1) / CK_T), (unsigned)((r1 - r0 + CK_T - 1) / CK_T));
+    cudaStream_t st = (cudaStream_t)stream;
+#define GT_CASE(DPV) case DPV: grad_trace_kernel<DPV><<<grid, 256, 0, st>>>(X, ldx, n, d, hyp, Kinv, ldk, alpha, r0, r1, work); break;
+    switch (dp) {
+        GT_CASE(1) GT_CASE(2) GT_CASE(3) GT_CASE(4) GT_CASE(8) GT_CASE(16) GT_CASE(32)
+        default: return fail(-1, "grad_trace: unsupported padded dimension %d", dp);
+    }
+#undef GT_CASE
+    GPK_LAUNCHED();
+    reduce_partials_kernel<<<dp + 2, 256, 0, st>>>(work, (long)grid.x * grid.y, dp + 2, out);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+}  // extern "C"

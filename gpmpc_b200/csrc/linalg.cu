@@ -1,0 +1,440 @@
+// Blocked fp64 Cholesky / triangular inverse / K^-1 / alpha for the N x N training kernel matrix.
+//
+// Replaces what the reference reaches through gpytorch -> torch LAPACK at gpmpc/gp.py:62 (potrf + solves
+// inside ExactMarginalLogLikelihood) and gpmpc/gp.py:46 (torch.linalg.inv), see SURVEY.md section 2.
+// Everything O(N^3) is expressed through ONE tensor-pipe kernel, the DMMA "NT" GEMM of dgemm_nt.cuh:
+//   potrf   : recursive right-looking Cholesky; leaves are 128x128 single-CTA factorisations that also
+//             emit the inverse of the diagonal block, so every triangular solve becomes a GEMM
+//   trtri   : W = L^-1 (lower) and U = W^T (upper), recursive, two triangular GEMMs per level
+//   kinv    : K^-1 = U U^T (lower tiles on the tensor pipe, mirrored afterwards)
+//   alpha   : t = W y, alpha = U t (two triangular GEMVs, HBM-bound), quad = |t|^2, logdet = 2 sum log L_ii
+// All matrices are row-major, padded to a multiple of 128 with an identity block (see engine.py).
+#include "dgemm_nt.cuh"
+
+namespace gpk {
+
+thread_local char g_err[512] = {0};
+std::atomic<long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+// ------------------------------------------------------------------------------------------------
+// GEMM launcher
+// ------------------------------------------------------------------------------------------------
+int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
+    GPK_ARG(p.M > 0 && p.N > 0 && p.K > 0, "empty GEMM");
+    GPK_ARG(p.M % G_BM == 0 && p.N % G_BN == 0 && p.K % G_BK == 0, "GEMM dims must be multiples of 128/128/16");
+    GPK_ARG(p.lda % 2 == 0 && p.ldb % 2 == 0, "lda/ldb must be even");
+    GPK_ARG(((uintptr_t)p.A % 16) == 0 && ((uintptr_t)p.B % 16) == 0, "A/B must be 16-byte aligned");
+    if (epilogue == 0) GPK_ARG(p.ldc % 2 == 0 && ((uintptr_t)p.C % 16) == 0, "C must be 16-byte aligned with even ldc");
+    if (epilogue == 1) GPK_ARG(p.colsq != nullptr, "colsq output missing");
+    p.tiles_m = p.M / G_BM;
+    p.tiles_n = p.N / G_BN;
+    p.group_m = p.tiles_m <= 18 ? p.tiles_m : 12;
+    p.group_n = 148 / p.group_m > 0 ? 148 / p.group_m : 1;
+    static bool attr_done[2] = {false, false};
+    if (!attr_done[epilogue]) {
+        if (epilogue == 0)
+            GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+        else
+            GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+        attr_done[epilogue] = true;
+    }
+    dim3 grid((unsigned)(p.tiles_m * p.tiles_n), 1, (unsigned)batch);
+    if (epilogue == 0)
+        dgemm_nt_kernel<0><<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
+    else
+        dgemm_nt_kernel<1><<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+static GemmParams gemm_args(const double* A, long lda, const double* B, long ldb, double* C, long ldc, long M, long N,
+                            long K, double alpha, double beta, int a_tri, int c_lower) {
+    GemmParams p{};
+    p.A = A; p.B = B; p.C = C;
+    p.lda = lda; p.ldb = ldb; p.ldc = ldc;
+    p.M = (int)M; p.N = (int)N; p.K = (int)K;
+    p.alpha = alpha; p.beta = beta;
+    p.a_tri = a_tri; p.c_lower = c_lower;
+    return p;
+}
+
+// ------------------------------------------------------------------------------------------------
+// 128x128 leaf: Cholesky of a diagonal block in shared memory + inverse of its factor
+// ------------------------------------------------------------------------------------------------
+constexpr int P_N = 128, P_LD = 129;
+constexpr int P_SMEM = (P_N * P_LD + 256) * 8;
+
+__global__ void __launch_bounds__(256, 1)
+potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, int* __restrict__ info, int row_offset) {
+    extern __shared__ __align__(16) double S[];
+    double* scratch = S + P_N * P_LD;
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < P_N * (P_N / 2); idx += 256) {
+        const int r = idx >> 6, c = (idx & 63) * 2;
+        const double2 v = *reinterpret_cast<const double2*>(A + (long)r * lda + c);
+        S[r * P_LD + c] = v.x;
+        S[r * P_LD + c + 1] = v.y;
+    }
+    __syncthreads();
+    const int row = tid & 127, half = tid >> 7;
+
+    // --- right-looking Cholesky, one column per step (lower triangle) ---
+    for (int j = 0; j < P_N; j++) {
+        double d = S[j * P_LD + j];
+        if (!(d > 0.0) || isinf(d)) {           // also catches NaN
+            if (tid == 0) atomicCAS(info, 0, row_offset + j + 1);
+            d = 1.0;
+        }
+        const double r = sqrt(d), rinv = 1.0 / r;
+        __syncthreads();                        // pivot read by everyone before it is overwritten
+        double lij = 0.0;
+        if (row > j) {
+            lij = S[row * P_LD + j] * rinv;
+            if (half == 0) S[row * P_LD + j] = lij;
+        }
+        if (tid == j) S[j * P_LD + j] = r;
+        __syncthreads();                        // column j is final
+        if (row > j)
+            for (int c = j + 1 + half; c <= row; c += 2) S[row * P_LD + c] -= lij * S[c * P_LD + j];
+        __syncthreads();
+    }
+    // L (lower incl. diagonal) back to global; the strict upper part of the block is left untouched
+    for (int idx = tid; idx < P_N * P_N; idx += 256) {
+        const int r = idx >> 7, c = idx & 127;
+        if (c <= r) A[(long)r * lda + c] = S[r * P_LD + c];
+    }
+    for (int idx = tid; idx < P_N * P_N; idx += 256) {
+        const int r = idx >> 7, c = idx & 127;
+        if (c > r) S[r * P_LD + c] = 0.0;
+    }
+    __syncthreads();
+
+    // --- in-place inverse of the lower-triangular factor (column sweep from the right, LAPACK dtrti2) ---
+    for (int j = P_N - 1; j >= 0; j--) {
+        const double ajj = 1.0 / S[j * P_LD + j];
+        double part = 0.0;
+        if (row > j)
+            for (int c = j + 1 + half; c <= row; c += 2) part = fma(S[row * P_LD + c], S[c * P_LD + j], part);
+        scratch[half * P_N + row] = part;
+        __syncthreads();                        // column j fully read; partial sums visible
+        if (half == 0) {
+            if (row > j) S[row * P_LD + j] = -ajj * (scratch[row] + scratch[P_N + row]);
+            else if (row == j) S[j * P_LD + j] = ajj;
+        }
+        __syncthreads();
+    }
+    for (int idx = tid; idx < P_N * P_N; idx += 256) {
+        const int r = idx >> 7, c = idx & 127;
+        Dinv[r * P_N + c] = S[r * P_LD + c];
+    }
+}
+
+static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_offset, cudaStream_t st) {
+    static bool attr_done = false;
+    if (!attr_done) {
+        GPK_CUDA(cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+        attr_done = true;
+    }
+    potf2_inv_kernel<<<1, 256, P_SMEM, st>>>(A, lda, Dinv, info, row_offset);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// small memory-bound helpers
+// ------------------------------------------------------------------------------------------------
+// dst[c][r] = src[r][c]  for a rows x cols block
+__global__ void transpose_kernel(const double* __restrict__ src, long lds, double* __restrict__ dst, long ldd, int rows,
+                                 int cols) {
+    __shared__ double tile[32][33];
+    const int bx = blockIdx.x * 32, by = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = by + i, c = bx + threadIdx.x;
+        if (r < rows && c < cols) tile[i][threadIdx.x] = src[(long)r * lds + c];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = bx + i, r = by + threadIdx.x;
+        if (r < rows && c < cols) dst[(long)c * ldd + r] = tile[threadIdx.x][i];
+    }
+}
+
+static int launch_transpose(const double* src, long lds, double* dst, long ldd, long rows, long cols, cudaStream_t st) {
+    dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32));
+    transpose_kernel<<<grid, dim3(32, 8), 0, st>>>(src, lds, dst, ldd, (int)rows, (int)cols);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+// upper[r][c] = lower[c][r] for c > r (mirror the computed lower triangle of a symmetric matrix)
+__global__ void mirror_lower_kernel(double* __restrict__ A, long lda, int n) {
+    __shared__ double tile[32][33];
+    const int bx = blockIdx.x, by = blockIdx.y;   // tile (by, bx) with by >= bx is the source
+    if (by < bx) return;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = by * 32 + i, c = bx * 32 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < n && c < n) ? A[(long)r * lda + c] : 0.0;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = bx * 32 + i, c = by * 32 + threadIdx.x;      // destination element (r, c) = source (c, r)
+        if (r < n && c < n && c > r) A[(long)r * lda + c] = tile[threadIdx.x][i];
+    }
+}
+
+// y[i] = sum_{k<=i} A[i][k] x[k]  (mode 0, lower)   or   sum_{k>=i} A[i][k] x[k]  (mode 1, upper); one warp per row
+__global__ void trmv_rows_kernel(const double* __restrict__ A, long lda, int n, const double* __restrict__ x,
+                                 double* __restrict__ y, int mode) {
+    const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= n) return;
+    const int k0 = mode == 0 ? 0 : (row & ~1);
+    const int k1 = mode == 0 ? ((row + 2) & ~1) : n;      // exclusive, even; the other triangle holds exact zeros
+    const double* a = A + (long)row * lda;
+    double s = 0.0;
+    for (int k = k0 + 2 * lane; k < k1; k += 64) {
+        const double2 av = *reinterpret_cast<const double2*>(a + k);
+        const double2 xv = *reinterpret_cast<const double2*>(x + k);
+        s = fma(av.x, xv.x, s);
+        s = fma(av.y, xv.y, s);
+    }
+    s = warp_sum(s);
+    if (lane == 0) y[row] = s;
+}
+
+// out[0] = sum t_i^2 ; out[1] = 2 sum log L_ii   (single block)
+__global__ void fit_scalars_kernel(const double* __restrict__ t, const double* __restrict__ L, long ldl, int n,
+                                   double* __restrict__ out) {
+    __shared__ double sq[32], sl[32];
+    double q = 0.0, l = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        q = fma(t[i], t[i], q);
+        l += log(L[(long)i * ldl + i]);
+    }
+    q = warp_sum(q);
+    l = warp_sum(l);
+    if ((threadIdx.x & 31) == 0) { sq[threadIdx.x >> 5] = q; sl[threadIdx.x >> 5] = l; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int nw = blockDim.x >> 5;
+        q = threadIdx.x < nw ? sq[threadIdx.x] : 0.0;
+        l = threadIdx.x < nw ? sl[threadIdx.x] : 0.0;
+        q = warp_sum(q);
+        l = warp_sum(l);
+        if (threadIdx.x == 0) { out[0] = q; out[1] = 2.0 * l; }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// recursions (host side; every step is enqueued on `st`, no synchronisation)
+// ------------------------------------------------------------------------------------------------
+struct Rec {
+    cudaStream_t st;
+    double* A;      // matrix being factored (lower triangle), lda
+    long lda;
+    double* Dinv;   // (n/128) inverted diagonal blocks, 128x128 each
+    int* info;
+};
+
+static long split(long n) { return (n / TILE / 2) * TILE; }   // n >= 256, multiple of 128
+
+// B (m x n at rows r0.., cols c0..) <- B * L^-T, L = A[c0:c0+n, c0:c0+n]
+static int trsm_rec(const Rec& r, long r0, long m, long c0, long n) {
+    double* Bp = r.A + r0 * r.lda + c0;
+    if (n == TILE) {
+        const double* Di = r.Dinv + (c0 / TILE) * TILE * TILE;
+        // in place: one CTA owns all 128 columns of its rows and has consumed them before its epilogue
+        return launch_dgemm_nt(gemm_args(Bp, r.lda, Di, TILE, Bp, r.lda, m, TILE, TILE, 1.0, 0.0, 0, 0), 0, 1, r.st);
+    }
+    const long n1 = split(n), n2 = n - n1;
+    GPK_TRY(trsm_rec(r, r0, m, c0, n1));
+    // B2 -= B1 * Lb^T,  Lb = A[c0+n1 : c0+n, c0 : c0+n1]
+    GPK_TRY(launch_dgemm_nt(gemm_args(Bp, r.lda, r.A + (c0 + n1) * r.lda + c0, r.lda, Bp + n1, r.lda, m, n2, n1, -1.0,
+                                      1.0, 0, 0), 0, 1, r.st));
+    return trsm_rec(r, r0, m, c0 + n1, n2);
+}
+
+static int potrf_rec(const Rec& r, long off, long n) {
+    if (n == TILE)
+        return launch_potf2(r.A + off * r.lda + off, r.lda, r.Dinv + (off / TILE) * TILE * TILE, r.info, (int)off, r.st);
+    const long n1 = split(n), n2 = n - n1;
+    GPK_TRY(potrf_rec(r, off, n1));
+    GPK_TRY(trsm_rec(r, off + n1, n2, off, n1));
+    double* A21 = r.A + (off + n1) * r.lda + off;
+    double* A22 = r.A + (off + n1) * r.lda + off + n1;
+    GPK_TRY(launch_dgemm_nt(gemm_args(A21, r.lda, A21, r.lda, A22, r.lda, n2, n2, n1, -1.0, 1.0, 0, 1), 0, 1, r.st));
+    return potrf_rec(r, off + n1, n2);
+}
+
+struct RecInv {
+    cudaStream_t st;
+    const double* L; long ldl;
+    const double* Dinv;
+    double* W; long ldw;
+    double* U; long ldu;
+    double* T;      // scratch, at least (n/2 rounded) x (n/2 rounded) doubles
+};
+
+static int trtri_rec(const RecInv& r, long off, long n) {
+    if (n == TILE) {
+        const double* Di = r.Dinv + (off / TILE) * TILE * TILE;
+        GPK_CUDA(cudaMemcpy2DAsync(r.W + off * r.ldw + off, r.ldw * 8, Di, TILE * 8, TILE * 8, TILE,
+                                   cudaMemcpyDeviceToDevice, r.st));
+        return launch_transpose(Di, TILE, r.U + off * r.ldu + off, r.ldu, TILE, TILE, r.st);
+    }
+    const long n1 = split(n), n2 = n - n1;
+    GPK_TRY(trtri_rec(r, off, n1));
+    GPK_TRY(trtri_rec(r, off + n1, n2));
+    // T (n1 x n2) = U11 * L21^T     (= (L21 W11)^T; U11 upper triangular)
+    const double* U11 = r.U + off * r.ldu + off;
+    const double* L21 = r.L + (off + n1) * r.ldl + off;
+    GPK_TRY(launch_dgemm_nt(gemm_args(U11, r.ldu, L21, r.ldl, r.T, n2, n1, n2, n1, 1.0, 0.0, 2, 0), 0, 1, r.st));
+    // W21 (n2 x n1) = - W22 * T^T   (W22 lower triangular)
+    const double* W22 = r.W + (off + n1) * r.ldw + off + n1;
+    double* W21 = r.W + (off + n1) * r.ldw + off;
+    GPK_TRY(launch_dgemm_nt(gemm_args(W22, r.ldw, r.T, n2, W21, r.ldw, n2, n1, n2, -1.0, 0.0, 1, 0), 0, 1, r.st));
+    // U12 = W21^T
+    return launch_transpose(W21, r.ldw, r.U + off * r.ldu + off + n1, r.ldu, n2, n1, r.st);
+}
+
+}  // namespace gpk
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+using namespace gpk;
+
+extern "C" {
+
+const char* gpk_last_error(void) { return g_err; }
+long gpk_launch_count(void) { return g_launches.load(); }
+void gpk_reset_launch_count(void) { g_launches.store(0); }
+int gpk_abi_version(void) { return 1; }
+
+int gpk_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C, long ldc, long M, long N, long K,
+                 double alpha, double beta, int a_tri, int c_lower, void* stream) {
+    return launch_dgemm_nt(gemm_args(A, lda, B, ldb, C, ldc, M, N, K, alpha, beta, a_tri, c_lower), 0, 1,
+                           (cudaStream_t)stream);
+}
+
+int gpk_potrf(double* A, long lda, long npad, double* dinv, int* info_dev, void* stream) {
+    GPK_ARG(npad > 0 && npad % TILE == 0, "npad must be a positive multiple of 128");
+    GPK_ARG(lda >= npad && lda % 2 == 0, "lda");
+    GPK_ARG(A && dinv && info_dev, "null pointer");
+    Rec r{(cudaStream_t)stream, A, lda, dinv, info_dev};
+    GPK_CUDA(cudaMemsetAsync(info_dev, 0, sizeof(int), r.st));
+    return potrf_rec(r, 0, npad);
+}
+
+int gpk_trtri(const double* L, long ldl, long npad, const double* dinv, double* W, long ldw, double* U, long ldu,
+              double* tmp, long tmp_elems, void* stream) {
+    GPK_ARG(npad > 0 && npad % TILE == 0, "npad must be a positive multiple of 128");
+    GPK_ARG(L && dinv && W && U, "null pointer");
+    GPK_ARG(ldw >= npad && ldu >= npad && ldw % 2 == 0 && ldu % 2 == 0, "ldw/ldu");
+    if (npad > TILE) {
+        const long n1 = split(npad), n2 = npad - n1;
+        GPK_ARG(tmp && tmp_elems >= n1 * n2, "scratch too small (need split(n) * (n - split(n)) doubles)");
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    GPK_CUDA(cudaMemset2DAsync(W, ldw * 8, 0, npad * 8, npad, st));
+    GPK_CUDA(cudaMemset2DAsync(U, ldu * 8, 0, npad * 8, npad, st));
+    RecInv r{st, L, ldl, dinv, W, ldw, U, ldu, tmp};
+    return trtri_rec(r, 0, npad);
+}
+
+long gpk_trtri_scratch_elems(long npad) {
+    if (npad <= TILE) return 0;
+    const long n1 = split(npad);
+    return n1 * (npad - n1);
+}
+
+int gpk_kinv(const double* U, long ldu, long npad, double* Kinv, long ldk, void* stream) {
+    GPK_ARG(npad > 0 && npad % TILE == 0, "npad must be a positive multiple of 128");
+    cudaStream_t st = (cudaStream_t)stream;
+    // lower tiles of U U^T on the tensor pipe, then mirror
+    GPK_TRY(launch_dgemm_nt(gemm_args(U, ldu, U, ldu, Kinv, ldk, npad, npad, npad, 1.0, 0.0, 2, 1), 0, 1, st));
+    dim3 grid((unsigned)(npad / 32), (unsigned)(npad / 32));
+    mirror_lower_kernel<<<grid, dim3(32, 8), 0, st>>>(Kinv, ldk, (int)npad);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+// t = W y ; alpha = U t ; scal[0] = y^T K^-1 y ; scal[1] = log det K
+int gpk_solve_alpha(const double* W, long ldw, const double* U, long ldu, const double* L, long ldl, long npad,
+                    const double* y, double* t_work, double* alpha, double* scal, void* stream) {
+    GPK_ARG(npad > 0 && npad % TILE == 0, "npad must be a positive multiple of 128");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int wpb = 8;
+    trmv_rows_kernel<<<(unsigned)((npad + wpb - 1) / wpb), wpb * 32, 0, st>>>(W, ldw, (int)npad, y, t_work, 0);
+    GPK_LAUNCHED();
+    trmv_rows_kernel<<<(unsigned)((npad + wpb - 1) / wpb), wpb * 32, 0, st>>>(U, ldu, (int)npad, t_work, alpha, 1);
+    GPK_LAUNCHED();
+    fit_scalars_kernel<<<1, 1024, 0, st>>>(t_work, L, ldl, (int)npad, scal);
+    GPK_LAUNCHED();
+    return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// posterior variance  var_f(z) = sf2 - || W k(X,z) ||^2 ,  W = L^-1   (gpmpc/gpmpc.py:443-445 keeps only
+// this diagonal of the posterior covariance).  Per chunk of queries: (1) K_ZX written once to HBM by the
+// SIMT cross kernel, (2) triangular DMMA GEMM V = W K_ZX^T whose epilogue reduces V to per-tile column
+// sums of squares (V is never stored, the Q x Q covariance is never formed), (3) finalise.
+// ------------------------------------------------------------------------------------------------
+extern "C" int gpk_cross_kernel(int dtype_a, const void* A, long lda, long na, long strideA, const double* B, long ldb,
+                                long nb, long strideB, int d, const double* hyp, double* out, long ldo, long strideO,
+                                long rows_pad, long cols_pad, int mode, int batch, void* stream);
+extern "C" int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,
+                                const double* hyp, void* var, long stride_var, int batch, void* stream);
+
+extern "C" long gpk_predict_var_work_bytes(long q_chunk, long npad, int batch) {
+    const long qc = (q_chunk + TILE - 1) / TILE * TILE;
+    return (qc * npad + (npad / TILE) * qc) * 8 * batch;
+}
+
+extern "C" int gpk_predict_var(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                               const double* X, long ldx, long n, long strideX, const double* W, long ldw,
+                               long strideW, long npad, void* var, long stride_var, void* work, long work_bytes,
+                               int batch, void* stream) {
+    GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    GPK_ARG(Z && hyp && X && W && var && work, "null pointer");
+    GPK_ARG(npad % TILE == 0 && npad >= n && n > 0 && batch >= 1, "n / npad / batch");
+    if (q == 0) return 0;
+    const int tiles_m = (int)(npad / TILE);
+    // largest query chunk (multiple of 128) whose K_ZX block and column partials fit the scratch
+    long qc = work_bytes / ((npad + tiles_m) * 8 * batch);
+    qc = qc / TILE * TILE;
+    GPK_ARG(qc >= TILE, "scratch too small (see gpk_predict_var_work_bytes)");
+    const long q_round = (q + TILE - 1) / TILE * TILE;
+    if (qc > q_round) qc = q_round;
+    double* kzx = (double*)work;                       // [batch][qc][npad]
+    double* colsq = kzx + (long)batch * qc * npad;     // [batch][tiles_m][qc]
+    const int esz = dtype == 0 ? 4 : 8;
+    cudaStream_t st = (cudaStream_t)stream;
+    for (long q0 = 0; q0 < q; q0 += qc) {
+        const long qn = (q - q0 < qc) ? (q - q0) : qc;             // valid queries in this chunk
+        const long qp = (qn + TILE - 1) / TILE * TILE;             // padded
+        const void* Zc = (const char*)Z + q0 * ldz * esz;
+        GPK_TRY(gpk_cross_kernel(dtype, Zc, ldz, qn, strideZ, X, ldx, n, strideX, d, hyp, kzx, npad, qc * npad, qp,
+                                 npad, 0, batch, st));
+        GemmParams p = gemm_args(W, ldw, kzx, npad, nullptr, 0, npad, qp, npad, 1.0, 0.0, 1, 0);
+        p.strideA = strideW;
+        p.strideB = qc * npad;
+        p.colsq = colsq;
+        p.ld_colsq = qc;
+        p.stride_colsq = (long)tiles_m * qc;
+        GPK_TRY(launch_dgemm_nt(p, 1, batch, st));
+        void* vout = (char*)var + q0 * esz;
+        GPK_TRY(gpk_var_finalize(dtype, colsq, qc, (long)tiles_m * qc, tiles_m, qn, hyp, vout, stride_var, batch, st));
+    }
+    return 0;
+}

@@ -1,0 +1,404 @@
+"""Device-side engine of the GP hot path: owns the HBM buffers and drives the C ABI (include/gpmpc_b200.h).
+
+Everything numeric happens in libgpmpc_b200.so (hand-written sm_100a CUDA); torch is used for device
+memory, streams and the tiny host<->device scalar traffic only.  There is no CPU path.
+
+HBM layout (row-major, float64 unless noted; npad = N rounded up to 128, identity on the padding):
+  X      (N, d)          training inputs, raw (centred / scaled on the fly inside the kernels)
+  hyp    (72,)           centre[32] | 1/ell[32] | sf2 | noise | pad      (per GP)
+  L      (npad, npad)    K = K_f + noise I, overwritten by its lower Cholesky factor   (fit scratch)
+  W, U   (npad, npad)    W = L^-1 (lower, kept for the variance), U = W^T (fit scratch)
+  Kinv   (npad, npad)    K^-1 = U U^T, only when the MLL gradient or gp.K_inv is wanted (fit scratch)
+  alpha  (npad,)         K^-1 y, zero on the padding
+  pack   tiles of 256 training points [x~ | -1/2|x~|^2 | sf2 alpha] in the prediction dtype
+"""
+
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import torch
+
+from . import _lib
+from ._lib import call, ptr
+
+TILE = 128
+LOG_2PI = math.log(2.0 * math.pi)
+F64 = torch.float64
+DTYPE_CODE = {torch.float32: 0, torch.float64: 1}
+
+
+class NotPSDError(RuntimeError):
+    """K + noise I was not positive definite even after the jitter retries (gpytorch's NotPSDError)."""
+
+
+def round_up(n: int, m: int) -> int:
+    return (n + m - 1) // m * m
+
+
+def make_hyp(center, ell, sf2: float, noise: float, d: int, device) -> torch.Tensor:
+    """Hyper-parameter block for the kernels (layout in include/gpmpc_b200.h), built on the host."""
+    stride = _lib.load().gpk_hyp_stride()
+    h = torch.zeros(stride, dtype=F64)
+    ell = torch.as_tensor(ell, dtype=F64).reshape(-1).cpu()
+    if ell.numel() == 1:
+        ell = ell.expand(d)
+    assert ell.numel() == d and d <= 32, "lengthscale must have 1 or d entries, d <= 32"
+    h[:d] = torch.as_tensor(center, dtype=F64).reshape(-1).cpu()
+    h[32:64] = 1.0
+    h[32 : 32 + d] = 1.0 / ell
+    h[64] = float(sf2)
+    h[65] = float(noise)
+    return h.to(device, non_blocking=True)
+
+
+@dataclass
+class FitScratch:
+    """Scratch for fitting one GP of padded size npad; reused across GPs and MLL iterations."""
+
+    npad: int
+    device: torch.device
+    L: torch.Tensor = None
+    U: torch.Tensor = None
+    T: torch.Tensor = None
+    dinv: torch.Tensor = None
+    t_work: torch.Tensor = None
+    scal: torch.Tensor = None
+    info: torch.Tensor = None
+    Kinv: torch.Tensor = None
+    grad_work: torch.Tensor = None
+    grad_out: torch.Tensor = None
+    y_pad: torch.Tensor = None
+
+    def __post_init__(self):
+        lib = _lib.load()
+        n, dev = self.npad, self.device
+        self.L = torch.empty(n, n, dtype=F64, device=dev)
+        self.U = torch.empty(n, n, dtype=F64, device=dev)
+        self.T = torch.empty(max(1, lib.gpk_trtri_scratch_elems(n)), dtype=F64, device=dev)
+        self.dinv = torch.empty(n * TILE, dtype=F64, device=dev)
+        self.t_work = torch.empty(n, dtype=F64, device=dev)
+        self.scal = torch.zeros(2, dtype=F64, device=dev)
+        self.info = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.grad_out = torch.zeros(34, dtype=F64, device=dev)
+        self.y_pad = torch.zeros(n, dtype=F64, device=dev)
+
+    def need_kinv(self):
+        if self.Kinv is None:
+            self.Kinv = torch.empty(self.npad, self.npad, dtype=F64, device=self.device)
+        return self.Kinv
+
+
+_scratch_cache: dict = {}
+
+
+def get_fit_scratch(npad: int, device: torch.device) -> FitScratch:
+    key = (npad, device.index)
+    if key not in _scratch_cache:
+        # keep at most one size per device alive: the big configs need the memory back
+        for k in [k for k in _scratch_cache if k[1] == device.index]:
+            del _scratch_cache[k]
+        _scratch_cache[key] = FitScratch(npad, device)
+    return _scratch_cache[key]
+
+
+def release_scratch():
+    _scratch_cache.clear()
+    _work_cache.clear()
+
+
+_work_cache: dict = {}
+
+
+def get_work(name: str, nbytes: int, device: torch.device) -> torch.Tensor:
+    """Grow-only byte scratch per (name, device)."""
+    key = (name, device.index)
+    t = _work_cache.get(key)
+    if t is None or t.numel() < nbytes:
+        _work_cache[key] = t = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+    return t
+
+
+@dataclass
+class GPFit:
+    """Fitted state of one exact GP at fixed hyper-parameters (what gpytorch's prediction strategy caches)."""
+
+    X: torch.Tensor            # (N, d) float64, device
+    y: torch.Tensor            # (N,)
+    n: int
+    d: int
+    npad: int
+    center: torch.Tensor       # (d,) host float64
+    ell: torch.Tensor          # (d,) host float64
+    sf2: float
+    noise: float
+    hyp: torch.Tensor          # (72,) device
+    W: torch.Tensor            # (npad, npad) L^-1
+    alpha: torch.Tensor        # (npad,)
+    quad: float = float("nan")
+    logdet: float = float("nan")
+    jitter: float = 0.0
+    packs: dict = field(default_factory=dict)
+
+    @property
+    def device(self):
+        return self.X.device
+
+    def mll_per_n(self) -> float:
+        """log p(y) / N  (what ExactMarginalLogLikelihood returns, gpmpc/gp.py:57,62)."""
+        return -0.5 * (self.quad + self.logdet + self.n * LOG_2PI) / self.n
+
+    def pack(self, dtype: torch.dtype) -> torch.Tensor:
+        """Resident training pack for the fused mean/Jacobian kernel in the prediction dtype."""
+        if dtype not in self.packs:
+            lib = _lib.load()
+            elems = lib.gpk_pack_train_elems(self.n, self.d)
+            p = torch.empty(elems, dtype=dtype, device=self.device)
+            call("gpk_pack_train", DTYPE_CODE[dtype], ptr(self.X), self.X.stride(0), self.n, self.d, ptr(self.alpha),
+                 ptr(self.hyp), ptr(p), elems, _lib.stream_ptr(self.device))
+            self.packs[dtype] = p
+        return self.packs[dtype]
+
+
+def _as_device_f64(t: torch.Tensor, device) -> torch.Tensor:
+    return t.detach().to(device=device, dtype=F64).contiguous()
+
+
+def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *, center=None,
+              want_kinv: bool = False, W_out: torch.Tensor | None = None, max_tries: int = 3) -> tuple[GPFit, FitScratch]:
+    """Assemble K, Cholesky, W = L^-1, alpha, y^T K^-1 y and log det K on the GPU (float64).
+
+    Replaces the gpytorch work behind gpmpc/gp.py:61-62 (train mode) and the prediction-strategy cache
+    behind gpmpc/gpmpc.py:444 (eval mode).  On a failed pivot the diagonal jitter policy of gpytorch's
+    psd_safe_cholesky is applied (1e-8 for float64, x10 per retry, `max_tries` retries).
+    """
+    dev = _lib.require_cuda(X.device if X.is_cuda else None)
+    X = _as_device_f64(X, dev)
+    y = _as_device_f64(y, dev).reshape(-1)
+    n, d = X.shape
+    assert y.numel() == n, "x and y disagree on the number of training points"
+    npad = round_up(n, TILE)
+    ws = get_fit_scratch(npad, dev)
+    st = _lib.stream_ptr(dev)
+    ell_t = torch.as_tensor(ell, dtype=F64).reshape(-1).cpu()
+    if ell_t.numel() == 1:
+        ell_t = ell_t.expand(d).clone()
+    if center is None:
+        center = X.mean(dim=0)
+    center_h = torch.as_tensor(center, dtype=F64).reshape(-1).cpu()
+    W = W_out if W_out is not None else torch.empty(npad, npad, dtype=F64, device=dev)
+    alpha = torch.empty(npad, dtype=F64, device=dev)
+    ws.y_pad.zero_()
+    ws.y_pad[:n] = y
+
+    jitter = 0.0
+    for attempt in range(max_tries + 1):
+        hyp = make_hyp(center_h, ell_t, sf2, noise + jitter, d, dev)
+        call("gpk_cross_kernel", 1, ptr(X), X.stride(0), n, 0, ptr(X), X.stride(0), n, 0, d, ptr(hyp), ptr(ws.L),
+             npad, 0, npad, npad, 1, 1, st)
+        call("gpk_potrf", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(ws.info), st)
+        info = int(ws.info.item())          # the reference syncs here too (loss value / NotPSD check)
+        if info == 0:
+            break
+        if attempt == max_tries:
+            raise NotPSDError(f"K + noise I not positive definite after jitter {jitter:g} (potrf info={info})")
+        jitter = 1e-8 if jitter == 0.0 else jitter * 10.0
+    call("gpk_trtri", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(W), npad, ptr(ws.U), npad, ptr(ws.T), ws.T.numel(), st)
+    call("gpk_solve_alpha", ptr(W), npad, ptr(ws.U), npad, ptr(ws.L), npad, npad, ptr(ws.y_pad), ptr(ws.t_work),
+         ptr(alpha), ptr(ws.scal), st)
+    if want_kinv:
+        call("gpk_kinv", ptr(ws.U), npad, npad, ptr(ws.need_kinv()), npad, st)
+    quad, logdet = ws.scal.tolist()
+    fit = GPFit(X=X, y=y, n=n, d=d, npad=npad, center=center_h, ell=ell_t, sf2=float(sf2), noise=float(noise),
+                hyp=make_hyp(center_h, ell_t, sf2, noise, d, dev) if jitter else hyp, W=W, alpha=alpha,
+                quad=quad, logdet=logdet, jitter=jitter)
+    return fit, ws
+
+
+def grad_partials(fit: GPFit, ws: FitScratch, r0: int = 0, r1: int | None = None) -> torch.Tensor:
+    """(d+2) partial sums of the MLL gradient trace over rows [r0, r1) (device tensor, float64).
+    Needs ws.Kinv from factorize(want_kinv=True)."""
+    lib = _lib.load()
+    r1 = fit.n if r1 is None else r1
+    assert ws.Kinv is not None, "factorize(..., want_kinv=True) first"
+    elems = lib.gpk_grad_trace_work_elems(fit.n, fit.d, r0, r1)
+    work = get_work("grad", elems * 8, fit.device)
+    call("gpk_mll_grad_reduce", ptr(fit.X), fit.X.stride(0), fit.n, fit.d, ptr(fit.hyp), ptr(ws.Kinv), fit.npad,
+         ptr(fit.alpha), r0, r1, ptr(work), elems, ptr(ws.grad_out), _lib.stream_ptr(fit.device))
+    return ws.grad_out[: lib.gpk_pad_dim(fit.d) + 2]
+
+
+def loss_and_grad_from_partials(fit: GPFit, partials: torch.Tensor):
+    """loss = -MLL/N and d loss / d (noise, sf2, ell_j) from the reduced trace partials (host floats).
+    Closed form of SURVEY.md 8c: dMLL/dnoise = tr(G)/2, dMLL/dsf2 = sum(G K_f)/(2 sf2),
+    dMLL/dell_j = sum(G K_f (x_aj-x_bj)^2/ell_j^2) / (2 ell_j)."""
+    p = partials.tolist()
+    n = fit.n
+    loss = -fit.mll_per_n()
+    g_noise = -(0.5 * p[0]) / n
+    g_sf2 = -(0.5 * p[1] / fit.sf2) / n
+    g_ell = [-(0.5 * p[2 + j] / float(fit.ell[j])) / n for j in range(fit.d)]
+    return loss, g_noise, g_sf2, g_ell
+
+
+def dense_K(fit: GPFit) -> torch.Tensor:
+    """K_f(X,X) + noise I as a dense (N,N) tensor (gpmpc/gp.py:45)."""
+    n, npad = fit.n, round_up(fit.n, 64)
+    out = torch.empty(npad, npad, dtype=F64, device=fit.device)
+    call("gpk_cross_kernel", 1, ptr(fit.X), fit.X.stride(0), n, 0, ptr(fit.X), fit.X.stride(0), n, 0, fit.d,
+         ptr(fit.hyp), ptr(out), npad, 0, npad, npad, 1, 1, _lib.stream_ptr(fit.device))
+    return out[:n, :n]
+
+
+def cross_K(fit: GPFit, A: torch.Tensor, B: torch.Tensor | None = None) -> torch.Tensor:
+    """Noise-free K_f(A, B) with this GP's hyper-parameters (gp.covar_module(a, b).to_dense(), gpmpc.py:392-393)."""
+    dev = fit.device
+    A = _as_device_f64(A, dev)
+    B = A if B is None else _as_device_f64(B, dev)
+    na, nb = A.shape[0], B.shape[0]
+    rp, cp = round_up(na, 64), round_up(nb, 64)
+    out = torch.empty(rp, cp, dtype=F64, device=dev)
+    call("gpk_cross_kernel", 1, ptr(A), A.stride(0), na, 0, ptr(B), B.stride(0), nb, 0, fit.d, ptr(fit.hyp), ptr(out),
+         cp, 0, rp, cp, 0, 1, _lib.stream_ptr(dev))
+    return out[:na, :nb]
+
+
+@dataclass
+class GPBatch:
+    """`batch` fitted GPs of identical (N, d) stacked for one-launch prediction (grid.z = GP)."""
+
+    fits: list
+    X: torch.Tensor        # (B, N, d)
+    W: torch.Tensor        # (B, npad, npad)
+    hyp: torch.Tensor      # (B, 72)
+    packs: dict = field(default_factory=dict)
+
+    @classmethod
+    def from_fits(cls, fits: list) -> "GPBatch":
+        f0 = fits[0]
+        assert all(f.n == f0.n and f.d == f0.d and f.device == f0.device for f in fits), "GPs must share (N, d, device)"
+        if len(fits) == 1:
+            return cls(fits, f0.X[None], f0.W[None], f0.hyp[None])
+        # W tensors allocated by fit_batch are already slices of one (B, npad, npad) buffer
+        base = fits[0].W._base if fits[0].W._base is not None else None
+        if base is not None and base.dim() == 3 and base.shape[0] == len(fits) and all(
+            f.W._base is base and f.W.data_ptr() == base[i].data_ptr() for i, f in enumerate(fits)
+        ):
+            W = base
+        else:
+            W = torch.stack([f.W for f in fits])
+        X = torch.stack([f.X for f in fits])
+        hyp = torch.stack([f.hyp for f in fits])
+        return cls(fits, X, W, hyp)
+
+    @property
+    def n(self):
+        return self.fits[0].n
+
+    @property
+    def d(self):
+        return self.fits[0].d
+
+    @property
+    def npad(self):
+        return self.fits[0].npad
+
+    @property
+    def device(self):
+        return self.X.device
+
+    def pack(self, dtype):
+        if dtype not in self.packs:
+            self.packs[dtype] = torch.stack([f.pack(dtype) for f in self.fits])
+        return self.packs[dtype]
+
+
+def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise) -> GPBatch:
+    """Fit P independent GPs that share the inputs X (N,d) with targets Y (N,P) at fixed hyper-parameters.
+    ell: (P,d) or (d,) ; sf2, noise: (P,) or scalars.  The factors are written straight into one stacked buffer."""
+    dev = _lib.require_cuda(X.device if X.is_cuda else None)
+    X = _as_device_f64(X, dev)
+    Y = _as_device_f64(Y, dev)
+    n, d = X.shape
+    P = Y.shape[1]
+    npad = round_up(n, TILE)
+    Wall = torch.empty(P, npad, npad, dtype=F64, device=dev)
+    ell = torch.as_tensor(ell, dtype=F64)
+    fits = []
+    for p in range(P):
+        ell_p = ell[p] if ell.dim() == 2 else ell
+        sf2_p = float(sf2[p]) if hasattr(sf2, "__len__") else float(sf2)
+        noise_p = float(noise[p]) if hasattr(noise, "__len__") else float(noise)
+        f, _ = factorize(X, Y[:, p], ell_p, sf2_p, noise_p, W_out=Wall[p])
+        fits.append(f)
+    return GPBatch.from_fits(fits)
+
+
+VAR_WORK_BYTES = 4 << 30   # default scratch budget for the K_ZX chunks of the variance path
+
+
+def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_work_bytes: int | None = None):
+    """Posterior mean (B,Q), latent variance var_f (B,Q) and input-Jacobian (B,Q,d) at queries Z.
+
+    Z: (Q,d) shared by all GPs or (B,Q,d); float64 or float32 selects the prediction path.  The batched
+    entry configs 2-5 time; per stage it is what acados evaluates through gpytorch_predict2casadi
+    (gpmpc/gp.py:72-85) plus the variance diagonal of gpmpc/gpmpc.py:443-445.
+    """
+    if isinstance(gp, GPFit):
+        gp = GPBatch.from_fits([gp])
+    lib = _lib.load()
+    dev = gp.device
+    assert Z.dtype in DTYPE_CODE, "queries must be float32 or float64"
+    dt = Z.dtype
+    code = DTYPE_CODE[dt]
+    Z = Z.to(dev).contiguous()
+    B, n, d, npad = len(gp.fits), gp.n, gp.d, gp.npad
+    if Z.dim() == 2:
+        q, strideZ = Z.shape[0], 0
+    else:
+        assert Z.shape[0] == B
+        q, strideZ = Z.shape[1], Z.stride(0)
+    assert Z.shape[-1] == d
+    st = _lib.stream_ptr(dev)
+    mean = torch.empty(B, q, dtype=dt, device=dev)
+    jac = torch.empty(B, q, d, dtype=dt, device=dev)
+    var = torch.empty(B, q, dtype=dt, device=dev) if want_var else None
+    if q == 0:
+        return mean, var, jac
+    pack = gp.pack(dt)
+    wbytes = min(lib.gpk_mean_jac_work_bytes(code, q, n, d, B), 1 << 30)
+    work = get_work("mean_jac", wbytes, dev)
+    call("gpk_predict_mean_jac", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(pack), pack.stride(0), n,
+         ptr(mean), q, ptr(jac), d, q * d, ptr(work), wbytes, B, st)
+    if want_var:
+        budget = VAR_WORK_BYTES if var_work_bytes is None else var_work_bytes
+        need = lib.gpk_predict_var_work_bytes(q, npad, B)
+        vbytes = max(min(need, budget), lib.gpk_predict_var_work_bytes(TILE, npad, B))
+        vwork = get_work("var", vbytes, dev)
+        strideX = gp.X.stride(0) if B > 1 else 0
+        call("gpk_predict_var", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(gp.X), gp.X.stride(1), n,
+             strideX, ptr(gp.W), npad, gp.W.stride(0) if B > 1 else 0, npad, ptr(var), q, ptr(vwork), vbytes, B, st)
+    return mean, var, jac
+
+
+def posterior_covariance(fit: GPFit, Z: torch.Tensor) -> torch.Tensor:
+    """Dense latent posterior covariance K_zz - K_zX K^-1 K_Xz (Q,Q) for modest Q: the matrix
+    gp(z).covariance_matrix returns at gpmpc/gpmpc.py:444 (the caller keeps only its diagonal, for which
+    `predict` is the fast path).  Three tensor-pipe GEMMs: V^T = K_zX W^T, cov = K_zz - V^T V."""
+    dev = fit.device
+    Z = _as_device_f64(Z, dev)
+    q, npad = Z.shape[0], fit.npad
+    qp = round_up(max(q, 1), TILE)
+    st = _lib.stream_ptr(dev)
+    kzx = torch.empty(qp, npad, dtype=F64, device=dev)
+    vt = torch.empty(qp, npad, dtype=F64, device=dev)
+    cov = torch.empty(qp, qp, dtype=F64, device=dev)
+    X = fit.X
+    call("gpk_cross_kernel", 1, ptr(Z), Z.stride(0), q, 0, ptr(X), X.stride(0), fit.n, 0, fit.d, ptr(fit.hyp), ptr(kzx),
+         npad, 0, qp, npad, 0, 1, st)
+    call("gpk_cross_kernel", 1, ptr(Z), Z.stride(0), q, 0, ptr(Z), Z.stride(0), q, 0, fit.d, ptr(fit.hyp), ptr(cov),
+         qp, 0, qp, qp, 0, 1, st)
+    call("gpk_dgemm_nt", ptr(kzx), npad, ptr(fit.W), npad, ptr(vt), npad, qp, npad, npad, 1.0, 0.0, 0, 0, st)
+    call("gpk_dgemm_nt", ptr(vt), npad, ptr(vt), npad, ptr(cov), qp, qp, qp, npad, -1.0, 1.0, 0, 0, st)
+    return cov[:q, :q].clone()

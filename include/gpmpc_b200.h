@@ -1,0 +1,121 @@
+/* gpmpc_b200 -- C ABI of the B200-native Gaussian-process hot path of gp-mpc.
+ *
+ * One shared library (gpmpc_b200/libgpmpc_b200.so, sm_100a only).  Every entry point takes raw DEVICE
+ * pointers, explicit sizes / leading dimensions (in elements), an explicit cudaStream_t (passed as
+ * void*), and returns int:  0 = ok,  < 0 = bad argument (-1) or CUDA error (-(1000 + cudaError_t));
+ * numerical failure of the Cholesky is reported LAPACK-style through the device-side `info` word
+ * (first non-positive pivot, 1-based; 0 = ok).  Nothing is allocated, nothing synchronises; scratch is
+ * caller-provided.  gpk_last_error() returns the message of the last failing call on this thread.
+ *
+ * The reference has no FFI of its own: its GP layer is Python over gpytorch/torch.  Each
+ * entry below names the reference call site (file:line under the gp-mpc tree) whose library work it
+ * replaces; the Python binding a maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - matrices are row-major; "npad" is N rounded up to a multiple of 128, padded matrices carry an
+ *     identity block on the padding (K, L, W, U, K^-1) so that padded rows/columns are inert;
+ *   - dtype: 0 = float32, 1 = float64 (prediction entry points only; the fit is always float64, as in
+ *     the reference where float64 data promotes the kernel matrix, gpmpc/gpmpc.py:155-156);
+ *   - hyp: per-GP hyper-parameter block of gpk_hyp_stride() doubles in device memory:
+ *       [0..31] centre c_j, [32..63] 1/ell_j, [64] sf2 (outputscale), [65] noise (sigma^2);
+ *     inputs are used as (x - c) / ell, which is what gpytorch's RBFKernel does before its distance;
+ *   - batch: number of independent GPs of identical shape processed by one launch (grid.z); per-GP
+ *     buffers are addressed with the given element strides, a stride of 0 shares the buffer.
+ */
+#ifndef GPMPC_B200_H
+#define GPMPC_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- library info ------------------------------------------------------------------------- */
+int gpk_abi_version(void);
+const char* gpk_last_error(void);
+long gpk_launch_count(void);            /* kernels launched by this library since load / last reset */
+void gpk_reset_launch_count(void);
+int gpk_pad_dim(int d);                 /* padded input dimension used by packs (d <= 32), -1 if unsupported */
+int gpk_hyp_stride(void);               /* doubles per hyper-parameter block */
+int gpk_train_tile(void);               /* training points per pack tile */
+
+/* ---- (1) kernel assembly -------------------------------------------------------------------
+ * mode 0: out = K_f(A, B)           replaces gp.covar_module(a, b).to_dense()      gpmpc/gpmpc.py:392-393
+ * mode 1: out = K_f(A, A) + noise I replaces covar_module(X).add_diag(noise)       gpmpc/gp.py:45, and the
+ *         lazy K that gpytorch densifies inside the MLL                            gpmpc/gp.py:61-62
+ * kernel formula: gpmpc/gp.py:12-14.  A is dtype_a (0/1), B float64; out is rows_pad x cols_pad
+ * (multiples of 64) with zeros (mode 0) or identity (mode 1) on the padding. */
+int gpk_cross_kernel(int dtype_a, const void* A, long lda, long na, long strideA,
+                     const double* B, long ldb, long nb, long strideB, int d, const double* hyp,
+                     double* out, long ldo, long strideO, long rows_pad, long cols_pad,
+                     int mode, int batch, void* stream);
+
+/* ---- (2) blocked Cholesky ------------------------------------------------------------------
+ * In-place lower Cholesky of the padded npad x npad matrix; replaces the potrf that gpytorch's
+ * psd_safe_cholesky issues for gpmpc/gp.py:62.  dinv receives the inverses of the npad/128 diagonal
+ * blocks of L (npad * 128 doubles).  *info_dev = first failing pivot (1-based) or 0. */
+int gpk_potrf(double* A, long lda, long npad, double* dinv, int* info_dev, void* stream);
+
+/* ---- (4) triangular inverse and K^-1 --------------------------------------------------------
+ * W = L^-1 (lower) and U = W^T (upper) from the factor and dinv of gpk_potrf; scratch of
+ * gpk_trtri_scratch_elems(npad) doubles.  gpk_kinv forms K^-1 = U U^T (dense, symmetric): replaces
+ * torch.linalg.inv(K) at gpmpc/gp.py:46 and feeds the MLL gradient. */
+long gpk_trtri_scratch_elems(long npad);
+int gpk_trtri(const double* L, long ldl, long npad, const double* dinv, double* W, long ldw,
+              double* U, long ldu, double* tmp, long tmp_elems, void* stream);
+int gpk_kinv(const double* U, long ldu, long npad, double* Kinv, long ldk, void* stream);
+
+/* ---- (3) alpha, y^T K^-1 y, log det K --------------------------------------------------------
+ * alpha = K^-1 y = U (W y); scal[0] = y^T K^-1 y, scal[1] = log det K (from diag L).  Replaces the
+ * solves / inv_quad_logdet inside ExactMarginalLogLikelihood (gpmpc/gp.py:57,62) and the prediction
+ * strategy's mean cache (gpmpc/gpmpc.py:444).  y, t_work, alpha have npad entries (y zero-padded). */
+int gpk_solve_alpha(const double* W, long ldw, const double* U, long ldu, const double* L, long ldl,
+                    long npad, const double* y, double* t_work, double* alpha, double* scal,
+                    void* stream);
+
+/* ---- (5) MLL gradient trace reduction --------------------------------------------------------
+ * With G = alpha alpha^T - K^-1, over rows [r0, r1) and all columns < n:
+ *   out[0] = sum G_aa, out[1] = sum G_ab K_f,ab, out[2+j] = sum G_ab K_f,ab ((x_aj - x_bj)/ell_j)^2.
+ * Replaces loss.backward() at gpmpc/gp.py:63 (closed form instead of autograd).  Row ranges let one
+ * GP's trace be split over GPUs; the (d+2) partials are then all-reduced by the caller. */
+long gpk_grad_trace_work_elems(long n, int d, long r0, long r1);
+int gpk_mll_grad_reduce(const double* X, long ldx, long n, int d, const double* hyp,
+                        const double* Kinv, long ldk, const double* alpha, long r0, long r1,
+                        double* work, long work_elems, double* out, void* stream);
+
+/* ---- (6) fused posterior mean + input-Jacobian ------------------------------------------------
+ * gpk_pack_train builds the resident training pack (scaled points, -1/2|x|^2, sf2*alpha) in the
+ * prediction dtype.  gpk_predict_mean_jac evaluates mean(z) = k(z,X) alpha (gpmpc/gp.py:85) and
+ * jac(z) = d mean / d z (CasADi AD of gpmpc/gp.py:12-14 inside acados, gpmpc/gpmpc.py:189-211) for q
+ * queries; K_ZX is never written.  work may be NULL (then the training set is not split over CTAs). */
+long gpk_pack_train_elems(long n, int d);
+int gpk_pack_train(int dtype, const double* X, long ldx, long n, int d, const double* alpha,
+                   const double* hyp, void* pack, long pack_elems, void* stream);
+long gpk_mean_jac_work_bytes(int dtype, long q, long n, int d, int batch);
+int gpk_predict_mean_jac(int dtype, const void* Z, long ldz, long q, long strideZ, int d,
+                         const double* hyp, const void* pack, long stride_pack, long n,
+                         void* mean, long stride_mean, void* jac, long ldj, long stride_jac,
+                         void* work, long work_bytes, int batch, void* stream);
+
+/* ---- (7) posterior variance ---------------------------------------------------------------------
+ * var_f(z) = sf2 - || W k(X,z) ||^2: the diagonal that gpmpc/gpmpc.py:443-445 keeps of
+ * gp.likelihood(gp(z)).covariance_matrix, without the likelihood noise (the caller adds hyp noise).
+ * The Q x Q covariance is never formed.  Scratch: gpk_predict_var_work_bytes(q_chunk, npad, batch);
+ * queries are processed in chunks that fit the scratch given. */
+long gpk_predict_var_work_bytes(long q_chunk, long npad, int batch);
+int gpk_predict_var(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                    const double* X, long ldx, long n, long strideX, const double* W, long ldw,
+                    long strideW, long npad, void* var, long stride_var, void* work, long work_bytes,
+                    int batch, void* stream);
+int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,
+                     const double* hyp, void* var, long stride_var, int batch, void* stream);
+
+/* ---- building block exposed for tests ---------------------------------------------------------
+ * C = beta C + alpha A B^T on the FP64 DMMA pipe; M, N multiples of 128, K of 16.
+ * a_tri: 0 full, 1 A lower triangular, 2 A upper triangular; c_lower: only tiles on/below the diagonal. */
+int gpk_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C, long ldc,
+                 long M, long N, long K, double alpha, double beta, int a_tri, int c_lower, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPMPC_B200_H */
