@@ -39,6 +39,7 @@ SIGNATURES = {
     "gpk_predict_mean_jac": (_i, [_i, _p, _l, _l, _l, _i, _p, _p, _l, _l, _p, _l, _p, _l, _l, _p, _l, _i, _p]),
     "gpk_predict_var_work_bytes": (_l, [_l, _l, _i]),
     "gpk_predict_var": (_i, [_i, _p, _l, _l, _l, _i, _p, _p, _l, _l, _l, _p, _l, _l, _l, _p, _l, _p, _l, _i, _p]),
+    "gpk_var_colsq": (_i, [_p, _l, _l, _p, _l, _l, _l, _l, _p, _l, _l, _i, _p]),
     "gpk_var_finalize": (_i, [_i, _p, _l, _l, _i, _l, _p, _p, _l, _i, _p]),
     "gpk_dgemm_nt": (_i, [_p, _l, _p, _l, _p, _l, _l, _l, _l, _d, _d, _i, _i, _p]),
 }

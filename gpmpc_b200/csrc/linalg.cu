@@ -396,6 +396,22 @@ extern "C" int gpk_cross_kernel(int dtype_a, const void* A, long lda, long na, l
 extern "C" int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,
                                 const double* hyp, void* var, long stride_var, int batch, void* stream);
 
+// V = W K_ZX^T reduced to per-tile column sums of squares (the dominant kernel of the variance path),
+// exposed on its own so that tests and bench.py can drive / time it in isolation.
+extern "C" int gpk_var_colsq(const double* W, long ldw, long strideW, const double* kzx, long ldk, long strideK,
+                             long npad, long qpad, double* colsq, long ld_colsq, long stride_colsq, int batch,
+                             void* stream) {
+    GPK_ARG(W && kzx && colsq, "null pointer");
+    GPK_ARG(npad % TILE == 0 && qpad % TILE == 0 && ld_colsq >= qpad, "npad / qpad / ld_colsq");
+    GemmParams p = gemm_args(W, ldw, kzx, ldk, nullptr, 0, npad, qpad, npad, 1.0, 0.0, 1, 0);
+    p.strideA = strideW;
+    p.strideB = strideK;
+    p.colsq = colsq;
+    p.ld_colsq = ld_colsq;
+    p.stride_colsq = stride_colsq;
+    return launch_dgemm_nt(p, 1, batch, (cudaStream_t)stream);
+}
+
 extern "C" long gpk_predict_var_work_bytes(long q_chunk, long npad, int batch) {
     const long qc = (q_chunk + TILE - 1) / TILE * TILE;
     return (qc * npad + (npad / TILE) * qc) * 8 * batch;
@@ -426,13 +442,7 @@ extern "C" int gpk_predict_var(int dtype, const void* Z, long ldz, long q, long 
         const void* Zc = (const char*)Z + q0 * ldz * esz;
         GPK_TRY(gpk_cross_kernel(dtype, Zc, ldz, qn, strideZ, X, ldx, n, strideX, d, hyp, kzx, npad, qc * npad, qp,
                                  npad, 0, batch, st));
-        GemmParams p = gemm_args(W, ldw, kzx, npad, nullptr, 0, npad, qp, npad, 1.0, 0.0, 1, 0);
-        p.strideA = strideW;
-        p.strideB = qc * npad;
-        p.colsq = colsq;
-        p.ld_colsq = qc;
-        p.stride_colsq = (long)tiles_m * qc;
-        GPK_TRY(launch_dgemm_nt(p, 1, batch, st));
+        GPK_TRY(gpk_var_colsq(W, ldw, strideW, kzx, npad, qc * npad, npad, qp, colsq, qc, (long)tiles_m * qc, batch, st));
         void* vout = (char*)var + q0 * esz;
         GPK_TRY(gpk_var_finalize(dtype, colsq, qc, (long)tiles_m * qc, tiles_m, qn, hyp, vout, stride_var, batch, st));
     }

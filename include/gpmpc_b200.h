@@ -106,6 +106,10 @@ int gpk_predict_var(int dtype, const void* Z, long ldz, long q, long strideZ, in
                     const double* X, long ldx, long n, long strideX, const double* W, long ldw,
                     long strideW, long npad, void* var, long stride_var, void* work, long work_bytes,
                     int batch, void* stream);
+/* the dominant kernel of (7) on its own: colsq[tile_m][q] = sum over the 128 rows of tile_m of (W K_ZX^T)[i][q]^2 */
+int gpk_var_colsq(const double* W, long ldw, long strideW, const double* kzx, long ldk, long strideK,
+                  long npad, long qpad, double* colsq, long ld_colsq, long stride_colsq, int batch,
+                  void* stream);
 int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,
                      const double* hyp, void* var, long stride_var, int batch, void* stream);
 
