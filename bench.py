@@ -1,0 +1,365 @@
+"""bench.py -- GP posterior predictions/s (mean + variance + Jacobian) of the gp-mpc GP hot path on B200.
+
+Workload (BASELINE.json configs[1], SURVEY.md 8d "config 2"): P=3 independent exact GPs sharing N=2048
+training points in d=16 (12 states + 4 inputs), Q=8192 horizon queries per step, float64 (the reference's
+arithmetic type: float64 data promotes gpytorch's kernel matrix).  One step = one pass of the hot path
+over one batch: mean, variance and d-vector Jacobian for Q queries of each of the P GPs = P*Q predictions.
+With --gpus N every rank holds the replicated fitted state and its own Q-query shard (weak scaling, no
+data-path collective); value = all ranks' predictions / max-over-ranks device time.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+Prints ONE JSON line (rank 0).  Synthetic data: seed 1337, X~U(-1,1), y=sin(Xw)+0.05eps, ell=0.5 sqrt(d),
+sf2=1, noise=1e-2, Z~U(-1.2,1.2).
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_TRAIN, DIM, N_QUERY, N_GP = 2048, 16, 8192, 3
+METRIC = "gp_posterior_preds_per_s"
+UNIT = "preds/s"
+WORKLOAD = f"config2: P={N_GP} GPs, N={N_TRAIN} train pts, d={DIM}, Q={N_QUERY} queries/step, mean+var+Jacobian"
+DMMA_PEAK_TFLOPS = 37.1   # measured on this pool's B200 by tools/peaks (profiles/peaks_micro_r01.json); nominal 40
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the fp32 / MLL side measurements")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------------------------
+# clocks during the timed region
+# --------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                smax = float(r[1])
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def l2_flusher(device):
+    buf = torch.empty(256 << 20, dtype=torch.uint8, device=device)   # > 126 MB L2
+
+    def flush():
+        buf.fill_(1)
+
+    return flush
+
+
+def make_problem(rank: int):
+    """Synthetic recipe of SURVEY.md 8d (same numbers as oracle.synthetic_problem, restated here so the
+    product arm does not import the oracle)."""
+    import math
+
+    g = torch.Generator().manual_seed(1337)
+    X = torch.rand(N_TRAIN, DIM, generator=g, dtype=torch.float64) * 2.0 - 1.0
+    Wm = torch.randn(DIM, N_GP, generator=g, dtype=torch.float64)
+    eps = torch.randn(N_TRAIN, N_GP, generator=g, dtype=torch.float64)
+    Y = torch.sin(X @ Wm) + 0.05 * eps
+    Z = (torch.rand(N_QUERY, DIM, generator=g, dtype=torch.float64) * 2.0 - 1.0) * 1.2
+    if rank > 0:   # every rank predicts its own shard of the global query batch
+        g2 = torch.Generator().manual_seed(1337 + rank)
+        Z = (torch.rand(N_QUERY, DIM, generator=g2, dtype=torch.float64) * 2.0 - 1.0) * 1.2
+    ell = torch.full((DIM,), 0.5 * math.sqrt(DIM), dtype=torch.float64)
+    return {"X": X, "Y": Y, "Z": Z, "ell": ell, "sf2": 1.0, "noise": 1e-2}
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (torch float64 restatement of the gpytorch math) on the host cores.
+# gpytorch itself is not installable here, so kind = "port".
+# --------------------------------------------------------------------------------------------------
+def cpu_predict_rate(problem, n_queries: int, steps: int = 1, warmup: int = 0):
+    """Times oracle.predict (mean + variance + Jacobian) for the P GPs on `n_queries` of the workload's
+    queries with all host threads.  Fit states (Cholesky, alpha) are prepared outside the timed region,
+    like the GPU arm's resident state.  Returns (preds/s, seconds per step)."""
+    from oracle import gp_oracle as o
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    X, Y, Z = problem["X"], problem["Y"], problem["Z"][:n_queries]
+    states = [o.fit_state(X, Y[:, p], problem["ell"], problem["sf2"], problem["noise"]) for p in range(N_GP)]
+
+    def step():
+        for st in states:
+            o.predict(Z, X, problem["ell"], problem["sf2"], st["L"], st["alpha"])
+
+    for _ in range(warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    dt = (time.perf_counter() - t0) / steps
+    return N_GP * n_queries / dt, dt, cores
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path.  gpytorch 1.12.0 cannot be installed
+    here (no wheel, no network), so this is the oracle port on all host cores; each step is a bounded sample
+    of the workload's queries sized so the whole run stays within a few minutes."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    problem = make_problem(0)
+    # calibrate on 512 queries, then size the per-step sample for ~2.5 s per step
+    rate0, _, cores = cpu_predict_rate(problem, 512, steps=1, warmup=1)
+    total_steps = max(1, args.steps + args.warmup)
+    budget_s = min(2.5, 150.0 / total_steps)
+    sample = int(min(N_QUERY, max(256, rate0 * budget_s / N_GP)))
+    rate, dt, cores = cpu_predict_rate(problem, sample, steps=args.steps, warmup=args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": f"{sample} of {N_QUERY} queries per step x {N_GP} GPs"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{sample} of {N_QUERY} queries x {N_GP} GPs per step, fit state prepared untimed; "
+                                   "gpytorch 1.12.0 not installable, oracle/gp_oracle.py (torch float64) timed instead"},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# B200 arm
+# --------------------------------------------------------------------------------------------------
+def timed_steps(fn, steps, flush, device):
+    """Sum of per-step CUDA-event durations (ms) on the current stream, L2 flushed before every step."""
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for e0, e1 in evs:
+        flush()
+        e0.record()
+        fn()
+        e1.record()
+    torch.cuda.synchronize(device)
+    return sum(e0.elapsed_time(e1) for e0, e1 in evs)
+
+
+def run_b200(args):
+    import torch.distributed as dist
+
+    from gpmpc_b200 import _lib, engine as E
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = _lib.require_cuda(f"cuda:{local_rank}")
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+
+    problem = make_problem(rank)
+    X, Y, Z = problem["X"].to(dev), problem["Y"].to(dev), problem["Z"].to(dev)
+    t0 = time.perf_counter()
+    gb = E.fit_batch(X, Y, problem["ell"], problem["sf2"], problem["noise"])   # replicated fitted state
+    torch.cuda.synchronize(dev)
+    fit_s = time.perf_counter() - t0
+    flush = l2_flusher(dev)
+    preds_per_step = N_GP * N_QUERY
+
+    def step():
+        return E.predict(gb, Z)
+
+    # ---- value: inputs resident in HBM ----------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(dev.index)
+    sampler.start()
+    lib.gpk_reset_launch_count()
+    total_ms = timed_steps(step, args.steps, flush, dev)
+    launches = lib.gpk_launch_count()
+    barrier()
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    value = world * preds_per_step * args.steps / (total_ms * 1e-3)
+
+    # ---- e2e: host buffers through the public API, H2D + D2H inside the timed region ------------------
+    from gpmpc_b200.gp import predict_host
+
+    Zh = problem["Z"].pin_memory()
+    out_h = None
+    for _ in range(3):
+        out_h = predict_host(gb, Zh, out_h)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out_h = predict_host(gb, Zh, out_h)      # returns after the results are on the host
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * preds_per_step * args.steps / float(t.item())
+    clocks = sampler.stop()
+    h2d = Zh.numel() * 8
+    d2h = sum(o_.numel() * o_.element_size() for o_ in out_h)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "per_gpu_queries": N_QUERY, "parallelism": f"query-sharded x{world}, state replicated",
+                   "l2": "flushed (256 MB write) before every timed step"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches, "clocks": clocks, "fit_state_s": fit_s,
+    }
+    if rank == 0:
+        line["roofline"] = measure_roofline(gb, Z, flush, dev, args.steps)
+        if not args.no_extras:
+            line["extras"] = measure_extras(gb, problem, Z, flush, dev)
+        if world == 1 and not args.no_cpu_baseline:
+            rate0, _, cores = cpu_predict_rate(problem, 512, steps=1, warmup=1)
+            sample = int(min(N_QUERY, max(512, rate0 * 12.0 / N_GP)))   # ~12 s of CPU work
+            rate, dt, cores = cpu_predict_rate(problem, sample, steps=1, warmup=0)
+            line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": f"{sample} of {N_QUERY} queries x {N_GP} GPs, one pass, fit state prepared "
+                                              "untimed; oracle/gp_oracle.py (torch float64, all host threads)"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def measure_roofline(gb, Z, flush, dev, steps):
+    """Dominant kernel = dgemm_nt_kernel<1> (V = W K_ZX^T with the column-norm epilogue, FP64 DMMA pipe).
+    Algorithmic work per launch: N^2 flops per prediction (triangular contraction) x P*Q
+    predictions.  Timed alone with CUDA events on its launch stream, K_ZX prepared beforehand, L2 flushed."""
+    from gpmpc_b200 import _lib, engine as E
+    from gpmpc_b200._lib import call, ptr
+
+    B, n, d, npad = len(gb.fits), gb.n, gb.d, gb.npad
+    q = Z.shape[0]
+    qp = E.round_up(q, 128)
+    tiles_m = npad // 128
+    st = _lib.stream_ptr(dev)
+    kzx = torch.empty(B, qp, npad, dtype=torch.float64, device=dev)
+    colsq = torch.empty(B, tiles_m, qp, dtype=torch.float64, device=dev)
+    call("gpk_cross_kernel", 1, ptr(Z), Z.stride(0), q, 0, ptr(gb.X), gb.X.stride(1), n, gb.X.stride(0), d, ptr(gb.hyp),
+         ptr(kzx), npad, qp * npad, qp, npad, 0, B, st)
+
+    def gemm():
+        call("gpk_var_colsq", ptr(gb.W), npad, gb.W.stride(0), ptr(kzx), npad, qp * npad, npad, qp, ptr(colsq), qp,
+             tiles_m * qp, B, st)
+
+    for _ in range(3):
+        gemm()
+    ms = timed_steps(gemm, steps, flush, dev) / steps
+    flops = float(n) * n * B * q
+    achieved = flops / (ms * 1e-3) / 1e12
+    return {"kernel": "dgemm_nt_kernel<1> (variance contraction, fp64 DMMA)", "bound": "tensor", "achieved": achieved,
+            "peak": DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": achieved / DMMA_PEAK_TFLOPS, "traffic": None,
+            "ms_per_launch": ms, "algorithmic_flops_per_launch": flops,
+            "peak_source": "fp64 DMMA m8n8k4 microbenchmark on this pool's B200 (profiles/peaks_micro_r01.json); "
+                           "MEASURED_PEAKS.json holds only bf16/HBM peaks, tcgen05 has no f64 kind"}
+
+
+def measure_extras(gb, problem, Z, flush, dev):
+    """Side measurements (not the headline): float32 prediction path, mean+Jacobian kernel alone, MLL+grad."""
+    from gpmpc_b200 import engine as E
+
+    out = {}
+    Z32 = Z.float()
+    for _ in range(3):
+        E.predict(gb, Z32)
+    ms = timed_steps(lambda: E.predict(gb, Z32), 10, flush, dev) / 10
+    out["f32_path_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
+    for name, zz in (("f64", Z), ("f32", Z32)):
+        for _ in range(3):
+            E.predict(gb, zz, want_var=False)
+        ms = timed_steps(lambda: E.predict(gb, zz, want_var=False), 10, flush, dev) / 10
+        out[f"mean_jac_only_{name}_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
+        out[f"mean_jac_only_{name}_pairs_per_s"] = N_GP * N_QUERY * N_TRAIN / (ms * 1e-3)
+    # MLL value + full gradient for one GP (fit_gp's inner iteration), N = 2048
+    X, y = problem["X"].to(dev), problem["Y"][:, 0].to(dev)
+
+    def mll_iter():
+        fit, ws = E.factorize(X, y, problem["ell"], problem["sf2"], problem["noise"], want_kinv=True)
+        E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
+
+    for _ in range(2):
+        mll_iter()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for _ in range(5):
+        mll_iter()
+    torch.cuda.synchronize(dev)
+    out["mll_grad_iters_per_s_n2048"] = 5 / (time.perf_counter() - t0)
+    return out
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -426,3 +426,21 @@ def predict_callable(gp: GaussianProcess):
         return {"mean": mean[0] if single else mean, "jac": jac[0] if single else jac}
 
     return pred
+
+
+@torch.no_grad()
+def predict_host(batch, Z_host: torch.Tensor, out: tuple | None = None):
+    """End-to-end prediction from HOST buffers: copies the (pinned) queries to the GPU, runs the batched
+    mean + variance + Jacobian path and returns (mean, var, jac) in pinned host memory; blocks until the
+    results are on the host.  `batch` is an engine.GPBatch / GPFit or a list of fitted GaussianProcess."""
+    if isinstance(batch, (list, tuple)):
+        batch = E.GPBatch.from_fits([gp._prediction_fit() for gp in batch])
+    dev = batch.device
+    Zd = Z_host.to(dev, non_blocking=True)
+    res = E.predict(batch, Zd)
+    if out is None:
+        out = tuple(torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in res)
+    for o_, r in zip(out, res):
+        o_.copy_(r, non_blocking=True)
+    torch.cuda.current_stream(dev).synchronize()
+    return out
