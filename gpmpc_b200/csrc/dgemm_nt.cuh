@@ -62,7 +62,7 @@ __device__ __forceinline__ void tile_coords(const GemmParams& p, int id, int& tm
 }
 
 template <int EPI>
-__global__ void __launch_bounds__(G_THREADS, 1) dgemm_nt_kernel(const GemmParams p) {
+__device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
     extern __shared__ __align__(16) double smem[];
 
     int tm, tn;
@@ -191,6 +191,11 @@ __global__ void __launch_bounds__(G_THREADS, 1) dgemm_nt_kernel(const GemmParams
         }
     }
 }
+
+// EPI 0: C = beta C + alpha A B^T (potrf / trtri / K^-1 building block)
+__global__ void __launch_bounds__(G_THREADS, 1) dgemm_nt_kernel(const GemmParams p) { dgemm_nt_body<0>(p); }
+// EPI 1: posterior-variance contraction, column sums of squares of W K_ZX^T (the dominant predict kernel)
+__global__ void __launch_bounds__(G_THREADS, 1) var_colsq_kernel(const GemmParams p) { dgemm_nt_body<1>(p); }
 
 // host-side launcher (defined in linalg.cu)
 int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st);

@@ -41,16 +41,16 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
     static bool attr_done[2] = {false, false};
     if (!attr_done[epilogue]) {
         if (epilogue == 0)
-            GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+            GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
         else
-            GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+            GPK_CUDA(cudaFuncSetAttribute(var_colsq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
         attr_done[epilogue] = true;
     }
     dim3 grid((unsigned)(p.tiles_m * p.tiles_n), 1, (unsigned)batch);
     if (epilogue == 0)
-        dgemm_nt_kernel<0><<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
+        dgemm_nt_kernel<<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
     else
-        dgemm_nt_kernel<1><<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
+        var_colsq_kernel<<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
     GPK_LAUNCHED();
     return 0;
 }

@@ -71,6 +71,31 @@ __global__ void __launch_bounds__(256) k_dmma(double* out, int iters, double s) 
     if (r == 12345.678) out[0] = r;
 }
 
+// DMMA and DFMA issued from the same warps: do the two FP64 paths overlap?
+template<int NM, int NF>
+__global__ void __launch_bounds__(256) k_mix(double* out, int iters, double s) {
+    double c[NM][2], f[NF];
+#pragma unroll
+    for (int i = 0; i < NM; i++) { c[i][0] = 0; c[i][1] = 0; }
+#pragma unroll
+    for (int i = 0; i < NF; i++) f[i] = threadIdx.x * 1e-9 + i;
+    double a = s + threadIdx.x * 1e-9, b = s * 0.5, m = 1.0 + s;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < NM; i++)
+            asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1},{%2},{%3},{%0,%1};\n"
+                         : "+d"(c[i][0]), "+d"(c[i][1]) : "d"(a), "d"(b));
+#pragma unroll
+        for (int i = 0; i < NF; i++) f[i] = fma(f[i], m, s);
+    }
+    double r = 0;
+#pragma unroll
+    for (int i = 0; i < NM; i++) r += c[i][0] + c[i][1];
+#pragma unroll
+    for (int i = 0; i < NF; i++) r += f[i];
+    if (r == 12345.678) out[0] = r;
+}
+
 // numerical check of the m8n8k4 fragment layout: C(8x8) = A(8x4) * B(4x8)
 __global__ void k_dmma_check(const double* A, const double* B, double* C) {
     int lane = threadIdx.x, g = lane >> 2, t = lane & 3;
@@ -138,6 +163,16 @@ int main() {
         float ms = timeit([&] { k_ex2<8><<<grid, 256>>>(fout, iters, -0.5f); }, 5);
         double g = 8.0 * iters * 256.0 * grid / (ms * 1e-3) / 1e12;
         printf(", \"ex2_tera_per_s\": %.3f", g);
+    }
+    {   // mixed DMMA + DFMA: NM DMMA (512 flop/lane-group... 2*256 per warp) and NF DFMA (2*32 per warp) per iteration
+        int grid = sms * 4;
+        float ms = timeit([&] { k_mix<8, 8><<<grid, 256>>>(dout, iters / 4, 1e-12); }, 5);
+        double n = (double)(iters / 4) * 8.0 * grid;   // warp-iterations
+        printf(", \"mix8_8_dmma_tflops\": %.2f, \"mix8_8_dfma_tflops\": %.2f", 2.0 * 256 * 8 * n / (ms * 1e-3) / 1e12, 2.0 * 32 * 8 * n / (ms * 1e-3) / 1e12);
+        ms = timeit([&] { k_mix<8, 32><<<grid, 256>>>(dout, iters / 4, 1e-12); }, 5);
+        printf(", \"mix8_32_dmma_tflops\": %.2f, \"mix8_32_dfma_tflops\": %.2f", 2.0 * 256 * 8 * n / (ms * 1e-3) / 1e12, 2.0 * 32 * 32 * n / (ms * 1e-3) / 1e12);
+        ms = timeit([&] { k_mix<4, 32><<<grid, 256>>>(dout, iters / 4, 1e-12); }, 5);
+        printf(", \"mix4_32_dmma_tflops\": %.2f, \"mix4_32_dfma_tflops\": %.2f", 2.0 * 256 * 4 * n / (ms * 1e-3) / 1e12, 2.0 * 32 * 32 * n / (ms * 1e-3) / 1e12);
     }
     {   // layout check
         double hA[32], hB[32], hC[64], ref[64];
