@@ -37,6 +37,7 @@ struct GemmParams {
     int c_lower;     // 1: skip tiles with tile_m < tile_n
     int tiles_m, tiles_n;
     int group_m, group_n;   // super-tile for L2 reuse across the ~148 concurrently resident CTAs
+    int order, nbatch;      // tile enumeration (see tile_coords)
     double* colsq;          // epilogue 1 output: [tiles_m][ld_colsq]
     long ld_colsq, stride_colsq;
 };
@@ -47,8 +48,27 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
                  : "d"(a), "d"(b));
 }
 
-// linear CTA id -> (tile_m, tile_n), super-tiles of group_m x group_n tiles enumerated row-major
-__device__ __forceinline__ void tile_coords(const GemmParams& p, int id, int& tm, int& tn) {
+// linear CTA id -> (tile_m, tile_n, batch).
+// order 0: super-tiles of group_m x group_n tiles enumerated row-major (L2 reuse of both operand panels);
+//          the batch index comes from blockIdx.z.
+// order 1 (lower-triangular A, work per tile grows with tile_m): the batch is flattened into the columns,
+//          columns are cut into chunks of group_n tiles whose B panels stay L2-resident, and inside a
+//          chunk the heaviest tile rows go first (longest-processing-time order, so the grid ends on the
+//          cheapest tiles and the tail is short).
+__device__ __forceinline__ void tile_coords(const GemmParams& p, int id, int& tm, int& tn, int& batch) {
+    if (p.order == 1) {
+        const int cols = p.tiles_n * p.nbatch;
+        const int per_chunk = p.tiles_m * p.group_n;
+        const int chunk = id / per_chunk;
+        const int rem = id - chunk * per_chunk;
+        const int gn = min(p.group_n, cols - chunk * p.group_n);
+        tm = p.tiles_m - 1 - rem / gn;
+        const int col = chunk * p.group_n + rem % gn;
+        batch = col / p.tiles_n;
+        tn = col - batch * p.tiles_n;
+        return;
+    }
+    batch = blockIdx.z;
     const int per_srow = p.group_m * p.tiles_n;
     const int sr = id / per_srow;
     const int rem = id - sr * per_srow;
@@ -58,15 +78,14 @@ __device__ __forceinline__ void tile_coords(const GemmParams& p, int id, int& tm
     const int rem2 = rem - sc * per_st;
     tm = sr * p.group_m + rem2 % gm;
     tn = sc * p.group_n + rem2 / gm;
-    if (p.a_tri == 1) tm = p.tiles_m - 1 - tm;   // heaviest rows first for a lower-triangular A
 }
 
 template <int EPI>
 __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
     extern __shared__ __align__(16) double smem[];
 
-    int tm, tn;
-    tile_coords(p, blockIdx.x, tm, tn);
+    int tm, tn, batch_i;
+    tile_coords(p, blockIdx.x, tm, tn, batch_i);
     if (p.c_lower && tm < tn) return;
 
     const int tid = threadIdx.x;
@@ -74,7 +93,7 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
     const int g = lane >> 2, t = lane & 3;
     const int wm = warp >> 2, wn = warp & 3;     // 2 x 4 warps
 
-    const long batch = blockIdx.z;
+    const long batch = batch_i;
     const double* __restrict__ A = p.A + batch * p.strideA + (long)tm * G_BM * p.lda;
     const double* __restrict__ B = p.B + batch * p.strideB + (long)tn * G_BN * p.ldb;
 
@@ -83,23 +102,21 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
     if (p.a_tri == 2) kbeg = min(p.K, tm * G_BM);
     const int nk = (kend - kbeg) / G_BK;
 
-    // each thread copies 4 + 4 16-byte chunks per k-block: chunk c -> row c/8, k-chunk c%8
-    auto load_stage = [&](int stage, int kb) {
+    // each thread copies 4 + 4 16-byte chunks per k-block: chunk c -> row c/8, k-chunk c%8.  The copies of
+    // one k-block are issued in 4 parts, one per k-step, so the LDGSTS never queue up in front of the
+    // fragment LDS of the compute loop (MIO is in-order).
+    auto load_part = [&](int stage, int kb, int part) {
         double* As = smem + stage * G_STAGE_ELEMS;
         double* Bs = As + G_BM * G_ROW;
         const long k0 = kbeg + (long)kb * G_BK;
+        const int c = tid + part * G_THREADS;
+        const int row = c >> 3, kc = (c & 7) * 2;
+        cp_async16(As + row * G_ROW + kc, A + (long)row * p.lda + k0 + kc);
+        cp_async16(Bs + row * G_ROW + kc, B + (long)row * p.ldb + k0 + kc);
+    };
+    auto load_stage = [&](int stage, int kb) {
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int c = tid + i * G_THREADS;
-            const int row = c >> 3, kc = (c & 7) * 2;
-            cp_async16(As + row * G_ROW + kc, A + (long)row * p.lda + k0 + kc);
-        }
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int c = tid + i * G_THREADS;
-            const int row = c >> 3, kc = (c & 7) * 2;
-            cp_async16(Bs + row * G_ROW + kc, B + (long)row * p.ldb + k0 + kc);
-        }
+        for (int i = 0; i < 4; i++) load_part(stage, kb, i);
     };
 
     double acc[8][4][2];
@@ -120,11 +137,10 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
     for (int kb = 0; kb < nk; kb++) {
         cp_async_wait<G_STAGES - 2>();
         __syncthreads();
-        {   // refill the stage consumed in the previous iteration
-            const int nxt = kb + G_STAGES - 1;
-            if (nxt < nk) load_stage(nxt % G_STAGES, nxt);
-            cp_async_commit();
-        }
+        // the stage consumed in the previous iteration is refilled piecewise inside the k-step loop
+        const int nxt = kb + G_STAGES - 1;
+        const bool refill = nxt < nk;
+        const int nstage = nxt % G_STAGES;
         const double* st = smem + (kb % G_STAGES) * G_STAGE_ELEMS;
 #pragma unroll
         for (int ks = 0; ks < G_BK / 4; ks++) {
@@ -133,11 +149,13 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
             for (int f = 0; f < 8; f++) a[f] = st[a_off + f * 8 * G_ROW + ks * 4];
 #pragma unroll
             for (int f = 0; f < 4; f++) b[f] = st[b_off + f * 8 * G_ROW + ks * 4];
+            if (refill) load_part(nstage, nxt, ks);
 #pragma unroll
             for (int i = 0; i < 8; i++)
 #pragma unroll
                 for (int j = 0; j < 4; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
         }
+        cp_async_commit();
     }
     cp_async_wait<0>();
 

@@ -36,8 +36,23 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
     if (epilogue == 1) GPK_ARG(p.colsq != nullptr, "colsq output missing");
     p.tiles_m = p.M / G_BM;
     p.tiles_n = p.N / G_BN;
-    p.group_m = p.tiles_m <= 18 ? p.tiles_m : 12;
-    p.group_n = 148 / p.group_m > 0 ? 148 / p.group_m : 1;
+    p.nbatch = batch;
+    dim3 grid((unsigned)(p.tiles_m * p.tiles_n), 1, (unsigned)batch);
+    if (p.a_tri == 1 && !p.c_lower) {
+        // LPT order inside L2-sized column chunks (B panel of one column tile = 128 x K doubles)
+        p.order = 1;
+        const long panel = (long)G_BN * p.K * 8;
+        long gn = (48L << 20) / panel;
+        const long min_gn = (2 * 148 + p.tiles_m - 1) / p.tiles_m;
+        if (gn < min_gn) gn = min_gn;
+        p.group_n = (int)gn;
+        p.group_m = p.tiles_m;
+        grid = dim3((unsigned)(p.tiles_m * p.tiles_n * batch), 1, 1);
+    } else {
+        p.order = 0;
+        p.group_m = p.tiles_m <= 18 ? p.tiles_m : 12;
+        p.group_n = 148 / p.group_m > 0 ? 148 / p.group_m : 1;
+    }
     static bool attr_done[2] = {false, false};
     if (!attr_done[epilogue]) {
         if (epilogue == 0)
@@ -46,7 +61,6 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
             GPK_CUDA(cudaFuncSetAttribute(var_colsq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
         attr_done[epilogue] = true;
     }
-    dim3 grid((unsigned)(p.tiles_m * p.tiles_n), 1, (unsigned)batch);
     if (epilogue == 0)
         dgemm_nt_kernel<<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
     else
