@@ -1,0 +1,202 @@
+"""GPU parity tests of the reference-facing Python surface (GaussianProcess / fit_gp / eval-mode
+prediction) against the CPU oracle and the committed golden fixtures.  Run with -m gpu."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gp_oracle as o
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+TOL64, TOL32 = 1e-6, 1e-4
+
+
+def _gp_at(X, y, ell, sf2, noise, ard=True):
+    from gpmpc_b200.gp import GaussianProcess
+
+    gp = GaussianProcess(X, y, ard=ard)
+    gp.set_hyperparameters(ell, sf2, noise)
+    # compare at the float32-rounded values the GP actually holds (parameters are float32)
+    return gp, gp.hyperparameters()
+
+
+@pytest.mark.parametrize("name", sorted(f[:-4] for f in os.listdir(GOLD) if f.endswith(".npz")))
+def test_golden_fixtures(name):
+    from gpmpc_b200 import engine as E
+
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    X, y, Z = (torch.from_numpy(g[k]) for k in ("X", "y", "Z"))
+    ell, sf2, noise = torch.from_numpy(g["ell"]), float(g["sf2"]), float(g["noise"])
+    dev = torch.device("cuda", 0)
+    fit, ws = E.factorize(X.to(dev), y.to(dev), ell, sf2, noise, want_kinv=True)
+    assert o.rel_err(fit.alpha[: fit.n].cpu(), g["alpha"]) < TOL64
+    assert abs(fit.mll_per_n() - float(g["mll_per_n"])) < TOL64 * abs(float(g["mll_per_n"]))
+    for dtype, tol in ((torch.float64, TOL64), (torch.float32, TOL32)):
+        mean, var, jac = E.predict(fit, Z.to(dev).to(dtype))
+        assert o.rel_err(mean[0].cpu(), g["mean"]) < tol, (name, dtype)
+        assert o.rel_err(var[0].cpu(), g["var"]) < tol, (name, dtype)
+        assert o.rel_err(jac[0].cpu(), g["jac"]) < tol, (name, dtype)
+    loss, g_noise, g_sf2, g_ell = E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
+    assert abs(loss - float(g["loss_raw"])) < TOL64 * abs(float(g["loss_raw"]))
+    rl = torch.from_numpy(g["raw_ell"])
+    gl = torch.tensor(g_ell, dtype=torch.float64)
+    gl = (gl.reshape(1, -1) if rl.shape[1] > 1 else gl.sum().reshape(1, 1)) * torch.sigmoid(rl)
+    assert o.rel_err(gl, g["g_raw_ell"]) < TOL64
+    gn = g_noise * float(torch.sigmoid(torch.from_numpy(g["raw_noise"])))
+    assert abs(gn - float(g["g_raw_noise"].reshape(-1)[0])) < TOL64 * max(abs(float(g["g_raw_noise"].reshape(-1)[0])), 1e-3)
+
+
+@pytest.mark.parametrize("n,d", [(15, 1), (30, 3), (45, 3)])
+def test_fit_gp_follows_reference_adam_loop(n, d):
+    """fit_gp (gpmpc/gp.py:49-69): same losses and final raw parameters as the oracle's restatement of the
+    loop; then gp.K / gp.K_inv as compute_covariances (gp.py:43-46)."""
+    from gpmpc_b200.gp import GaussianProcess, fit_gp
+
+    p = o.synthetic_problem(n, d, 1, seed=50 + n)
+    X, y = p["X"], p["Y"][:, 0]
+    gp = GaussianProcess(X, y)
+    fit_gp(gp, n_train=60, lr=0.05, device="cpu")
+    ref = o.fit_hyperparameters(X, y, n_train=60, lr=0.05)
+    assert len(gp.fit_losses) == len(ref["losses"])
+    assert o.rel_err(torch.tensor(gp.fit_losses), torch.tensor(ref["losses"])) < 1e-5
+    assert torch.allclose(gp.likelihood.noise_covar.raw_noise.detach().cpu(), ref["raw_noise"], atol=2e-4)
+    assert torch.allclose(gp.covar_module.raw_outputscale.detach().cpu(), ref["raw_sf2"], atol=2e-4)
+    assert torch.allclose(gp.covar_module.base_kernel.raw_lengthscale.detach().cpu(), ref["raw_ell"], atol=2e-4)
+    ell, sf2, noise = gp.hyperparameters()
+    K_ref = o.assemble_K(X, ell, sf2, noise)
+    assert gp.K.shape == (n, n) and gp.K.device.type == "cpu" and gp.K.dtype == torch.float64
+    assert o.rel_err(gp.K, K_ref) < 1e-12
+    assert o.rel_err(gp.K_inv, torch.linalg.inv(K_ref)) < TOL64
+    assert len(gp.fit_losses) < 60 or gp.fit_losses[-1] < gp.fit_losses[0]
+
+
+def test_fit_gp_early_stop_and_ard():
+    from gpmpc_b200.gp import GaussianProcess, fit_gp
+
+    p = o.synthetic_problem(40, 3, 1, seed=77)
+    X, y = p["X"], p["Y"][:, 0]
+    gp = GaussianProcess(X, y, ard=True)
+    fit_gp(gp, n_train=400, lr=0.05, device="cuda")
+    ref = o.fit_hyperparameters(X, y, n_train=400, lr=0.05, ard=True)
+    assert len(gp.fit_losses) == len(ref["losses"]) < 400       # |delta loss| < 1e-3 stops both at the same step
+    assert gp.K.is_cuda and next(gp.parameters()).is_cuda
+
+
+@pytest.mark.parametrize("n,d,q", [(15, 1, 25), (45, 3, 25), (300, 16, 25)])
+def test_eval_mode_distribution_like_gpmpc_call_site(n, d, q):
+    """gp.eval(); cov = gp.likelihood(gp(z)).covariance_matrix; diag(cov)   (gpmpc/gpmpc.py:441-445)."""
+    p = o.synthetic_problem(n, d, q, seed=9 + n)
+    X, y, Z = p["X"], p["Y"][:, 0], p["Z"]
+    gp, (ell, sf2, noise) = _gp_at(X, y, p["ell"] * 0.9, 1.4, 0.03)
+    gp.eval()
+    dist = gp(Z)
+    cov = gp.likelihood(dist).covariance_matrix
+    st = o.fit_state(X, y, ell, sf2, noise)
+    m_ref, v_ref, j_ref = o.predict(Z, X, ell, sf2, st["L"], st["alpha"])
+    kzx = o.se_kernel(Z, X, ell, sf2)
+    v = torch.linalg.solve_triangular(st["L"], kzx.T, upper=False)
+    cov_ref = o.se_kernel(Z, Z, ell, sf2) - v.T @ v + noise * torch.eye(q, dtype=torch.float64)
+    assert cov.shape == (q, q) and cov.device.type == "cpu"
+    assert o.rel_err(cov, cov_ref) < TOL64
+    assert o.rel_err(torch.diag(cov), v_ref + noise) < TOL64
+    assert o.rel_err(dist.mean, m_ref) < TOL64
+    assert o.rel_err(gp.likelihood(dist).variance, v_ref + noise) < TOL64
+    assert o.rel_err(dist.jacobian, j_ref) < TOL64
+    mean, var, jac = gp.predict(Z, include_noise=True)
+    assert o.rel_err(var, v_ref + noise) < TOL64 and o.rel_err(jac, j_ref) < TOL64
+    # train() drops the cached prediction state, like gpytorch
+    gp.train()
+    assert gp._pred_fit is None
+    prior = gp(Z)
+    assert float(prior.mean.abs().max()) == 0.0
+    assert o.rel_err(prior.covariance_matrix, o.se_kernel(Z, Z, ell, sf2)) < 1e-12
+
+
+def test_kernel_evaluator_and_fitc_flow():
+    """gp.covar_module(a[,b]).to_dense(), .add_diag(noise) and the FITC weights of gpmpc/gpmpc.py:391-398."""
+    p = o.synthetic_problem(45, 3, 1, seed=3)
+    X, y = p["X"], p["Y"][:, 0]
+    gp, (ell, sf2, noise) = _gp_at(X, y, torch.full((3,), 0.8), 1.1, 0.02, ard=False)
+    gp.K, gp.K_inv = gp.compute_covariances()
+    S = X[torch.randperm(45, generator=torch.Generator().manual_seed(0))[:40]]
+    K_ss = gp.covar_module(S).to_dense()
+    K_xs = gp.covar_module(X, S).to_dense()
+    assert o.rel_err(K_ss, o.se_kernel(S, S, ell, sf2)) < 1e-12 and o.rel_err(K_xs, o.se_kernel(X, S, ell, sf2)) < 1e-12
+    Kn = gp.covar_module(X).add_diag(gp.likelihood.noise).to_dense()
+    assert o.rel_err(Kn, gp.K) < 1e-13
+    Gamma = torch.diagonal(gp.K - K_xs @ torch.linalg.solve(K_ss, K_xs.T))
+    Gamma_inv = torch.diag_embed(1 / Gamma)
+    Sigma_inv = K_ss + K_xs.T @ Gamma_inv @ K_xs
+    w = torch.linalg.solve(Sigma_inv, K_xs.T) @ Gamma_inv @ y
+    assert o.rel_err(w, o.fitc_posterior_mean(X, y, S, ell, sf2, noise)) < 1e-6
+
+
+def test_known_answer_cases():
+    from gpmpc_b200 import engine as E
+
+    dev = torch.device("cuda", 0)
+    sf2, noise, ell = 1.7, 0.3, torch.tensor([0.8, 1.1], dtype=torch.float64)
+    X = torch.tensor([[0.2, -0.4]], dtype=torch.float64)
+    y = torch.tensor([1.3], dtype=torch.float64)
+    Z = torch.tensor([[0.5, 0.1], [0.2, -0.4], [60.0, -70.0]], dtype=torch.float64)
+    fit, _ = E.factorize(X.to(dev), y.to(dev), ell, sf2, noise)
+    mean, var, jac = (t[0].cpu() for t in E.predict(fit, Z.to(dev)))
+    k = o.se_kernel(Z, X, ell, sf2)[:, 0]
+    assert torch.allclose(mean, k / (sf2 + noise) * 1.3, rtol=1e-12, atol=1e-300)
+    assert torch.allclose(var, sf2 - k * k / (sf2 + noise), rtol=1e-12)
+    assert float(jac[1].abs().max()) < 1e-15                     # at the data point
+    assert float(mean[2]) == 0.0 and float(var[2]) == sf2 and float(jac[2].abs().max()) == 0.0   # far away
+    # query == training point, tiny noise: mean -> y_i, var_f -> ~0; duplicated rows survive
+    p = o.synthetic_problem(20, 3, 1, seed=2)
+    Xd = torch.cat([p["X"], p["X"][:3]])
+    yd = torch.cat([p["Y"][:, 0], p["Y"][:3, 0]])
+    fit, _ = E.factorize(Xd.to(dev), yd.to(dev), p["ell"], 1.0, 1e-6)
+    mean, var, _ = (t[0].cpu() for t in E.predict(fit, Xd[:5].to(dev)))
+    assert o.rel_err(mean, yd[:5]) < 1e-3 and float(var.abs().max()) < 1e-5
+
+
+def test_full_size_properties_config2():
+    """BASELINE config 2 size (P=3, N=2048, d=16, Q=8192): size-independent properties instead of an oracle
+    pass: linearity of the mean/Jacobian in y, 0 <= var_f <= sf2, var independent of y, batched == single."""
+    from gpmpc_b200 import engine as E
+
+    dev = torch.device("cuda", 0)
+    p = o.synthetic_problem(2048, 16, 8192, p=2, seed=1337)
+    X, Y, Z = p["X"].to(dev), p["Y"].to(dev), p["Z"].to(dev)
+    Y3 = torch.stack([Y[:, 0], Y[:, 1], 2.0 * Y[:, 0] - 3.0 * Y[:, 1]], dim=1)
+    gb = E.fit_batch(X, Y3, p["ell"], p["sf2"], p["noise"])
+    mean, var, jac = E.predict(gb, Z)
+    assert o.rel_err(mean[2].cpu(), (2.0 * mean[0] - 3.0 * mean[1]).cpu()) < 1e-9
+    assert o.rel_err(jac[2].cpu(), (2.0 * jac[0] - 3.0 * jac[1]).cpu()) < 1e-9
+    assert torch.equal(var[0], var[1]) and torch.equal(var[0], var[2])
+    assert float(var.min()) > 0.0 and float(var.max()) <= p["sf2"]
+    m1, v1, j1 = E.predict(gb.fits[1], Z)
+    # the training-set split over CTAs depends on the batch size, so the summation order differs
+    assert o.rel_err(m1[0], mean[1]) < 1e-12 and o.rel_err(j1[0], jac[1]) < 1e-12 and torch.equal(v1[0], var[1])
+    # a sample of the queries against the oracle
+    idx = torch.arange(0, 8192, 64)
+    st = o.fit_state(p["X"], p["Y"][:, 0], p["ell"], p["sf2"], p["noise"])
+    m_ref, v_ref, j_ref = o.predict(p["Z"][idx], p["X"], p["ell"], p["sf2"], st["L"], st["alpha"])
+    assert o.rel_err(mean[0][idx].cpu(), m_ref) < TOL64
+    assert o.rel_err(var[0][idx].cpu(), v_ref) < TOL64
+    assert o.rel_err(jac[0][idx].cpu(), j_ref) < TOL64
+    # float32 path, same sample
+    m32, v32, j32 = E.predict(gb, Z.float())
+    assert o.rel_err(m32[0][idx].cpu(), m_ref) < TOL32
+    assert o.rel_err(v32[0][idx].cpu(), v_ref) < TOL32
+    assert o.rel_err(j32[0][idx].cpu(), j_ref) < TOL32
+
+
+def test_predict_host_roundtrip():
+    from gpmpc_b200 import engine as E
+    from gpmpc_b200.gp import predict_host
+
+    dev = torch.device("cuda", 0)
+    p = o.synthetic_problem(256, 4, 300, p=2, seed=8)
+    gb = E.fit_batch(p["X"].to(dev), p["Y"].to(dev), p["ell"], 1.0, 1e-2)
+    out = predict_host(gb, p["Z"].pin_memory())
+    ref = E.predict(gb, p["Z"].to(dev))
+    assert all(not t.is_cuda and t.is_pinned() for t in out)
+    assert all(torch.equal(a, b.cpu()) for a, b in zip(out, ref))
