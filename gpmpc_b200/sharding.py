@@ -1,0 +1,147 @@
+"""Sharding layer (north-star subsystem d): one process per GPU under torch.distributed.
+
+The reference has no counterpart (single process, a Python loop over its three GPs, gpmpc/gpmpc.py:159-162);
+the three axes below are the ones SURVEY.md 8e names:
+
+  queries      embarrassingly parallel given the fitted state: contiguous Q/G blocks per rank, fitted state
+               (X, hyp, W, alpha) replicated once after the fit -> NO collective during prediction;
+               an optional all_gather returns the full result on every rank.
+  output GPs   GP p is owned by rank p mod G; each rank assembles / factorises / fits its own GPs -> no
+               collective for the fit, one all_gather of the (d+2) fitted hyper-parameters afterwards.
+  gradient rows  one GP's MLL-gradient trace G (.) dK/dtheta is split by rows [gN/G, (g+1)N/G) over the ranks;
+               the (d+2) float64 partial sums are all-reduced (NCCL over NVLink; latency-bound, 18 doubles
+               at d=16).  The Cholesky itself stays on one GPU per GP ("replicas only").
+
+Every function takes the compute step as a callable so the same host logic runs over NCCL on GPUs and over
+gloo in the CPU tests (where the callable is a test double; the product callables are in engine.py).
+"""
+
+from __future__ import annotations
+
+from typing import Callable, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def world_info(group=None) -> tuple[int, int]:
+    """(rank, world_size); (0, 1) when torch.distributed is not initialised."""
+    if not (dist.is_available() and dist.is_initialized()):
+        return 0, 1
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def shard_bounds(n: int, world: int, rank: int) -> tuple[int, int]:
+    """Contiguous block [lo, hi) of rank `rank` when n items are split over `world` ranks; the first
+    n % world ranks get one extra item, empty shards are allowed (n < world)."""
+    assert world >= 1 and 0 <= rank < world and n >= 0
+    base, extra = divmod(n, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def gp_owner(p: int, world: int) -> int:
+    """Rank that owns output GP p (round robin)."""
+    return p % world
+
+
+def owned_gps(n_gps: int, world: int, rank: int) -> list[int]:
+    return [p for p in range(n_gps) if gp_owner(p, world) == rank]
+
+
+# --------------------------------------------------------------------------------------------------
+# query sharding
+# --------------------------------------------------------------------------------------------------
+def predict_sharded(predict_fn: Callable, Z: torch.Tensor, *, gather: bool = False, group=None):
+    """Each rank predicts its contiguous block of the global query batch Z (Q,d).
+
+    predict_fn(Z_local) -> tuple of tensors whose query axis is dim 1 for 2-D+ outputs shaped (B,q,...)
+    (what engine.predict returns: mean (B,q), var (B,q), jac (B,q,d)).  Returns (lo, hi, outputs).  With
+    gather=True the outputs are all_gathered along the query axis so that every rank holds all Q results
+    in the original order; otherwise nothing is communicated.
+    """
+    rank, world = world_info(group)
+    lo, hi = shard_bounds(Z.shape[0], world, rank)
+    outs = predict_fn(Z[lo:hi])
+    if not gather or world == 1:
+        return lo, hi, outs
+    gathered = []
+    sizes = [shard_bounds(Z.shape[0], world, r) for r in range(world)]
+    qmax = max(h - l for l, h in sizes)
+    for t in outs:
+        if t is None:
+            gathered.append(None)
+            continue
+        # pad the query axis to the largest shard so that all_gather sees equal shapes
+        pad_shape = list(t.shape)
+        pad_shape[1] = qmax
+        buf = t.new_zeros(pad_shape)
+        buf[:, : t.shape[1]] = t
+        parts = [torch.empty_like(buf) for _ in range(world)]
+        dist.all_gather(parts, buf, group=group)
+        gathered.append(torch.cat([p[:, : h - l] for p, (l, h) in zip(parts, sizes)], dim=1))
+    return 0, Z.shape[0], tuple(gathered)
+
+
+def broadcast_tensors(tensors: Sequence[torch.Tensor], src: int = 0, group=None) -> None:
+    """Replicate fitted state (W, alpha, hyp, X ...) from `src` into the same-shaped buffers of every rank:
+    the one-time state broadcast after a fit (about 1.07 GB per GP at N=16k float32 W)."""
+    _, world = world_info(group)
+    if world == 1:
+        return
+    for t in tensors:
+        dist.broadcast(t, src=src, group=group)
+
+
+# --------------------------------------------------------------------------------------------------
+# output-GP sharding
+# --------------------------------------------------------------------------------------------------
+def fit_gps_sharded(fit_one: Callable[[int], torch.Tensor], n_gps: int, width: int, *, device=None, group=None):
+    """Rank r fits the GPs it owns with fit_one(p) -> 1-D tensor of `width` float64 values (the fitted
+    hyper-parameters noise, sf2, ell_1..d, and anything else the caller wants shared, e.g. the final loss).
+    Returns an (n_gps, width) tensor available on every rank (one all_gather)."""
+    rank, world = world_info(group)
+    mine = owned_gps(n_gps, world, rank)
+    per_rank = (n_gps + world - 1) // world
+    local = torch.zeros(per_rank, width, dtype=torch.float64, device=device)
+    for slot, p in enumerate(mine):
+        v = fit_one(p)
+        local[slot] = v.to(local.device, torch.float64)
+    if world == 1:
+        return local[:n_gps]
+    parts = [torch.empty_like(local) for _ in range(world)]
+    dist.all_gather(parts, local, group=group)
+    out = torch.zeros(n_gps, width, dtype=torch.float64, device=local.device)
+    for r in range(world):
+        for slot, p in enumerate(owned_gps(n_gps, world, r)):
+            out[p] = parts[r][slot]
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# row-split MLL gradient
+# --------------------------------------------------------------------------------------------------
+def allreduce_row_partials(partials_fn: Callable[[int, int], torch.Tensor], n_rows: int, *, group=None) -> torch.Tensor:
+    """partials_fn(r0, r1) -> (d+2,) float64 partial sums of the gradient trace over rows [r0, r1)
+    (engine.grad_partials).  Every rank reduces its row block; one all_reduce(sum) of d+2 doubles makes the
+    full sums available everywhere.  A rank with an empty block contributes zeros."""
+    rank, world = world_info(group)
+    r0, r1 = shard_bounds(n_rows, world, rank)
+    if r1 > r0:
+        part = partials_fn(r0, r1).clone()
+    else:
+        part = torch.zeros_like(partials_fn(0, min(1, n_rows)))
+    if world > 1:
+        dist.all_reduce(part, op=dist.ReduceOp.SUM, group=group)
+    return part
+
+
+def rowsplit_grad_reduce(group=None) -> Callable:
+    """grad_reduce callback for gp.fit_gp(..., grad_reduce=...): every rank factorises the same GP (the
+    Cholesky is not distributed) and the N x N trace pass is split by rows and all-reduced."""
+    from . import engine as E
+
+    def reduce(fit, ws):
+        return allreduce_row_partials(lambda r0, r1: E.grad_partials(fit, ws, r0, r1), fit.n, group=group)
+
+    return reduce

@@ -1,0 +1,111 @@
+"""world_size-2 gloo tests (CPU) of the sharding layer's host logic: partition arithmetic, gather order,
+GP ownership and the row-split gradient all-reduce.  The compute callables are oracle-backed test doubles;
+the product callables (engine.predict / engine.grad_partials) are exercised in test_gpu_multi.py."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from gpmpc_b200 import sharding as S
+from oracle import gp_oracle as o
+
+
+def test_shard_bounds_cover_everything():
+    for n in (0, 1, 5, 8192, 8193, 4194304):
+        for world in (1, 2, 3, 8):
+            blocks = [S.shard_bounds(n, world, r) for r in range(world)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == n
+            assert all(blocks[i][1] == blocks[i + 1][0] for i in range(world - 1))
+            sizes = [h - l for l, h in blocks]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_gp_ownership_round_robin():
+    assert [S.gp_owner(p, 8) for p in range(8)] == list(range(8))
+    assert S.owned_gps(3, 2, 0) == [0, 2] and S.owned_gps(3, 2, 1) == [1]
+    assert S.owned_gps(3, 8, 5) == []
+
+
+def test_single_process_paths_need_no_process_group():
+    Z = torch.arange(12.0).reshape(6, 2)
+    lo, hi, outs = S.predict_sharded(lambda z: (z.sum(1)[None],), Z, gather=True)
+    assert (lo, hi) == (0, 6) and torch.equal(outs[0][0], Z.sum(1))
+    part = S.allreduce_row_partials(lambda a, b: torch.tensor([float(b - a)], dtype=torch.float64), 10)
+    assert float(part) == 10.0
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, q_total):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.set_num_threads(1)
+        p = o.synthetic_problem(60, 3, q_total, p=3, seed=5)
+        X, Y, Z = p["X"], p["Y"], p["Z"]
+        states = [o.fit_state(X, Y[:, i], p["ell"], 1.0, 1e-2) for i in range(3)]
+
+        def predict_fn(z):   # same output convention as engine.predict: (B,q), (B,q), (B,q,d)
+            res = [o.predict(z, X, p["ell"], 1.0, s["L"], s["alpha"]) for s in states]
+            return tuple(torch.stack([r[k] for r in res]) for k in range(3))
+
+        full = predict_fn(Z)
+        # --- query sharding, no gather: my block only
+        lo, hi, outs = S.predict_sharded(predict_fn, Z)
+        assert (lo, hi) == S.shard_bounds(q_total, world, rank)
+        for a, b in zip(outs, full):
+            assert torch.equal(a, b[:, lo:hi])
+        # --- with gather: everything, original order, on every rank (ragged shards when q_total is odd)
+        lo, hi, outs = S.predict_sharded(predict_fn, Z, gather=True)
+        assert (lo, hi) == (0, q_total)
+        for a, b in zip(outs, full):
+            assert torch.equal(a, b)
+        # --- row-split gradient trace: sum of per-rank row blocks == full trace
+        n, d = X.shape
+        rn, rs, rl = torch.tensor([-2.0]), torch.tensor(0.3), torch.full((1, d), 0.5)
+        noise, sf2, ell = o.constrained(rn, rs, rl)
+        st = o.fit_state(X, Y[:, 0], ell.reshape(-1), sf2, noise)
+        Kf = st["K"] - float(noise) * torch.eye(n, dtype=torch.float64)
+        G = torch.outer(st["alpha"], st["alpha"]) - torch.cholesky_inverse(st["L"])
+        Xs = X / ell.reshape(-1)
+
+        def partials(r0, r1):   # same layout as engine.grad_partials: [tr G, sum G K_f, sum G K_f dx_j^2 ...]
+            GK = (G * Kf)[r0:r1]
+            out = [G.diagonal()[r0:r1].sum(), GK.sum()]
+            for j in range(d):
+                df = Xs[r0:r1, j : j + 1] - Xs[:, j : j + 1].T
+                out.append((GK * df * df).sum())
+            return torch.stack(out)
+
+        red = S.allreduce_row_partials(partials, n)
+        assert torch.allclose(red, partials(0, n), rtol=1e-12, atol=1e-12)
+        # --- output-GP sharding: each rank "fits" its own GPs, everybody gets all results
+        calls = []
+
+        def fit_one(pidx):
+            calls.append(pidx)
+            return torch.tensor([pidx, 10.0 * pidx, rank], dtype=torch.float64)
+
+        allp = S.fit_gps_sharded(fit_one, 3, 3)
+        assert calls == S.owned_gps(3, world, rank)
+        assert torch.equal(allp[:, 0], torch.tensor([0.0, 1.0, 2.0], dtype=torch.float64))
+        assert torch.equal(allp[:, 2], torch.tensor([float(S.gp_owner(i, world)) for i in range(3)], dtype=torch.float64))
+        # --- state broadcast
+        t = torch.full((4,), float(rank))
+        S.broadcast_tensors([t], src=1)
+        assert torch.equal(t, torch.ones(4))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("q_total", [64, 37])
+def test_world_size_2_gloo(q_total):
+    mp.spawn(_worker, args=(2, _free_port(), q_total), nprocs=2, join=True)
