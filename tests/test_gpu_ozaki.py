@@ -1,0 +1,134 @@
+"""GPU parity tests of the tcgen05 int8 ("Ozaki") variance path: digit images, the exact int32 tensor-core
+accumulators, and the recombined column sums of squares, each against an independent host computation."""
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+F64 = torch.float64
+
+
+def _decode(img: torch.Tensor, tiles: int, kb_total: int, S: int, rows: int) -> torch.Tensor:
+    """digit image [tile][kb][s][rows x 64 B core-matrix layout] -> int tensor (S, tiles*rows, kb_total*64)."""
+    a = img.cpu().view(torch.int8).reshape(tiles, kb_total, S, rows // 8, 4, 8, 16)   # rg, kchunk, r%8, k%16
+    a = a.permute(2, 0, 3, 5, 1, 4, 6).reshape(S, tiles * rows, kb_total * 64)
+    return a.to(torch.int64)
+
+
+def _digits_ref(x: torch.Tensor, S: int) -> torch.Tensor:
+    """signed base-128 digits (most significant first) of round(x * 2^(6+7(S-1))), |x| <= 1."""
+    I = torch.round(x * float(2 ** (6 + 7 * (S - 1)))).to(torch.int64)
+    out = []
+    for _ in range(S - 1):
+        low = I & 127
+        d = torch.where(low >= 64, low - 128, low)
+        out.append(d)
+        I = (I - d) >> 7
+    out.append(I)
+    return torch.stack(out[::-1])
+
+
+@pytest.fixture(scope="module")
+def env():
+    from gpmpc_b200 import _lib, engine as E
+    from oracle import gp_oracle as o
+
+    dev = _lib.require_cuda()
+    return _lib, E, o, dev
+
+
+@pytest.mark.parametrize("S", [5, 6, 7])
+def test_w_image_digits(env, S):
+    _lib, E, o, dev = env
+    npad = 256
+    g = torch.Generator().manual_seed(3)
+    W = torch.tril(torch.randn(npad, npad, generator=g, dtype=F64) * torch.logspace(-3, 1, npad, dtype=F64)[:, None])
+    Wd = W.to(dev)
+    img = torch.zeros(_lib.load().gpk_oz_w_image_bytes(npad, S), dtype=torch.int8, device=dev)
+    scale = torch.empty(npad, dtype=F64, device=dev)
+    _lib.call("gpk_oz_slice_w", _lib.ptr(Wd), npad, npad, S, _lib.ptr(img), _lib.ptr(scale), _lib.stream_ptr(dev))
+    sc = scale.cpu()
+    m = W.abs().max(dim=1).values
+    assert torch.all(sc > m) and torch.all(sc <= 2 * m), "row scale must be the next power of two above max|row|"
+    assert torch.all(torch.log2(sc) == torch.round(torch.log2(sc)))
+    got = _decode(img, npad // 128, npad // 64, S, 128)
+    ref = _digits_ref(W / sc[:, None], S)
+    # blocks above the diagonal tile are never written / read
+    mask = (torch.arange(npad)[None, :] // 64) < ((torch.arange(npad)[:, None] // 128) + 1) * 2
+    assert torch.equal(got[:, mask], ref[:, mask])
+    assert got.abs().max() <= 64
+
+
+@pytest.mark.parametrize("S,dtype", [(5, F64), (6, F64), (7, F64), (6, torch.float32)])
+def test_e_image_reconstructs_kernel(env, S, dtype):
+    _lib, E, o, dev = env
+    n, d, q = 300, 16, 100
+    p = o.synthetic_problem(n, d, q, p=1, seed=5)
+    X, Z, ell = p["X"], p["Z"].to(dtype), p["ell"]
+    npad, qpad = 384, 128
+    hyp = E.make_hyp(X.mean(0), ell, p["sf2"], p["noise"], d, dev)
+    img = torch.zeros(_lib.load().gpk_oz_e_image_bytes(qpad, npad, S), dtype=torch.int8, device=dev)
+    Xd, Zd = X.to(dev), Z.to(dev)
+    _lib.call("gpk_oz_cross", E.DTYPE_CODE[dtype], _lib.ptr(Zd), d, q, 0, _lib.ptr(Xd), d, n, 0, d, _lib.ptr(hyp),
+              _lib.ptr(img), img.numel(), npad, qpad, S, 1, _lib.stream_ptr(dev))
+    dig = _decode(img, qpad // 64, npad // 64, S, 64).to(F64)
+    rec = sum(dig[s] * 2.0 ** (-6 - 7 * s) for s in range(S))
+    ref = o.se_kernel(Z.to(F64), X, ell, 1.0)
+    assert dig.abs().max() <= 64
+    assert (rec[:q, :n] - ref).abs().max() < 2.0 ** (-6 - 7 * (S - 1)) + 1e-15
+    assert rec[q:, :].abs().max() == 0 and rec[:, n:].abs().max() == 0
+
+
+@pytest.mark.parametrize("S", [5, 6, 7])
+def test_tensor_core_accumulators_exact(env, S):
+    """raw int32 TMEM accumulators D_g = sum_{s+t=g} a_s b_t^T against an int64 host matmul of the decoded digits"""
+    _lib, E, o, dev = env
+    lib = _lib.load()
+    npad, qpad = 384, 128
+    g = torch.Generator().manual_seed(11)
+    W = torch.tril(torch.randn(npad, npad, generator=g, dtype=F64))
+    n, d, q = 380, 3, 120
+    X = torch.rand(n, d, generator=g, dtype=F64)
+    Z = torch.rand(q, d, generator=g, dtype=F64)
+    hyp = E.make_hyp(X.mean(0), torch.full((d,), 0.7, dtype=F64), 1.3, 1e-2, d, dev)
+    wimg = torch.zeros(lib.gpk_oz_w_image_bytes(npad, S), dtype=torch.int8, device=dev)
+    eimg = torch.zeros(lib.gpk_oz_e_image_bytes(qpad, npad, S), dtype=torch.int8, device=dev)
+    scale = torch.empty(npad, dtype=F64, device=dev)
+    st = _lib.stream_ptr(dev)
+    Wd, Xd, Zd = W.to(dev), X.to(dev), Z.to(dev)
+    _lib.call("gpk_oz_slice_w", _lib.ptr(Wd), npad, npad, S, _lib.ptr(wimg), _lib.ptr(scale), st)
+    _lib.call("gpk_oz_cross", 1, _lib.ptr(Zd), d, q, 0, _lib.ptr(Xd), d, n, 0, d, _lib.ptr(hyp), _lib.ptr(eimg),
+              eimg.numel(), npad, qpad, S, 1, st)
+    tiles_m, qtiles = npad // 128, qpad // 64
+    colsq = torch.zeros(tiles_m, qpad, dtype=F64, device=dev)
+    dbg = torch.full((tiles_m * qtiles, S, 128, 64), -7, dtype=torch.int32, device=dev)
+    _lib.call("gpk_oz_var_colsq", _lib.ptr(wimg), 0, _lib.ptr(scale), 0, _lib.ptr(eimg), 0, _lib.ptr(hyp), npad, qpad, S,
+              _lib.ptr(colsq), qpad, 0, 1, _lib.ptr(dbg), st)
+    torch.cuda.synchronize()
+    a = _decode(wimg, tiles_m, npad // 64, S, 128)          # (S, npad, npad)
+    b = _decode(eimg, qtiles, npad // 64, S, 64)            # (S, qpad, npad)
+    a = a * (torch.arange(npad)[None, :] < ((torch.arange(npad)[:, None] // 128) + 1) * 128)   # unread blocks
+    D = torch.zeros(S, npad, qpad, dtype=torch.int64)
+    for s in range(S):
+        for t in range(S - s):
+            D[s + t] += a[s] @ b[t].T
+    # tile id -> (tm, qt): LPT order, one chunk (group_n >= all columns here)
+    got = torch.zeros_like(D)
+    dbg_h = dbg.cpu().to(torch.int64)
+    for tile in range(tiles_m * qtiles):
+        tm = tiles_m - 1 - tile // qtiles
+        qt = tile % qtiles
+        got[:, tm * 128:(tm + 1) * 128, qt * 64:(qt + 1) * 64] = dbg_h[tile]
+    assert torch.equal(got, D)
+    # recombination: V = sf2 * scale_i / 4096 * sum_g 128^-g D_g ; colsq = per-tile column sums of V^2
+    R = sum(D[gi].to(F64) * 128.0 ** (-gi) for gi in range(S))
+    V = 1.3 * scale.cpu()[:, None] / 4096.0 * R
+    ref = (V * V).reshape(tiles_m, 128, qpad).sum(1)
+    assert (colsq.cpu() - ref).abs().max() <= 1e-13 * ref.abs().max()
+    # and against plain fp64:  V = W K_ZX^T
+    Vd = W[:, :n] @ o.se_kernel(Z, X, torch.full((d,), 0.7, dtype=F64), 1.3).T
+    refd = (Vd * Vd).reshape(tiles_m, 128, q).sum(1)
+    tol = {5: 1e-6, 6: 1e-8, 7: 1e-10}[S]
+    assert (colsq.cpu()[:, :q] - refd).abs().max() <= tol * refd.abs().max()
