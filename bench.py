@@ -341,7 +341,7 @@ def measure_extras(gb, problem, Z, flush, dev):
     X, y = problem["X"].to(dev), problem["Y"][:, 0].to(dev)
 
     def mll_iter():
-        fit, ws = E.factorize(X, y, problem["ell"], problem["sf2"], problem["noise"], want_kinv=True)
+        fit, ws = E.factorize(X, y, problem["ell"], problem["sf2"], problem["noise"], want_kinv=True, want_image=False)
         E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
 
     for _ in range(2):

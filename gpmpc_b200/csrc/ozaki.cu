@@ -479,4 +479,49 @@ int gpk_oz_var_colsq(const void* Wimg, long strideW, const double* wscale, long 
     return oz_launch_var<7>(a, st);
 }
 
+
+// ---- (7') posterior variance on the int8 tensor pipe ------------------------------------------------
+// var_f(z) = sf2 - || W k(X,z) ||^2 for q queries of `batch` GPs; queries go through in chunks that fit `work`
+// (digit image of E + per-tile column partials).  Same contract as gpk_predict_var, W given as digit image.
+long gpk_predict_var_i8_work_bytes(long q_chunk, long npad, int S, int batch) {
+    const long qc = (q_chunk + OZ_BN - 1) / OZ_BN * OZ_BN;
+    return ((long)S * qc * npad + (npad / OZ_BM) * qc * 8) * batch;
+}
+
+int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,
+                     const double* hyp, void* var, long stride_var, int batch, void* stream);
+
+int gpk_predict_var_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                       const double* X, long ldx, long n, long strideX, const void* Wimg, long strideW,
+                       const double* wscale, long stride_ws, long npad, int S, void* var, long stride_var,
+                       void* work, long work_bytes, int batch, void* stream) {
+    GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    GPK_ARG(Z && hyp && X && Wimg && wscale && var && work, "null pointer");
+    GPK_ARG(npad % OZ_BM == 0 && npad >= n && n > 0 && batch >= 1, "n / npad / batch");
+    GPK_ARG(S >= 5 && S <= OZ_MAX_S, "digits must be 5, 6 or 7");
+    GPK_ARG(((uintptr_t)work % 16) == 0, "work must be 16-byte aligned");
+    if (q == 0) return 0;
+    const int tiles_m = (int)(npad / OZ_BM);
+    long qc = work_bytes / (((long)S * npad + tiles_m * 8) * batch);
+    qc = qc / OZ_BN * OZ_BN;
+    GPK_ARG(qc >= OZ_BN, "scratch too small (see gpk_predict_var_i8_work_bytes)");
+    const long q_round = (q + OZ_BN - 1) / OZ_BN * OZ_BN;
+    if (qc > q_round) qc = q_round;
+    int8_t* eimg = (int8_t*)work;                                         // [batch][S qc npad]
+    double* colsq = (double*)(eimg + (long)batch * S * qc * npad);        // [batch][tiles_m][qc]
+    const int esz = dtype == 0 ? 4 : 8;
+    for (long q0 = 0; q0 < q; q0 += qc) {
+        const long qn = (q - q0 < qc) ? (q - q0) : qc;
+        const long qp = (qn + OZ_BN - 1) / OZ_BN * OZ_BN;
+        const void* Zc = (const char*)Z + q0 * ldz * esz;
+        GPK_TRY(gpk_oz_cross(dtype, Zc, ldz, qn, strideZ, X, ldx, n, strideX, d, hyp, eimg, (long)S * qc * npad, npad, qp,
+                             S, batch, stream));
+        GPK_TRY(gpk_oz_var_colsq(Wimg, strideW, wscale, stride_ws, eimg, (long)S * qc * npad, hyp, npad, qp, S, colsq, qc,
+                                 (long)tiles_m * qc, batch, nullptr, stream));
+        void* vout = (char*)var + q0 * esz;
+        GPK_TRY(gpk_var_finalize(dtype, colsq, qc, (long)tiles_m * qc, tiles_m, qn, hyp, vout, stride_var, batch, stream));
+    }
+    return 0;
+}
+
 }  // extern "C"

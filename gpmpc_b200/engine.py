@@ -136,6 +136,9 @@ class GPFit:
     hyp: torch.Tensor          # (72,) device
     W: torch.Tensor            # (npad, npad) L^-1
     alpha: torch.Tensor        # (npad,)
+    wimg: torch.Tensor = None  # (digits * npad * npad,) int8 digit image of W for the tcgen05 variance path
+    wscale: torch.Tensor = None  # (npad,) power-of-two row scales of the image
+    digits: int = 0
     quad: float = float("nan")
     logdet: float = float("nan")
     jitter: float = 0.0
@@ -165,8 +168,23 @@ def _as_device_f64(t: torch.Tensor, device) -> torch.Tensor:
     return t.detach().to(device=device, dtype=F64).contiguous()
 
 
+def slice_w(W: torch.Tensor, npad: int, digits: int | None = None, wimg_out=None, wscale_out=None):
+    """int8 digit image + power-of-two row scales of W = L^-1 (operand of the tcgen05 variance contraction)."""
+    lib = _lib.load()
+    digits = lib.gpk_oz_default_digits() if digits is None else digits
+    dev = W.device
+    nbytes = lib.gpk_oz_w_image_bytes(npad, digits)
+    assert nbytes > 0, "digits must be 5, 6 or 7"
+    wimg = wimg_out if wimg_out is not None else torch.empty(nbytes, dtype=torch.int8, device=dev)
+    wscale = wscale_out if wscale_out is not None else torch.empty(npad, dtype=F64, device=dev)
+    call("gpk_oz_slice_w", ptr(W), W.stride(0), npad, digits, ptr(wimg), ptr(wscale), _lib.stream_ptr(dev))
+    return wimg, wscale, digits
+
+
 def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *, center=None,
-              want_kinv: bool = False, W_out: torch.Tensor | None = None, max_tries: int = 3) -> tuple[GPFit, FitScratch]:
+              want_kinv: bool = False, W_out: torch.Tensor | None = None, max_tries: int = 3,
+              digits: int | None = None, wimg_out=None, wscale_out=None,
+              want_image: bool = True) -> tuple[GPFit, FitScratch]:
     """Assemble K, Cholesky, W = L^-1, alpha, y^T K^-1 y and log det K on the GPU (float64).
 
     Replaces the gpytorch work behind gpmpc/gp.py:61-62 (train mode) and the prediction-strategy cache
@@ -209,10 +227,13 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
          ptr(alpha), ptr(ws.scal), st)
     if want_kinv:
         call("gpk_kinv", ptr(ws.U), npad, npad, ptr(ws.need_kinv()), npad, st)
+    wimg = wscale = None
+    if want_image:
+        wimg, wscale, digits = slice_w(W, npad, digits, wimg_out, wscale_out)
     quad, logdet = ws.scal.tolist()
     fit = GPFit(X=X, y=y, n=n, d=d, npad=npad, center=center_h, ell=ell_t, sf2=float(sf2), noise=float(noise),
                 hyp=make_hyp(center_h, ell_t, sf2, noise, d, dev) if jitter else hyp, W=W, alpha=alpha,
-                quad=quad, logdet=logdet, jitter=jitter)
+                quad=quad, logdet=logdet, jitter=jitter, wimg=wimg, wscale=wscale, digits=digits or 0)
     return fit, ws
 
 
@@ -272,14 +293,19 @@ class GPBatch:
     X: torch.Tensor        # (B, N, d)
     W: torch.Tensor        # (B, npad, npad)
     hyp: torch.Tensor      # (B, 72)
+    wimg: torch.Tensor = None     # (B, digits * npad * npad) int8
+    wscale: torch.Tensor = None   # (B, npad)
+    digits: int = 0
     packs: dict = field(default_factory=dict)
 
     @classmethod
     def from_fits(cls, fits: list) -> "GPBatch":
         f0 = fits[0]
         assert all(f.n == f0.n and f.d == f0.d and f.device == f0.device for f in fits), "GPs must share (N, d, device)"
+        has_img = all(f.wimg is not None and f.digits == f0.digits for f in fits)
         if len(fits) == 1:
-            return cls(fits, f0.X[None], f0.W[None], f0.hyp[None])
+            return cls(fits, f0.X[None], f0.W[None], f0.hyp[None], f0.wimg[None] if has_img else None,
+                       f0.wscale[None] if has_img else None, f0.digits if has_img else 0)
         # W tensors allocated by fit_batch are already slices of one (B, npad, npad) buffer
         base = fits[0].W._base if fits[0].W._base is not None else None
         if base is not None and base.dim() == 3 and base.shape[0] == len(fits) and all(
@@ -290,7 +316,17 @@ class GPBatch:
             W = torch.stack([f.W for f in fits])
         X = torch.stack([f.X for f in fits])
         hyp = torch.stack([f.hyp for f in fits])
-        return cls(fits, X, W, hyp)
+        wimg = wscale = None
+        if has_img:
+            ib = fits[0].wimg._base
+            if ib is not None and ib.dim() == 2 and ib.shape[0] == len(fits) and all(
+                f.wimg._base is ib and f.wimg.data_ptr() == ib[i].data_ptr() for i, f in enumerate(fits)
+            ):
+                wimg = ib
+            else:
+                wimg = torch.stack([f.wimg for f in fits])
+            wscale = torch.stack([f.wscale for f in fits])
+        return cls(fits, X, W, hyp, wimg, wscale, f0.digits if has_img else 0)
 
     @property
     def n(self):
@@ -314,7 +350,7 @@ class GPBatch:
         return self.packs[dtype]
 
 
-def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise) -> GPBatch:
+def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise, digits: int | None = None) -> GPBatch:
     """Fit P independent GPs that share the inputs X (N,d) with targets Y (N,P) at fixed hyper-parameters.
     ell: (P,d) or (d,) ; sf2, noise: (P,) or scalars.  The factors are written straight into one stacked buffer."""
     dev = _lib.require_cuda(X.device if X.is_cuda else None)
@@ -324,13 +360,16 @@ def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise) -> GPBatch:
     P = Y.shape[1]
     npad = round_up(n, TILE)
     Wall = torch.empty(P, npad, npad, dtype=F64, device=dev)
+    lib = _lib.load()
+    digits = lib.gpk_oz_default_digits() if digits is None else digits
+    Iall = torch.empty(P, lib.gpk_oz_w_image_bytes(npad, digits), dtype=torch.int8, device=dev)
     ell = torch.as_tensor(ell, dtype=F64)
     fits = []
     for p in range(P):
         ell_p = ell[p] if ell.dim() == 2 else ell
         sf2_p = float(sf2[p]) if hasattr(sf2, "__len__") else float(sf2)
         noise_p = float(noise[p]) if hasattr(noise, "__len__") else float(noise)
-        f, _ = factorize(X, Y[:, p], ell_p, sf2_p, noise_p, W_out=Wall[p])
+        f, _ = factorize(X, Y[:, p], ell_p, sf2_p, noise_p, W_out=Wall[p], digits=digits, wimg_out=Iall[p])
         fits.append(f)
     return GPBatch.from_fits(fits)
 
@@ -338,7 +377,8 @@ def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise) -> GPBatch:
 VAR_WORK_BYTES = 4 << 30   # default scratch budget for the K_ZX chunks of the variance path
 
 
-def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_work_bytes: int | None = None):
+def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_work_bytes: int | None = None,
+            var_path: str = "i8"):
     """Posterior mean (B,Q), latent variance var_f (B,Q) and input-Jacobian (B,Q,d) at queries Z.
 
     Z: (Q,d) shared by all GPs or (B,Q,d); float64 or float32 selects the prediction path.  The batched
@@ -371,7 +411,19 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
     work = get_work("mean_jac", wbytes, dev)
     call("gpk_predict_mean_jac", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(pack), pack.stride(0), n,
          ptr(mean), q, ptr(jac), d, q * d, ptr(work), wbytes, B, st)
-    if want_var:
+    if want_var and var_path == "i8":
+        # variance contraction on the tcgen05 int8 pipe (exact digit products, fp64 recombination)
+        assert gp.wimg is not None, "fit without digit image: factorize(..., want_image=True)"
+        budget = VAR_WORK_BYTES if var_work_bytes is None else var_work_bytes
+        need = lib.gpk_predict_var_i8_work_bytes(q, npad, gp.digits, B)
+        vbytes = max(min(need, budget), lib.gpk_predict_var_i8_work_bytes(64, npad, gp.digits, B))
+        vwork = get_work("var_i8", vbytes, dev)
+        strideX = gp.X.stride(0) if B > 1 else 0
+        call("gpk_predict_var_i8", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(gp.X), gp.X.stride(1), n,
+             strideX, ptr(gp.wimg), gp.wimg.stride(0) if B > 1 else 0, ptr(gp.wscale), gp.wscale.stride(0) if B > 1 else 0,
+             npad, gp.digits, ptr(var), q, ptr(vwork), vbytes, B, st)
+    elif want_var:
+        assert var_path == "f64", "var_path must be 'i8' (tcgen05 int8 digits) or 'f64' (DMMA)"
         budget = VAR_WORK_BYTES if var_work_bytes is None else var_work_bytes
         need = lib.gpk_predict_var_work_bytes(q, npad, B)
         vbytes = max(min(need, budget), lib.gpk_predict_var_work_bytes(TILE, npad, B))

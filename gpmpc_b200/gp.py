@@ -342,7 +342,8 @@ def _loss_and_set_grads(gp: GaussianProcess, dev: torch.device, W_buf: torch.Ten
     .grad (replaces output = gp(train_x); loss = -mll(output, y); loss.backward(), gpmpc/gp.py:61-63)."""
     ell, sf2, noise = gp.hyperparameters()
     X = gp.train_inputs[0]
-    fit, ws = E.factorize(X.to(dev), gp.train_targets.to(dev), ell, sf2, noise, want_kinv=True, W_out=W_buf)
+    fit, ws = E.factorize(X.to(dev), gp.train_targets.to(dev), ell, sf2, noise, want_kinv=True, W_out=W_buf,
+                          want_image=False)
     if grad_reduce is None:
         partials = E.grad_partials(fit, ws)
     else:
