@@ -15,24 +15,27 @@
 // wants them in shared memory (K-major, no swizzle: 8-row x 16-byte core matrices), so a pipeline stage is
 // filled by ONE 1-D bulk TMA copy (cp.async.bulk, SASS UBLKCP) per operand and no tensor map is needed:
 //   byte offset of element (row r, k) inside a R x 64 slice tile:  (r/8)*512 + (k/16)*128 + (r%8)*16 + k%16
-//   W image : [gp][tile_m][kb][slice s][128 x 64 B]   (tile_m = 128 rows, kb = 64-wide k block)
-//   E image : [gp][qtile][kb][slice t][ 64 x 64 B]    (qtile = 64 queries)
+//   E image : [gp][qtile][kb][digit t][128 x 64 B]   (qtile = 128 queries = the MMA M side = TMEM lanes)
+//   W image : [gp][ib]   [kb][digit s][ 64 x 64 B]   (ib = block of 64 rows of W = the MMA N side; kb <= ib)
+// The queries sit on the TMEM lanes so that the sum over the rows of W of V^2 is a per-thread sum in the
+// epilogue (no cross-lane reduction), accumulated in registers over all the W row blocks a CTA walks through.
 #pragma once
 #include "common.cuh"
 
 namespace gpk {
 
-constexpr int OZ_BM = 128;            // rows of W per CTA tile (TMEM lanes)
-constexpr int OZ_BN = 64;             // queries per CTA tile (TMEM columns per digit group)
+constexpr int OZ_QT = 128;            // queries per CTA tile (MMA M, TMEM lanes)
+constexpr int OZ_WB = 64;             // rows of W per CTA tile (MMA N per digit group, TMEM columns)
 constexpr int OZ_BK = 64;             // k bytes per pipeline stage (2 MMA k-steps of 32)
-constexpr int OZ_A_SLICE = OZ_BM * OZ_BK;   // 8 KB
-constexpr int OZ_B_SLICE = OZ_BN * OZ_BK;   // 4 KB
+constexpr int OZ_A_SLICE = OZ_QT * OZ_BK;   // 8 KB  (E digit tile)
+constexpr int OZ_B_SLICE = OZ_WB * OZ_BK;   // 4 KB  (W digit tile)
 constexpr int OZ_MAX_S = 7;
+constexpr int OZ_MAX_PIECES = 8;
 constexpr int OZ_SMEM_LIMIT = 227 * 1024;
 
 __host__ __device__ constexpr int oz_stage_bytes(int S) { return S * (OZ_A_SLICE + OZ_B_SLICE); }
 __host__ __device__ constexpr int oz_stages(int S) {
-    return (OZ_SMEM_LIMIT - 2048) / oz_stage_bytes(S) > 4 ? 4 : (OZ_SMEM_LIMIT - 2048) / oz_stage_bytes(S);
+    return (OZ_SMEM_LIMIT - 4096) / oz_stage_bytes(S) > 4 ? 4 : (OZ_SMEM_LIMIT - 4096) / oz_stage_bytes(S);
 }
 // byte offset of (row r, k byte) inside one R x 64 slice tile
 __host__ __device__ constexpr int oz_tile_off(int r, int k) {
@@ -53,8 +56,74 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void tc_commit_pred(uint64_t* bar, uint32_t issue) {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.b32 q, %1, 0;\n"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(issue) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_pred(uint64_t* bar, uint32_t bytes, uint32_t issue) {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.b32 q, %2, 0;\n"
+        "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(bytes), "r"(issue) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s_pred(uint32_t smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar,
+                                                  uint32_t issue) {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.b32 q, %4, 0;\n"
+        "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
+        "}\n" ::"r"(smem_dst), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "r"(issue) : "memory");
+}
+// ---- CTA-pair (cluster of 2) variants: one copy feeds both CTAs' shared memory, one commit frees both ----
+__device__ __forceinline__ void tma_bulk_g2s_mcast_pred(uint32_t smem_dst, const void* gmem_src, uint32_t bytes,
+                                                        uint64_t* bar, uint16_t cta_mask, uint32_t issue) {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.b32 q, %5, 0;\n"
+        "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;\n"
+        "}\n" ::"r"(smem_dst), "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)), "h"(cta_mask), "r"(issue) : "memory");
+}
+__device__ __forceinline__ void tc_commit_mcast_pred(uint64_t* bar, uint16_t cta_mask, uint32_t issue) {
+    asm volatile(
+        "{\n"
+        ".reg .pred q;\n"
+        "setp.ne.b32 q, %2, 0;\n"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+        "}\n" ::"r"(smem_u32(bar)), "h"(cta_mask), "r"(issue) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");
+}
+// warp-uniform election of one lane (SASS ELECT): the single-thread tcgen05 / bulk-TMA instructions take their
+// operands from uniform registers, so the issuing code must stay warp-uniform and only be PREDICATED on the
+// elected lane -- inside a divergent `if (lane == 0)` region ptxas wraps every such instruction in a
+// convergence loop (R2UR + BRA.U.ANY) that costs ~150 cycles per instruction (measured, tools/peaks/umma_bench)
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.b32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(pred));
+    return pred != 0;
 }
 // D[tmem] (+)= A[smem] * B[smem]^T, int8 x int8 -> int32, one elected thread issues
 __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
@@ -64,6 +133,19 @@ __device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t a_desc, uint64
         "setp.ne.b32 p, %4, 0;\n"
         "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// the same, predicated inside the asm on `issue` (the elected lane): no C++ branch, so the surrounding code stays
+// warp-uniform and straight-line (no BSSY/BSYNC per instruction)
+__device__ __forceinline__ void umma_i8_pred(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate, uint32_t issue) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p, q;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "setp.ne.b32 q, %5, 0;\n"
+        "@q tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(issue)
         : "memory");
 }
 // shared-memory matrix descriptor: K-major, no swizzle; lbo = bytes between the two 16-byte k chunks of one
@@ -78,9 +160,15 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t 
 }
 // instruction descriptor: D = s32, A = B = signed int8, both K-major, M = 128, N = n
 __host__ __device__ constexpr uint32_t umma_idesc_i8(int n) {
-    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(OZ_BM >> 4) << 24);
+    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(OZ_QT >> 4) << 24);
 }
-// 32 lanes x 16 consecutive 32-bit columns: thread i of the warp receives lane (base lane + i)
+// 32 lanes x 8 consecutive 32-bit columns: thread i of the warp receives lane (base lane + i)
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, int32_t (&v)[8]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr));
+}
+// 32 lanes x 16 consecutive 32-bit columns
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, int32_t (&v)[16]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"

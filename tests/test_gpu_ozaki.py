@@ -53,10 +53,10 @@ def test_w_image_digits(env, S):
     m = W.abs().max(dim=1).values
     assert torch.all(sc > m) and torch.all(sc <= 2 * m), "row scale must be the next power of two above max|row|"
     assert torch.all(torch.log2(sc) == torch.round(torch.log2(sc)))
-    got = _decode(img, npad // 128, npad // 64, S, 128)
+    got = _decode(img, npad // 64, npad // 64, S, 64)
     ref = _digits_ref(W / sc[:, None], S)
-    # blocks above the diagonal tile are never written / read
-    mask = (torch.arange(npad)[None, :] // 64) < ((torch.arange(npad)[:, None] // 128) + 1) * 2
+    # blocks above the diagonal block are never written / read
+    mask = (torch.arange(npad)[None, :] // 64) <= ((torch.arange(npad)[:, None] // 64) | 1)
     assert torch.equal(got[:, mask], ref[:, mask])
     assert got.abs().max() <= 64
 
@@ -73,7 +73,7 @@ def test_e_image_reconstructs_kernel(env, S, dtype):
     Xd, Zd = X.to(dev), Z.to(dev)
     _lib.call("gpk_oz_cross", E.DTYPE_CODE[dtype], _lib.ptr(Zd), d, q, 0, _lib.ptr(Xd), d, n, 0, d, _lib.ptr(hyp),
               _lib.ptr(img), img.numel(), npad, qpad, S, 1, _lib.stream_ptr(dev))
-    dig = _decode(img, qpad // 64, npad // 64, S, 64).to(F64)
+    dig = _decode(img, qpad // 128, npad // 64, S, 128).to(F64)
     rec = sum(dig[s] * 2.0 ** (-6 - 7 * s) for s in range(S))
     ref = o.se_kernel(Z.to(F64), X, ell, 1.0)
     assert dig.abs().max() <= 64
@@ -101,34 +101,30 @@ def test_tensor_core_accumulators_exact(env, S):
     _lib.call("gpk_oz_slice_w", _lib.ptr(Wd), npad, npad, S, _lib.ptr(wimg), _lib.ptr(scale), st)
     _lib.call("gpk_oz_cross", 1, _lib.ptr(Zd), d, q, 0, _lib.ptr(Xd), d, n, 0, d, _lib.ptr(hyp), _lib.ptr(eimg),
               eimg.numel(), npad, qpad, S, 1, st)
-    tiles_m, qtiles = npad // 128, qpad // 64
-    colsq = torch.zeros(tiles_m, qpad, dtype=F64, device=dev)
-    dbg = torch.full((tiles_m * qtiles, S, 128, 64), -7, dtype=torch.int32, device=dev)
-    _lib.call("gpk_oz_var_colsq", _lib.ptr(wimg), 0, _lib.ptr(scale), 0, _lib.ptr(eimg), 0, _lib.ptr(hyp), npad, qpad, S,
-              _lib.ptr(colsq), qpad, 0, 1, _lib.ptr(dbg), st)
+    nib, qtiles = npad // 64, qpad // 128
+    pieces = 3
+    part = torch.zeros(2 * pieces, qpad, dtype=F64, device=dev)
+    dbg = torch.full((qtiles, nib, S, 128, 64), -7, dtype=torch.int32, device=dev)
+    _lib.call("gpk_oz_var_partials", _lib.ptr(eimg), 0, _lib.ptr(wimg), 0, _lib.ptr(scale), 0, _lib.ptr(hyp), npad, qpad, S,
+              _lib.ptr(part), qpad, 0, pieces, 1, _lib.ptr(dbg), st)
     torch.cuda.synchronize()
-    a = _decode(wimg, tiles_m, npad // 64, S, 128)          # (S, npad, npad)
-    b = _decode(eimg, qtiles, npad // 64, S, 64)            # (S, qpad, npad)
-    a = a * (torch.arange(npad)[None, :] < ((torch.arange(npad)[:, None] // 128) + 1) * 128)   # unread blocks
-    D = torch.zeros(S, npad, qpad, dtype=torch.int64)
-    for s in range(S):
-        for t in range(S - s):
-            D[s + t] += a[s] @ b[t].T
-    # tile id -> (tm, qt): LPT order, one chunk (group_n >= all columns here)
-    got = torch.zeros_like(D)
-    dbg_h = dbg.cpu().to(torch.int64)
-    for tile in range(tiles_m * qtiles):
-        tm = tiles_m - 1 - tile // qtiles
-        qt = tile % qtiles
-        got[:, tm * 128:(tm + 1) * 128, qt * 64:(qt + 1) * 64] = dbg_h[tile]
+    a = _decode(wimg, nib, npad // 64, S, 64)               # (S, npad, npad) digits of W
+    b = _decode(eimg, qtiles, npad // 64, S, 128)           # (S, qpad, npad) digits of E
+    a = a * ((torch.arange(npad)[None, :] // 64) <= ((torch.arange(npad)[:, None] // 64) | 1))   # unread blocks
+    D = torch.zeros(S, qpad, npad, dtype=torch.int64)
+    for s_ in range(S):
+        for t in range(S - s_):
+            D[s_ + t] += b[t] @ a[s_].T
+    got = dbg.cpu().to(torch.int64).permute(2, 0, 3, 1, 4).reshape(S, qpad, npad)   # (S, qt, row, ib, col)
     assert torch.equal(got, D)
-    # recombination: V = sf2 * scale_i / 4096 * sum_g 128^-g D_g ; colsq = per-tile column sums of V^2
+    # recombination: V = sf2 * scale_i / 4096 * sum_g 128^-g D_g ; part = per-piece sums over W rows of V^2
     R = sum(D[gi].to(F64) * 128.0 ** (-gi) for gi in range(S))
-    V = 1.3 * scale.cpu()[:, None] / 4096.0 * R
-    ref = (V * V).reshape(tiles_m, 128, qpad).sum(1)
-    assert (colsq.cpu() - ref).abs().max() <= 1e-13 * ref.abs().max()
-    # and against plain fp64:  V = W K_ZX^T
-    Vd = W[:, :n] @ o.se_kernel(Z, X, torch.full((d,), 0.7, dtype=F64), 1.3).T
-    refd = (Vd * Vd).reshape(tiles_m, 128, q).sum(1)
+    V = 1.3 * scale.cpu()[None, :] / 4096.0 * R             # (qpad, npad)
+    tot = part.cpu().sum(0)
+    ref = (V * V).sum(1)
+    assert (tot - ref).abs().max() <= 1e-13 * ref.abs().max()
+    # and against plain fp64:  V = K_ZX W^T
+    Vd = o.se_kernel(Z, X, torch.full((d,), 0.7, dtype=F64), 1.3) @ W[:, :n].T
+    refd = (Vd * Vd).sum(1)
     tol = {5: 1e-6, 6: 1e-8, 7: 1e-10}[S]
-    assert (colsq.cpu()[:, :q] - refd).abs().max() <= tol * refd.abs().max()
+    assert (tot[:q] - refd).abs().max() <= tol * refd.abs().max()
