@@ -88,83 +88,196 @@ oz_slice_w_kernel(const double* __restrict__ W, long ldw, int npad, const double
 }
 
 // ------------------------------------------------------------------------------------------------
-// queries -> E = exp(-1/2 |z~ - x~|^2) -> digit image.  One CTA per (kb group, qtile, gp): 128 queries,
-// thread = (query row, two 16-wide k chunks); the CTA walks over OZ_CK_KB k blocks.
-// Kernel formula gpmpc/gp.py:12-14 (sf2 is applied in the GEMM epilogue).
+// Fused prediction front end (north-star subsystem a + the operand of b):  for a tile of 128 queries and a
+// range of training points, E = exp(-1/2 |z~ - x~|^2) is evaluated ONCE in fp64 and used for
+//   (1) the int8 digit image of E (operand of the tcgen05 variance contraction), and
+//   (2) the posterior mean and input-Jacobian partial sums  m = sum_i a_i E_i,  S_j = sum_i a_i E_i x~_ij
+//       (a_i = sf2 alpha_i;  mean = m,  jac_j = (S_j - z~_j m) / ell_j;  gpmpc/gp.py:85 and the CasADi AD of
+//       gpmpc/gp.py:12-14 inside acados, gpmpc/gpmpc.py:189-211).
+// thread = (query row, every other 16-wide k chunk); digits come from ONE fused multiply-add per value
+// (E 2^(7S-1) + 1.5 2^52 leaves the fixed-point integer in the mantissa), a bias that turns the signed
+// base-128 digits into plain 7-bit fields, and byte permutes -- the FP64 pipe only sees the dot product,
+// exp, and the mean/Jacobian accumulation.
 // ------------------------------------------------------------------------------------------------
-constexpr int OZ_CK_KB = 4;          // k blocks (of 64 training points) per CTA
-constexpr int OZ_LD = HYP_MAXD + 1;
+template <int S>
+__device__ __forceinline__ void oz_pack_digits4(const double (&e)[4], uint32_t (&out)[S]) {
+    constexpr double SC = (double)(1ull << (6 + 7 * (S - 1)));
+    long long bias = 0;
+#pragma unroll
+    for (int i = 0; i < S; i++) bias += 64ll << (7 * i);
+    bias -= 0x4338000000000000LL;
+    uint32_t lo[4], mid[4];
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+        const long long b = __double_as_longlong(fma(e[v], SC, 6755399441055744.0)) + bias;   // sum_i (d_i + 64) 128^i
+        lo[v] = (uint32_t)b;
+        mid[v] = (uint32_t)(b >> 21);
+    }
+#pragma unroll
+    for (int i = 0; i < S; i++) {                       // i = 0: least significant digit
+        const int sh = i < 3 ? 7 * i : 7 * (i - 3);
+        uint32_t x[4];
+#pragma unroll
+        for (int v = 0; v < 4; v++) x[v] = (i < 3 ? lo[v] : mid[v]) >> sh;
+        uint32_t u = __byte_perm(__byte_perm(x[0], x[1], 0x0040), __byte_perm(x[2], x[3], 0x0040), 0x5410);
+        if (i == S - 1) {
+            u -= 0x40404040u;                           // leading field holds d + 64 in [64, 128]: no borrow
+        } else {
+            u = (u & 0x7F7F7F7Fu) ^ 0x40404040u;        // 7-bit offset binary -> 7-bit two's complement
+            u |= (u & 0x40404040u) << 1;                // sign-extend each byte
+        }
+        out[S - 1 - i] = u;
+    }
+}
 
-template <typename TZ, int S, int DP>
-__global__ void __launch_bounds__(256)
-oz_cross_kernel(const TZ* __restrict__ Z, long ldz, long q, long strideZ, const double* __restrict__ X, long ldx,
-                long n, long strideX, int d, const double* __restrict__ hyp_all, int8_t* __restrict__ img, long strideE,
-                int kb_total) {
-    __shared__ double Xs[OZ_BK * OZ_LD], ex[OZ_BK];
+struct OzFrontArgs {
+    const void* Z; long ldz, q, strideZ;
+    const double* X; long ldx, n, strideX;
+    const double* alpha; long stride_alpha;  // [gp][>= n]  (only when MJ)
+    int d;
+    const double* hyp;
+    int8_t* img; long strideE;               // digit image of E, [gp][qtile][kb][S][128 x 64]
+    int kb_total, kb_per_cta;
+    double* mj_part; long stride_mj;         // [gp][split][q][DP + 1] partial (m, S_j)
+};
+
+template <typename TZ, int S, int DP, bool MJ>
+__global__ void __launch_bounds__(256, 1) oz_front_kernel(const OzFrontArgs a) {
+    // staging of the training points; reused after the k loop to combine the two k halves of a query row
+    constexpr int SH_STAGE = OZ_BK * DP + 2 * OZ_BK, SH_COMB = MJ ? OZ_QT * (DP + 1) : 0;
+    __shared__ __align__(16) double sh[SH_STAGE > SH_COMB ? SH_STAGE : SH_COMB];
+    double* Xs = sh;
+    double* ex = sh + OZ_BK * DP;
+    double* as = ex + OZ_BK;
+    double* comb = sh;
     const long gp = blockIdx.z;
     const int qt = blockIdx.y;
-    const double* hyp = hyp_all + gp * HYP_STRIDE;
-    Z += gp * strideZ;
-    X += gp * strideX;
+    const double* hyp = a.hyp + gp * HYP_STRIDE;
+    const TZ* Z = reinterpret_cast<const TZ*>(a.Z) + gp * a.strideZ;
+    const double* X = a.X + gp * a.strideX;
     const int tid = threadIdx.x;
     const int r = tid & 127, kh = tid >> 7;              // 8 consecutive threads -> one 128-byte core matrix
     const long gq = (long)qt * OZ_QT + r;
+    const bool qvalid = gq < a.q;
 
-    double z[DP];
+    double z[DP], Sj[DP], m = 0.0;
     double ez = 0.0;
 #pragma unroll
     for (int j = 0; j < DP; j++) {
         double v = 0.0;
-        if (j < d && gq < q) v = ((double)Z[gq * ldz + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j];
+        if (j < a.d && qvalid) v = ((double)Z[gq * a.ldz + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j];
         z[j] = v;
+        Sj[j] = 0.0;
         ez = fma(v, v, ez);
     }
     ez *= -0.5;
 
-    for (int kbi = 0; kbi < OZ_CK_KB; kbi++) {
-        const int kb = blockIdx.x * OZ_CK_KB + kbi;
-        if (kb >= kb_total) break;
+    const int kb0 = blockIdx.x * a.kb_per_cta;
+    const int kb1 = min(a.kb_total, kb0 + a.kb_per_cta);
+    for (int kb = kb0; kb < kb1; kb++) {
         __syncthreads();
         {   // stage 64 scaled training points: 4 threads per point
             const int p = tid >> 2, part = tid & 3;
             const long gi = (long)kb * OZ_BK + p;
             double s = 0.0;
+#pragma unroll
             for (int j = part; j < DP; j += 4) {
-                const double v = (gi < n && j < d) ? (X[gi * ldx + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j] : 0.0;
-                Xs[p * OZ_LD + j] = v;
+                const double v = (gi < a.n && j < a.d) ? (X[gi * a.ldx + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j] : 0.0;
+                Xs[p * DP + j] = v;
                 s = fma(v, v, s);
             }
             s += __shfl_xor_sync(0xffffffffu, s, 1);
             s += __shfl_xor_sync(0xffffffffu, s, 2);
-            if (part == 0) ex[p] = -0.5 * s;
+            if (part == 0) {
+                ex[p] = gi < a.n ? -0.5 * s : -1.0e300;  // padding points: exp -> 0
+                if (MJ) as[p] = gi < a.n ? hyp[HYP_SF2] * a.alpha[gp * a.stride_alpha + gi] : 0.0;
+            }
         }
         __syncthreads();
-        int8_t* out = img + gp * strideE + ((long)qt * kb_total + kb) * S * OZ_A_SLICE;
+        int8_t* out = a.img + gp * a.strideE + ((long)qt * a.kb_total + kb) * S * OZ_A_SLICE;
 #pragma unroll 1
         for (int kc = kh; kc < OZ_BK / 16; kc += 2) {
-            int8_t dig[16][S];
+            uint32_t w[4][S];
 #pragma unroll
-            for (int k = 0; k < 16; k++) {
-                const int p = kc * 16 + k;
-                double a = ez + ex[p];
+            for (int g4 = 0; g4 < 4; g4++) {
+                double e[4];
 #pragma unroll
-                for (int j = 0; j < DP; j++) a = fma(z[j], Xs[p * OZ_LD + j], a);
-                const long gi = (long)kb * OZ_BK + p;
-                const double e = (gi < n && gq < q) ? exp(fmin(a, 0.0)) : 0.0;
-                signed_digits<S>(to_fixed<S>(e), dig[k]);
+                for (int v = 0; v < 4; v++) {
+                    const int p = kc * 16 + g4 * 4 + v;
+                    double x[DP];
+                    if constexpr (DP % 2 == 0) {
+#pragma unroll
+                        for (int j = 0; j < DP; j += 2) {
+                            const double2 t = *reinterpret_cast<const double2*>(&Xs[p * DP + j]);
+                            x[j] = t.x; x[j + 1] = t.y;
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < DP; j++) x[j] = Xs[p * DP + j];
+                    }
+                    double acc = ez + ex[p];
+#pragma unroll
+                    for (int j = 0; j < DP; j++) acc = fma(z[j], x[j], acc);
+                    const double ev = qvalid ? exp(fmin(acc, 0.0)) : 0.0;
+                    e[v] = ev;
+                    if (MJ) {
+                        const double wgt = ev * as[p];
+                        m += wgt;
+#pragma unroll
+                        for (int j = 0; j < DP; j++) Sj[j] = fma(wgt, x[j], Sj[j]);
+                    }
+                }
+                oz_pack_digits4<S>(e, w[g4]);
             }
 #pragma unroll
-            for (int s = 0; s < S; s++) {
-                uint32_t w4[4];
-#pragma unroll
-                for (int v = 0; v < 4; v++)
-                    w4[v] = (uint32_t)(uint8_t)dig[4 * v][s] | ((uint32_t)(uint8_t)dig[4 * v + 1][s] << 8) |
-                            ((uint32_t)(uint8_t)dig[4 * v + 2][s] << 16) | ((uint32_t)(uint8_t)dig[4 * v + 3][s] << 24);
+            for (int s = 0; s < S; s++)
                 *reinterpret_cast<uint4*>(out + (long)s * OZ_A_SLICE + oz_tile_off(r, kc * 16)) =
-                    make_uint4(w4[0], w4[1], w4[2], w4[3]);
-            }
+                    make_uint4(w[0][s], w[1][s], w[2][s], w[3][s]);
         }
     }
+    if (MJ) {
+        // combine the two k halves of each query row, then one partial per (split, query)
+        __syncthreads();
+        if (kh == 1) {
+            comb[r * (DP + 1)] = m;
+#pragma unroll
+            for (int j = 0; j < DP; j++) comb[r * (DP + 1) + 1 + j] = Sj[j];
+        }
+        __syncthreads();
+        if (kh == 0 && qvalid) {
+            double* dst = a.mj_part + gp * a.stride_mj + ((long)blockIdx.x * a.q + gq) * (DP + 1);
+            dst[0] = m + comb[r * (DP + 1)];
+#pragma unroll
+            for (int j = 0; j < DP; j++) dst[1 + j] = Sj[j] + comb[r * (DP + 1) + 1 + j];
+        }
+    }
+}
+
+// mean = sum of the split partials; jac_j = (S_j - z~_j mean) / ell_j
+template <typename TZ, int DP>
+__global__ void oz_mj_finalize_kernel(const OzFrontArgs a, int n_split, TZ* __restrict__ mean, long stride_mean,
+                                      TZ* __restrict__ jac, long ldj, long stride_jac) {
+    const long q = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long gp = blockIdx.z;
+    if (q >= a.q) return;
+    const double* hyp = a.hyp + gp * HYP_STRIDE;
+    const TZ* Z = reinterpret_cast<const TZ*>(a.Z) + gp * a.strideZ;
+    const double* part = a.mj_part + gp * a.stride_mj;
+    double acc[DP + 1];
+#pragma unroll
+    for (int j = 0; j <= DP; j++) acc[j] = 0.0;
+    for (int s = 0; s < n_split; s++) {
+        const double* w = part + ((long)s * a.q + q) * (DP + 1);
+#pragma unroll
+        for (int j = 0; j <= DP; j++) acc[j] += w[j];
+    }
+    mean[gp * stride_mean + q] = (TZ)acc[0];
+#pragma unroll
+    for (int j = 0; j < DP; j++)
+        if (j < a.d) {
+            const double zs = ((double)Z[q * a.ldz + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j];
+            jac[gp * stride_jac + q * ldj + j] = (TZ)((acc[1 + j] - zs * acc[0]) * hyp[HYP_INV_ELL + j]);
+        }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -443,18 +556,48 @@ static int oz_launch_var(const OzArgs& a, cudaStream_t st) {
     return 0;
 }
 
-template <typename TZ, int S>
-static int oz_launch_cross(const TZ* Z, long ldz, long q, long strideZ, const double* X, long ldx, long n, long strideX,
-                           int d, const double* hyp, int8_t* img, long strideE, int kb_total, long qtiles, int batch,
-                           cudaStream_t st) {
-    dim3 grid((unsigned)((kb_total + OZ_CK_KB - 1) / OZ_CK_KB), (unsigned)qtiles, (unsigned)batch);
-#define OZ_CROSS_CASE(DPV) case DPV: oz_cross_kernel<TZ, S, DPV><<<grid, 256, 0, st>>>(Z, ldz, q, strideZ, X, ldx, n, strideX, d, hyp, img, strideE, kb_total); break;
-    switch (oz_pad_dim(d)) {
-        OZ_CROSS_CASE(4) OZ_CROSS_CASE(8) OZ_CROSS_CASE(16) OZ_CROSS_CASE(32)
+// splits of the training range per query tile: the power of two (<= 16, <= k blocks) that wastes the least in
+// the last wave of CTAs (one 256-thread CTA per SM)
+static int oz_front_splits(long qtiles_total, int kb_total) {
+    int best = 1;
+    double best_waste = 1e30;
+    for (int ns = 1; ns <= 16 && ns <= kb_total; ns *= 2) {
+        const long ctas = qtiles_total * ns;
+        const long waves = (ctas + oz_sm_count() - 1) / oz_sm_count();
+        const double waste = (double)(waves * oz_sm_count()) / (double)ctas + 0.004 * ns;
+        if (waste < best_waste) { best_waste = waste; best = ns; }
     }
-#undef OZ_CROSS_CASE
+    return best;
+}
+
+template <typename TZ, int S, bool MJ>
+static int oz_launch_front(const OzFrontArgs& a, int n_split, long qtiles, int batch, TZ* mean, long stride_mean, TZ* jac,
+                           long ldj, long stride_jac, cudaStream_t st) {
+    dim3 grid((unsigned)n_split, (unsigned)qtiles, (unsigned)batch);
+    const int dp = oz_pad_dim(a.d);
+#define OZ_FRONT_CASE(DPV) case DPV: oz_front_kernel<TZ, S, DPV, MJ><<<grid, 256, 0, st>>>(a); break;
+    switch (dp) { OZ_FRONT_CASE(4) OZ_FRONT_CASE(8) OZ_FRONT_CASE(16) OZ_FRONT_CASE(32) }
+#undef OZ_FRONT_CASE
     GPK_LAUNCHED();
+    if (MJ) {
+        dim3 g2((unsigned)((a.q + 127) / 128), 1, (unsigned)batch);
+#define OZ_FIN_CASE(DPV) case DPV: oz_mj_finalize_kernel<TZ, DPV><<<g2, 128, 0, st>>>(a, n_split, mean, stride_mean, jac, ldj, stride_jac); break;
+        switch (dp) { OZ_FIN_CASE(4) OZ_FIN_CASE(8) OZ_FIN_CASE(16) OZ_FIN_CASE(32) }
+#undef OZ_FIN_CASE
+        GPK_LAUNCHED();
+    }
     return 0;
+}
+
+template <typename TZ>
+static int oz_front_dispatch(const OzFrontArgs& a, int S, bool mj, int n_split, long qtiles, int batch, void* mean,
+                             long stride_mean, void* jac, long ldj, long stride_jac, cudaStream_t st) {
+#define OZ_F(SV) \
+    if (S == SV) return mj ? oz_launch_front<TZ, SV, true>(a, n_split, qtiles, batch, (TZ*)mean, stride_mean, (TZ*)jac, ldj, stride_jac, st) \
+                           : oz_launch_front<TZ, SV, false>(a, n_split, qtiles, batch, nullptr, 0, nullptr, 0, 0, st);
+    OZ_F(5) OZ_F(6) OZ_F(7)
+#undef OZ_F
+    return fail(-1, "digits must be 5, 6 or 7");
 }
 
 extern "C" {
@@ -495,15 +638,17 @@ int gpk_oz_cross(int dtype, const void* Z, long ldz, long q, long strideZ, const
     GPK_ARG(npad % TILE == 0 && npad >= n && qpad % OZ_QT == 0 && qpad >= q && q > 0, "npad / qpad");
     GPK_ARG(S >= 5 && S <= OZ_MAX_S, "digits must be 5, 6 or 7");
     GPK_ARG(((uintptr_t)img % 16) == 0 && strideE % 16 == 0, "image alignment");
-    cudaStream_t st = (cudaStream_t)stream;
-    const int kb_total = (int)(npad / OZ_BK);
+    OzFrontArgs a{};
+    a.Z = Z; a.ldz = ldz; a.q = q; a.strideZ = strideZ;
+    a.X = X; a.ldx = ldx; a.n = n; a.strideX = strideX;
+    a.d = d; a.hyp = hyp;
+    a.img = (int8_t*)img; a.strideE = strideE;
+    a.kb_total = (int)(npad / OZ_BK);
     const long qtiles = qpad / OZ_QT;
-#define OZ_X(TZ, SV) return oz_launch_cross<TZ, SV>((const TZ*)Z, ldz, q, strideZ, X, ldx, n, strideX, d, hyp, (int8_t*)img, strideE, kb_total, qtiles, batch, st)
-    if (dtype == 0) { if (S == 5) OZ_X(float, 5); if (S == 6) OZ_X(float, 6); OZ_X(float, 7); }
-    if (S == 5) OZ_X(double, 5);
-    if (S == 6) OZ_X(double, 6);
-    OZ_X(double, 7);
-#undef OZ_X
+    const int ns = oz_front_splits(qtiles * batch, a.kb_total);
+    a.kb_per_cta = (a.kb_total + ns - 1) / ns;
+    if (dtype == 0) return oz_front_dispatch<float>(a, S, false, ns, qtiles, batch, nullptr, 0, nullptr, 0, 0, (cudaStream_t)stream);
+    return oz_front_dispatch<double>(a, S, false, ns, qtiles, batch, nullptr, 0, nullptr, 0, 0, (cudaStream_t)stream);
 }
 
 // part[gp][slot][q], slot < 2 n_pieces: sums of V[i][q]^2 over disjoint sets of W rows (V = sf2 W E^T);
@@ -546,45 +691,69 @@ int gpk_oz_var_partials(const void* Eimg, long strideE, const void* Wimg, long s
     return oz_launch_var<7>(a, st);
 }
 
-// ---- (7') posterior variance on the int8 tensor pipe ------------------------------------------------
-// var_f(z) = sf2 - || W k(X,z) ||^2 for q queries of `batch` GPs; queries go through in chunks that fit `work`
-// (digit image of E + per-piece partial sums).  Same contract as gpk_predict_var, W given as digit image.
+// ---- (6+7) fused posterior mean + Jacobian + variance ----------------------------------------------------
+// One pass over the (query, training point) pairs evaluates the kernel once: it feeds the mean / Jacobian sums
+// and the int8 digit image for the tcgen05 variance contraction  var_f(z) = sf2 - || W k(X,z) ||^2.
+// mean / jac may be NULL (variance only).  Queries go through in chunks that fit `work`.
 constexpr int OZ_SLOTS = 2 * OZ_MAX_PIECES;
-long gpk_predict_var_i8_work_bytes(long q_chunk, long npad, int S, int batch) {
+constexpr int OZ_MAX_SPLITS = 16;
+
+long gpk_predict_i8_work_bytes(long q_chunk, long npad, int d, int S, int batch) {
     const long qc = (q_chunk + OZ_QT - 1) / OZ_QT * OZ_QT;
-    return ((long)S * qc * npad + OZ_SLOTS * qc * 8) * batch;
+    return ((long)S * qc * npad + OZ_SLOTS * qc * 8 + (long)OZ_MAX_SPLITS * qc * (oz_pad_dim(d) + 1) * 8) * batch;
 }
 
 int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,
                      const double* hyp, void* var, long stride_var, int batch, void* stream);
 
-int gpk_predict_var_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
-                       const double* X, long ldx, long n, long strideX, const void* Wimg, long strideW,
-                       const double* wscale, long stride_ws, long npad, int S, void* var, long stride_var,
-                       void* work, long work_bytes, int batch, void* stream) {
+int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                   const double* X, long ldx, long n, long strideX, const double* alpha, long stride_alpha,
+                   const void* Wimg, long strideW, const double* wscale, long stride_ws, long npad, int S,
+                   void* mean, long stride_mean, void* jac, long ldj, long stride_jac, void* var, long stride_var,
+                   void* work, long work_bytes, int batch, void* stream) {
     GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
     GPK_ARG(Z && hyp && X && Wimg && wscale && var && work, "null pointer");
+    GPK_ARG((mean == nullptr) == (jac == nullptr), "mean and jac must both be given or both be NULL");
+    GPK_ARG(mean == nullptr || (alpha != nullptr && ldj >= d), "alpha / ldj");
+    GPK_ARG(d >= 1 && d <= HYP_MAXD, "d must be in [1, 32]");
     GPK_ARG(npad % TILE == 0 && npad >= n && n > 0 && batch >= 1, "n / npad / batch");
     GPK_ARG(S >= 5 && S <= OZ_MAX_S, "digits must be 5, 6 or 7");
     GPK_ARG(((uintptr_t)work % 16) == 0, "work must be 16-byte aligned");
     if (q == 0) return 0;
-    long qc = work_bytes / (((long)S * npad + OZ_SLOTS * 8) * batch);
+    const bool mj = mean != nullptr;
+    const int dp = oz_pad_dim(d);
+    const long per_q = ((long)S * npad + OZ_SLOTS * 8 + (long)OZ_MAX_SPLITS * (dp + 1) * 8) * batch;
+    long qc = work_bytes / per_q;
     qc = qc / OZ_QT * OZ_QT;
-    GPK_ARG(qc >= OZ_QT, "scratch too small (see gpk_predict_var_i8_work_bytes)");
+    GPK_ARG(qc >= OZ_QT, "scratch too small (see gpk_predict_i8_work_bytes)");
     const long q_round = (q + OZ_QT - 1) / OZ_QT * OZ_QT;
     if (qc > q_round) qc = q_round;
     int8_t* eimg = (int8_t*)work;                                         // [batch][S qc npad]
-    double* part = (double*)(eimg + (long)batch * S * qc * npad);         // [batch][pieces][qc]
+    double* part = (double*)(eimg + (long)batch * S * qc * npad);         // [batch][slots][qc]
+    double* mjp = part + (long)batch * OZ_SLOTS * qc;                     // [batch][splits][qn][dp + 1]
     const int esz = dtype == 0 ? 4 : 8;
+    cudaStream_t st = (cudaStream_t)stream;
     for (long q0 = 0; q0 < q; q0 += qc) {
         const long qn = (q - q0 < qc) ? (q - q0) : qc;
         const long qp = (qn + OZ_QT - 1) / OZ_QT * OZ_QT;
-        const int pieces = oz_num_pieces(qp / OZ_QT * batch, npad / (2 * OZ_WB));
-        const void* Zc = (const char*)Z + q0 * ldz * esz;
-        GPK_TRY(gpk_oz_cross(dtype, Zc, ldz, qn, strideZ, X, ldx, n, strideX, d, hyp, eimg, (long)S * qc * npad, npad, qp,
-                             S, batch, stream));
-        GPK_TRY(gpk_oz_var_partials(eimg, (long)S * qc * npad, Wimg, strideW, wscale, stride_ws, hyp, npad, qp, S, part,
-                                    qc, (long)OZ_SLOTS * qc, pieces, batch, nullptr, stream));
+        const long qtiles = qp / OZ_QT;
+        const int pieces = oz_num_pieces(qtiles * batch, npad / (2 * OZ_WB));
+        OzFrontArgs a{};
+        a.Z = (const char*)Z + q0 * ldz * esz; a.ldz = ldz; a.q = qn; a.strideZ = strideZ;
+        a.X = X; a.ldx = ldx; a.n = n; a.strideX = strideX;
+        a.alpha = alpha; a.stride_alpha = stride_alpha;
+        a.d = d; a.hyp = hyp;
+        a.img = eimg; a.strideE = (long)S * qc * npad;
+        a.kb_total = (int)(npad / OZ_BK);
+        const int ns = oz_front_splits(qtiles * batch, a.kb_total);
+        a.kb_per_cta = (a.kb_total + ns - 1) / ns;
+        a.mj_part = mjp; a.stride_mj = (long)OZ_MAX_SPLITS * qc * (dp + 1);
+        void* mout = mj ? (char*)mean + q0 * esz : nullptr;
+        void* jout = mj ? (char*)jac + q0 * ldj * esz : nullptr;
+        if (dtype == 0) GPK_TRY(oz_front_dispatch<float>(a, S, mj, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
+        else GPK_TRY(oz_front_dispatch<double>(a, S, mj, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
+        GPK_TRY(gpk_oz_var_partials(eimg, a.strideE, Wimg, strideW, wscale, stride_ws, hyp, npad, qp, S, part, qc,
+                                    (long)OZ_SLOTS * qc, pieces, batch, nullptr, stream));
         void* vout = (char*)var + q0 * esz;
         GPK_TRY(gpk_var_finalize(dtype, part, qc, (long)OZ_SLOTS * qc, 2 * pieces, qn, hyp, vout, stride_var, batch, stream));
     }

@@ -297,6 +297,13 @@ class GPBatch:
     wscale: torch.Tensor = None   # (B, npad)
     digits: int = 0
     packs: dict = field(default_factory=dict)
+    _alpha: torch.Tensor = None   # (B, npad), stacked lazily
+
+    @property
+    def alpha(self) -> torch.Tensor:
+        if self._alpha is None:
+            self._alpha = torch.stack([f.alpha for f in self.fits])
+        return self._alpha
 
     @classmethod
     def from_fits(cls, fits: list) -> "GPBatch":
@@ -406,23 +413,27 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
     var = torch.empty(B, q, dtype=dt, device=dev) if want_var else None
     if q == 0:
         return mean, var, jac
+    if want_var and var_path == "i8":
+        # fused front end (kernel evaluated once for mean, Jacobian and the digit image) + variance contraction
+        # on the tcgen05 int8 pipe (exact digit products, fp64 recombination)
+        assert gp.wimg is not None, "fit without digit image: factorize(..., want_image=True)"
+        budget = VAR_WORK_BYTES if var_work_bytes is None else var_work_bytes
+        need = lib.gpk_predict_i8_work_bytes(q, npad, d, gp.digits, B)
+        vbytes = max(min(need, budget), lib.gpk_predict_i8_work_bytes(128, npad, d, gp.digits, B))
+        vwork = get_work("predict_i8", vbytes, dev)
+        strideX = gp.X.stride(0) if B > 1 else 0
+        alpha = gp.alpha
+        call("gpk_predict_i8", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(gp.X), gp.X.stride(1), n,
+             strideX, ptr(alpha), alpha.stride(0), ptr(gp.wimg), gp.wimg.stride(0) if B > 1 else 0, ptr(gp.wscale),
+             gp.wscale.stride(0) if B > 1 else 0, npad, gp.digits, ptr(mean), q, ptr(jac), d, q * d, ptr(var), q,
+             ptr(vwork), vbytes, B, st)
+        return mean, var, jac
     pack = gp.pack(dt)
     wbytes = min(lib.gpk_mean_jac_work_bytes(code, q, n, d, B), 1 << 30)
     work = get_work("mean_jac", wbytes, dev)
     call("gpk_predict_mean_jac", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(pack), pack.stride(0), n,
          ptr(mean), q, ptr(jac), d, q * d, ptr(work), wbytes, B, st)
-    if want_var and var_path == "i8":
-        # variance contraction on the tcgen05 int8 pipe (exact digit products, fp64 recombination)
-        assert gp.wimg is not None, "fit without digit image: factorize(..., want_image=True)"
-        budget = VAR_WORK_BYTES if var_work_bytes is None else var_work_bytes
-        need = lib.gpk_predict_var_i8_work_bytes(q, npad, gp.digits, B)
-        vbytes = max(min(need, budget), lib.gpk_predict_var_i8_work_bytes(64, npad, gp.digits, B))
-        vwork = get_work("var_i8", vbytes, dev)
-        strideX = gp.X.stride(0) if B > 1 else 0
-        call("gpk_predict_var_i8", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(gp.X), gp.X.stride(1), n,
-             strideX, ptr(gp.wimg), gp.wimg.stride(0) if B > 1 else 0, ptr(gp.wscale), gp.wscale.stride(0) if B > 1 else 0,
-             npad, gp.digits, ptr(var), q, ptr(vwork), vbytes, B, st)
-    elif want_var:
+    if want_var:
         assert var_path == "f64", "var_path must be 'i8' (tcgen05 int8 digits) or 'f64' (DMMA)"
         budget = VAR_WORK_BYTES if var_work_bytes is None else var_work_bytes
         need = lib.gpk_predict_var_work_bytes(q, npad, B)

@@ -174,7 +174,8 @@ def test_full_size_properties_config2():
     assert float(var.min()) > 0.0 and float(var.max()) <= p["sf2"]
     m1, v1, j1 = E.predict(gb.fits[1], Z)
     # the training-set split over CTAs depends on the batch size, so the summation order differs
-    assert o.rel_err(m1[0], mean[1]) < 1e-12 and o.rel_err(j1[0], jac[1]) < 1e-12 and torch.equal(v1[0], var[1])
+    # (also for the variance: the number of W row pieces per query tile depends on the batch size)
+    assert o.rel_err(m1[0], mean[1]) < 1e-12 and o.rel_err(j1[0], jac[1]) < 1e-12 and o.rel_err(v1[0], var[1]) < 1e-12
     # a sample of the queries against the oracle
     idx = torch.arange(0, 8192, 64)
     st = o.fit_state(p["X"], p["Y"][:, 0], p["ell"], p["sf2"], p["noise"])
