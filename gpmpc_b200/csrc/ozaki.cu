@@ -130,6 +130,34 @@ __device__ __forceinline__ void oz_pack_digits4(const double (&e)[4], uint32_t (
     }
 }
 
+// exp(a) for a <= 0 to ~2^-51 relative error, branch-free: Cody-Waite reduction by ln 2, the degree-12 Taylor
+// polynomial on |r| <= ln2/2, and 2^n added straight into the exponent field (normal results down to
+// a = -708; below that the result is 0, where the library exp is subnormal or 0).
+__device__ __forceinline__ double oz_exp_neg(double a0) {
+    const double a = fmax(a0, -708.0);
+    const double MAGIC = 6755399441055744.0;             // 1.5 * 2^52
+    const double tn = fma(a, 1.4426950408889634074, MAGIC);
+    const double nd = tn - MAGIC;
+    double r = fma(nd, -6.93147180369123816490e-01, a);  // ln2 hi
+    r = fma(nd, -1.90821492927058770002e-10, r);         // ln2 lo
+    double p = 2.08767569878680989792e-09;               // 1/12!
+    p = fma(p, r, 2.50521083854417187751e-08);
+    p = fma(p, r, 2.75573192239858906526e-07);
+    p = fma(p, r, 2.75573192239858906526e-06);
+    p = fma(p, r, 2.48015873015873015873e-05);
+    p = fma(p, r, 1.98412698412698412698e-04);
+    p = fma(p, r, 1.38888888888888888889e-03);
+    p = fma(p, r, 8.33333333333333333333e-03);
+    p = fma(p, r, 4.16666666666666666667e-02);
+    p = fma(p, r, 1.66666666666666666667e-01);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    const int n = __double2loint(tn);                     // integer part of tn sits in the low mantissa word
+    const double e = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+    return a0 < -708.0 ? 0.0 : e;
+}
+
 struct OzFrontArgs {
     const void* Z; long ldz, q, strideZ;
     const double* X; long ldx, n, strideX;
@@ -141,114 +169,171 @@ struct OzFrontArgs {
     double* mj_part; long stride_mj;         // [gp][split][q][DP + 1] partial (m, S_j)
 };
 
+__device__ __forceinline__ void oz_dmma(double (&c)[2], double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+// Both GEMM-shaped parts run on the FP64 tensor pipe (DMMA m8n8k4), one warp per 16 queries:
+//   GEMM 1   -1/2 r^2 [8 queries x 8 points] = (-1/2|z~|^2 - 1/2|x~|^2) + z~ [8 x d] x~^T [d x 8]
+//   GEMM 2   S [8 queries x d] += (a E) [8 x 4 points] x~ [4 x d]
+// The point <-> fragment-column mapping is chosen so that the accumulator elements a thread holds after GEMM 1
+// are (i) exactly the A-fragment elements it must supply to GEMM 2 and (ii) four CONSECUTIVE training points
+// k = 4t .. 4t+3 of a 16-point unit, i.e. one aligned 32-bit word of each digit row: a warp's digit store is
+// one contiguous 128-byte core matrix.  Column c = 2t+u of block b  <->  point 4t + 2b + u.
 template <typename TZ, int S, int DP, bool MJ>
-__global__ void __launch_bounds__(256, 1) oz_front_kernel(const OzFrontArgs a) {
-    // staging of the training points; reused after the k loop to combine the two k halves of a query row
-    constexpr int SH_STAGE = OZ_BK * DP + 2 * OZ_BK, SH_COMB = MJ ? OZ_QT * (DP + 1) : 0;
-    __shared__ __align__(16) double sh[SH_STAGE > SH_COMB ? SH_STAGE : SH_COMB];
-    double* Xs = sh;
-    double* ex = sh + OZ_BK * DP;
-    double* as = ex + OZ_BK;
-    double* comb = sh;
+__global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
+    constexpr int KS = DP / 4;                           // GEMM 1 k-steps
+    constexpr int DPB = DP < 8 ? 8 : DP, NB = DPB / 8;   // GEMM 2 column blocks
+    constexpr int LDA = ((DP + 15) / 16) * 16 + 4;       // = 4 mod 16: conflict-free B fragments of GEMM 1
+    constexpr int LDB = DPB + 1;                         // = 1 mod 4 : conflict-free B fragments of GEMM 2
+    __shared__ __align__(16) double XsA[OZ_BK * LDA];    // rows in fragment-column order (see above)
+    __shared__ __align__(16) double XsB[MJ ? OZ_BK * LDB : 1];   // rows in natural order
+    __shared__ __align__(16) double ex[OZ_BK], as[OZ_BK];
     const long gp = blockIdx.z;
     const int qt = blockIdx.y;
     const double* hyp = a.hyp + gp * HYP_STRIDE;
     const TZ* Z = reinterpret_cast<const TZ*>(a.Z) + gp * a.strideZ;
     const double* X = a.X + gp * a.strideX;
-    const int tid = threadIdx.x;
-    const int r = tid & 127, kh = tid >> 7;              // 8 consecutive threads -> one 128-byte core matrix
-    const long gq = (long)qt * OZ_QT + r;
-    const bool qvalid = gq < a.q;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int g = lane >> 2, t = lane & 3;
 
-    double z[DP], Sj[DP], m = 0.0;
-    double ez = 0.0;
+    // A fragments of GEMM 1 (scaled queries) for the two 8-query blocks of this warp
+    double za[2][KS], ezq[2];
+    bool qv[2];
+    int qrow[2];
 #pragma unroll
-    for (int j = 0; j < DP; j++) {
-        double v = 0.0;
-        if (j < a.d && qvalid) v = ((double)Z[gq * a.ldz + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j];
-        z[j] = v;
-        Sj[j] = 0.0;
-        ez = fma(v, v, ez);
+    for (int mb = 0; mb < 2; mb++) {
+        qrow[mb] = warp * 16 + mb * 8 + g;
+        const long gq = (long)qt * OZ_QT + qrow[mb];
+        qv[mb] = gq < a.q;
+        double sq = 0.0;
+#pragma unroll
+        for (int s_ = 0; s_ < KS; s_++) {
+            const int j = t + 4 * s_;
+            double v = 0.0;
+            if (j < a.d && qv[mb]) v = ((double)Z[gq * a.ldz + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j];
+            za[mb][s_] = v;
+            sq = fma(v, v, sq);
+        }
+        sq += __shfl_xor_sync(0xffffffffu, sq, 1);
+        sq += __shfl_xor_sync(0xffffffffu, sq, 2);
+        ezq[mb] = -0.5 * sq;
     }
-    ez *= -0.5;
+    double S2[2][NB][2], msum[2] = {0.0, 0.0};
+#pragma unroll
+    for (int mb = 0; mb < 2; mb++)
+#pragma unroll
+        for (int nb = 0; nb < NB; nb++) S2[mb][nb][0] = S2[mb][nb][1] = 0.0;
 
     const int kb0 = blockIdx.x * a.kb_per_cta;
     const int kb1 = min(a.kb_total, kb0 + a.kb_per_cta);
+    // staging role: 4 threads per training point, thread `part` owns dimensions part, part + 4, ...
+    const int sp = tid >> 2, part = tid & 3;
+    const int kk = sp & 15;
+    const int slotA = (sp & ~15) + ((kk >> 1) & 1) * 8 + 2 * (kk >> 2) + (kk & 1);
+    constexpr int NPF = (DPB + 3) / 4;
+    double pf[NPF], pf_alpha = 0.0;
+    auto prefetch = [&](int kb) {                        // raw values of the next k block into registers
+        const long gi = (long)kb * OZ_BK + sp;
+#pragma unroll
+        for (int u = 0; u < NPF; u++) {
+            const int j = part + 4 * u;
+            pf[u] = (gi < a.n && j < a.d) ? X[gi * a.ldx + j] : 0.0;
+        }
+        if (MJ && part == 0) pf_alpha = gi < a.n ? a.alpha[gp * a.stride_alpha + gi] : 0.0;
+    };
+    if (kb0 < kb1) prefetch(kb0);
     for (int kb = kb0; kb < kb1; kb++) {
         __syncthreads();
-        {   // stage 64 scaled training points: 4 threads per point
-            const int p = tid >> 2, part = tid & 3;
-            const long gi = (long)kb * OZ_BK + p;
-            double s = 0.0;
+        {
+            const long gi = (long)kb * OZ_BK + sp;
+            double sq = 0.0;
 #pragma unroll
-            for (int j = part; j < DP; j += 4) {
-                const double v = (gi < a.n && j < a.d) ? (X[gi * a.ldx + j] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j] : 0.0;
-                Xs[p * DP + j] = v;
-                s = fma(v, v, s);
+            for (int u = 0; u < NPF; u++) {
+                const int j = part + 4 * u;
+                const double v = (gi < a.n && j < a.d) ? (pf[u] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j] : 0.0;
+                if (j < DP) XsA[slotA * LDA + j] = v;
+                if (MJ) XsB[sp * LDB + j] = v;
+                sq = fma(v, v, sq);
             }
-            s += __shfl_xor_sync(0xffffffffu, s, 1);
-            s += __shfl_xor_sync(0xffffffffu, s, 2);
+            sq += __shfl_xor_sync(0xffffffffu, sq, 1);
+            sq += __shfl_xor_sync(0xffffffffu, sq, 2);
             if (part == 0) {
-                ex[p] = gi < a.n ? -0.5 * s : -1.0e300;  // padding points: exp -> 0
-                if (MJ) as[p] = gi < a.n ? hyp[HYP_SF2] * a.alpha[gp * a.stride_alpha + gi] : 0.0;
+                ex[sp] = gi < a.n ? -0.5 * sq : -1.0e300;  // padding points: exp -> 0
+                as[sp] = MJ ? hyp[HYP_SF2] * pf_alpha : 0.0;
             }
         }
         __syncthreads();
+        if (kb + 1 < kb1) prefetch(kb + 1);              // in flight during the compute below
         int8_t* out = a.img + gp * a.strideE + ((long)qt * a.kb_total + kb) * S * OZ_A_SLICE;
 #pragma unroll 1
-        for (int kc = kh; kc < OZ_BK / 16; kc += 2) {
-            uint32_t w[4][S];
+        for (int unit = 0; unit < OZ_BK / 16; unit++) {
+            const int p0 = unit * 16 + 4 * t;            // this thread's four consecutive training points
+            double b1[2][KS];
 #pragma unroll
-            for (int g4 = 0; g4 < 4; g4++) {
-                double e[4];
+            for (int b = 0; b < 2; b++)
 #pragma unroll
-                for (int v = 0; v < 4; v++) {
-                    const int p = kc * 16 + g4 * 4 + v;
-                    double x[DP];
-                    if constexpr (DP % 2 == 0) {
+                for (int s_ = 0; s_ < KS; s_++) b1[b][s_] = XsA[(unit * 16 + b * 8 + g) * LDA + t + 4 * s_];
+            const double2 ex01 = *reinterpret_cast<const double2*>(&ex[p0]);
+            const double2 ex23 = *reinterpret_cast<const double2*>(&ex[p0 + 2]);
+            double b2[4][NB], as4[4];
+            if (MJ) {
+                const double2 as01 = *reinterpret_cast<const double2*>(&as[p0]);
+                const double2 as23 = *reinterpret_cast<const double2*>(&as[p0 + 2]);
+                as4[0] = as01.x; as4[1] = as01.y; as4[2] = as23.x; as4[3] = as23.y;
 #pragma unroll
-                        for (int j = 0; j < DP; j += 2) {
-                            const double2 t = *reinterpret_cast<const double2*>(&Xs[p * DP + j]);
-                            x[j] = t.x; x[j + 1] = t.y;
-                        }
-                    } else {
+                for (int i = 0; i < 4; i++)
 #pragma unroll
-                        for (int j = 0; j < DP; j++) x[j] = Xs[p * DP + j];
-                    }
-                    double acc = ez + ex[p];
-#pragma unroll
-                    for (int j = 0; j < DP; j++) acc = fma(z[j], x[j], acc);
-                    const double ev = qvalid ? exp(fmin(acc, 0.0)) : 0.0;
-                    e[v] = ev;
-                    if (MJ) {
-                        const double wgt = ev * as[p];
-                        m += wgt;
-#pragma unroll
-                        for (int j = 0; j < DP; j++) Sj[j] = fma(wgt, x[j], Sj[j]);
-                    }
-                }
-                oz_pack_digits4<S>(e, w[g4]);
+                    for (int nb = 0; nb < NB; nb++) b2[i][nb] = XsB[(p0 + i) * LDB + g + 8 * nb];
             }
 #pragma unroll
-            for (int s = 0; s < S; s++)
-                *reinterpret_cast<uint4*>(out + (long)s * OZ_A_SLICE + oz_tile_off(r, kc * 16)) =
-                    make_uint4(w[0][s], w[1][s], w[2][s], w[3][s]);
+            for (int mb = 0; mb < 2; mb++) {
+                double c[2][2];
+                c[0][0] = ezq[mb] + ex01.x; c[0][1] = ezq[mb] + ex01.y;
+                c[1][0] = ezq[mb] + ex23.x; c[1][1] = ezq[mb] + ex23.y;
+#pragma unroll
+                for (int s_ = 0; s_ < KS; s_++) {
+                    oz_dmma(c[0], za[mb][s_], b1[0][s_]);
+                    oz_dmma(c[1], za[mb][s_], b1[1][s_]);
+                }
+                double e[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) e[i] = qv[mb] ? oz_exp_neg(fmin(c[i >> 1][i & 1], 0.0)) : 0.0;
+                uint32_t w[S];
+                oz_pack_digits4<S>(e, w);
+                int8_t* dst = out + oz_tile_off(qrow[mb], unit * 16 + 4 * t);
+#pragma unroll
+                for (int s_ = 0; s_ < S; s_++) *reinterpret_cast<uint32_t*>(dst + (long)s_ * OZ_A_SLICE) = w[s_];
+                if (MJ) {
+#pragma unroll
+                    for (int i = 0; i < 4; i++) {
+                        const double wgt = e[i] * as4[i];
+                        msum[mb] += wgt;
+#pragma unroll
+                        for (int nb = 0; nb < NB; nb++) oz_dmma(S2[mb][nb], wgt, b2[i][nb]);
+                    }
+                }
+            }
         }
     }
     if (MJ) {
-        // combine the two k halves of each query row, then one partial per (split, query)
-        __syncthreads();
-        if (kh == 1) {
-            comb[r * (DP + 1)] = m;
 #pragma unroll
-            for (int j = 0; j < DP; j++) comb[r * (DP + 1) + 1 + j] = Sj[j];
-        }
-        __syncthreads();
-        if (kh == 0 && qvalid) {
+        for (int mb = 0; mb < 2; mb++) {
+            double m = msum[mb];
+            m += __shfl_xor_sync(0xffffffffu, m, 1);
+            m += __shfl_xor_sync(0xffffffffu, m, 2);
+            if (!qv[mb]) continue;
+            const long gq = (long)qt * OZ_QT + qrow[mb];
             double* dst = a.mj_part + gp * a.stride_mj + ((long)blockIdx.x * a.q + gq) * (DP + 1);
-            dst[0] = m + comb[r * (DP + 1)];
+            if (t == 0) dst[0] = m;
 #pragma unroll
-            for (int j = 0; j < DP; j++) dst[1 + j] = Sj[j] + comb[r * (DP + 1) + 1 + j];
+            for (int nb = 0; nb < NB; nb++)
+#pragma unroll
+                for (int cc = 0; cc < 2; cc++) {
+                    const int j = 8 * nb + 2 * t + cc;
+                    if (j < DP) dst[1 + j] = S2[mb][nb][cc];
+                }
         }
     }
 }
