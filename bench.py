@@ -40,7 +40,7 @@ DMMA_PEAK_TFLOPS = 37.1   # measured on this pool's B200 by tools/peaks (profile
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -289,36 +289,54 @@ def run_b200(args):
 
 
 def measure_roofline(gb, Z, flush, dev, steps):
-    """Dominant kernel = var_colsq_kernel (V = W K_ZX^T with the column-norm epilogue, FP64 DMMA pipe).
-    Algorithmic work per launch: N^2 flops per prediction (triangular contraction) x P*Q
-    predictions.  Timed alone with CUDA events on its launch stream, K_ZX prepared beforehand, L2 flushed."""
+    """Dominant kernel = oz_var_kernel: the variance contraction V = W K_ZX^T on the tcgen05 int8 pipe (exact
+    digit products in TMEM, fp64 recombination).  Timed alone with CUDA events on its launch stream, digit
+    image of E prepared beforehand, L2 flushed before every launch.
+
+    achieved = int8 tensor-pipe operations the algorithm needs per launch / launch time, where the algorithmic
+    count is SURVEY.md 8d's N^2 flops per prediction (triangular contraction) x the S(S+1)/2 digit products an
+    S-digit error-free fp64 product consists of x P*Q predictions.  peak = 2 x the measured dense bf16 burst of
+    MEASURED_PEAKS.json (the int8 tcgen05 rate is exactly twice the bf16 rate: 8192 vs 4096 MAC/clk/SM,
+    tools/peaks/umma_bench); the file holds no int8 figure of its own."""
     from gpmpc_b200 import _lib, engine as E
     from gpmpc_b200._lib import call, ptr
 
-    B, n, d, npad = len(gb.fits), gb.n, gb.d, gb.npad
+    lib = _lib.load()
+    B, n, d, npad, S = len(gb.fits), gb.n, gb.d, gb.npad, gb.digits
     q = Z.shape[0]
-    qp = E.round_up(q, 128)
-    tiles_m = npad // 128
+    qp = E.round_up(q, lib.gpk_oz_query_tile())
     st = _lib.stream_ptr(dev)
-    kzx = torch.empty(B, qp, npad, dtype=torch.float64, device=dev)
-    colsq = torch.empty(B, tiles_m, qp, dtype=torch.float64, device=dev)
-    call("gpk_cross_kernel", 1, ptr(Z), Z.stride(0), q, 0, ptr(gb.X), gb.X.stride(1), n, gb.X.stride(0), d, ptr(gb.hyp),
-         ptr(kzx), npad, qp * npad, qp, npad, 0, B, st)
+    eimg = torch.empty(B, S * qp * npad, dtype=torch.int8, device=dev)
+    pieces = lib.gpk_oz_pieces(qp // lib.gpk_oz_query_tile() * B, npad)
+    part = torch.empty(B, 16, qp, dtype=torch.float64, device=dev)
+    call("gpk_oz_cross", 1, ptr(Z), Z.stride(0), q, 0, ptr(gb.X), gb.X.stride(1), n, gb.X.stride(0), d, ptr(gb.hyp),
+         ptr(eimg), eimg.stride(0), npad, qp, S, B, st)
 
     def gemm():
-        call("gpk_var_colsq", ptr(gb.W), npad, gb.W.stride(0), ptr(kzx), npad, qp * npad, npad, qp, ptr(colsq), qp,
-             tiles_m * qp, B, st)
+        call("gpk_oz_var_partials", ptr(eimg), eimg.stride(0), ptr(gb.wimg), gb.wimg.stride(0), ptr(gb.wscale),
+             gb.wscale.stride(0), ptr(gb.hyp), npad, qp, S, ptr(part), qp, 16 * qp, pieces, B, None, st)
 
     for _ in range(3):
         gemm()
     ms = timed_steps(gemm, steps, flush, dev) / steps
-    flops = float(n) * n * B * q
-    achieved = flops / (ms * 1e-3) / 1e12
-    return {"kernel": "var_colsq_kernel (variance contraction W K_ZX^T, fp64 DMMA)", "bound": "tensor", "achieved": achieved,
-            "peak": DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": achieved / DMMA_PEAK_TFLOPS, "traffic": None,
-            "ms_per_launch": ms, "algorithmic_flops_per_launch": flops,
-            "peak_source": "fp64 DMMA m8n8k4 microbenchmark on this pool's B200 (profiles/peaks_micro_r01.json); "
-                           "MEASURED_PEAKS.json holds only bf16/HBM peaks, tcgen05 has no f64 kind"}
+    fp64_flops = float(n) * n * B * q                       # SURVEY.md 8d: N^2 flops per prediction
+    int8_ops = fp64_flops * S * (S + 1) / 2
+    achieved = int8_ops / (ms * 1e-3) / 1e12
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except OSError:
+        pass
+    bf16 = peaks.get("bf16_tflops")
+    peak = 2.0 * bf16 if bf16 else 2.0 * 1590.0
+    return {"kernel": f"oz_var_kernel<{S}> (variance contraction W K_ZX^T, {S}-digit int8 slices on tcgen05, int32 TMEM "
+                      "accumulators, fp64 recombination)",
+            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TOP/s (int8)", "frac": achieved / peak,
+            "traffic": None, "ms_per_launch": ms, "algorithmic_int8_ops_per_launch": int8_ops,
+            "fp64_equivalent_tflops": fp64_flops / (ms * 1e-3) / 1e12, "fp64_dmma_peak_tflops": DMMA_PEAK_TFLOPS,
+            "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops (burst, of measured)" if bf16 else
+                            "2 x 1590 TFLOP/s bf16 (of fallback)") + "; nominal int8 dense 4500 TOP/s"}
 
 
 def measure_extras(gb, problem, Z, flush, dev):
@@ -331,6 +349,11 @@ def measure_extras(gb, problem, Z, flush, dev):
         E.predict(gb, Z32)
     ms = timed_steps(lambda: E.predict(gb, Z32), 10, flush, dev) / 10
     out["f32_path_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
+    # the same step with the variance contraction on the FP64 DMMA pipe (round-1 first path, kept as var_path="f64")
+    for _ in range(3):
+        E.predict(gb, Z, var_path="f64")
+    ms = timed_steps(lambda: E.predict(gb, Z, var_path="f64"), 10, flush, dev) / 10
+    out["dmma_var_path_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
     for name, zz in (("f64", Z), ("f32", Z32)):
         for _ in range(3):
             E.predict(gb, zz, want_var=False)
