@@ -15,25 +15,25 @@
 namespace gpk {
 
 // ------------------------------------------------------------------------------------------------
-// signed base-128 digits of a non-negative / signed fixed-point integer (most significant digit first)
-//   I = sum_s dig[s] * 128^(S-1-s),  dig[s] in [-64, 64]
+// balanced base-256 digits of a signed fixed-point integer (most significant digit first)
+//   I = sum_s dig[s] * 256^(S-1-s),  dig[s] in [-128, 127]  (leading digit in [-64, 64] by the scaling)
 // ------------------------------------------------------------------------------------------------
 template <int S>
 __device__ __forceinline__ void signed_digits(long long I, int8_t (&dig)[S]) {
 #pragma unroll
     for (int s = S - 1; s > 0; s--) {
-        const int low = (int)(I & 127);
-        const int dgt = low >= 64 ? low - 128 : low;     // in [-64, 63]
+        const int low = (int)(I & 255);
+        const int dgt = low >= 128 ? low - 256 : low;    // in [-128, 127]
         dig[s] = (int8_t)dgt;
-        I = (I - dgt) >> 7;
+        I = (I - dgt) >> 8;
     }
     dig[0] = (int8_t)I;                                  // |I| <= 64 by construction of the scaling
 }
 
-// x in [-1, 1] -> nearest integer of x * 2^(6 + 7 (S-1)) (exact for S <= 7: fits the 52-bit mantissa)
+// x in [-1, 1] -> nearest integer of x * 2^(6 + 8 (S-1))  (S <= 6: 46 bits)
 template <int S>
 __device__ __forceinline__ long long to_fixed(double x) {
-    constexpr double SCALE = (double)(1ull << (6 + 7 * (S - 1)));
+    constexpr double SCALE = (double)(1ull << (6 + 8 * (S - 1)));
     return __double2ll_rn(x * SCALE);
 }
 
@@ -95,38 +95,30 @@ oz_slice_w_kernel(const double* __restrict__ W, long ldw, int npad, const double
 //       (a_i = sf2 alpha_i;  mean = m,  jac_j = (S_j - z~_j m) / ell_j;  gpmpc/gp.py:85 and the CasADi AD of
 //       gpmpc/gp.py:12-14 inside acados, gpmpc/gpmpc.py:189-211).
 // thread = (query row, every other 16-wide k chunk); digits come from ONE fused multiply-add per value
-// (E 2^(7S-1) + 1.5 2^52 leaves the fixed-point integer in the mantissa), a bias that turns the signed
-// base-128 digits into plain 7-bit fields, and byte permutes -- the FP64 pipe only sees the dot product,
-// exp, and the mean/Jacobian accumulation.
+// (E 2^(8S-2) + 1.5 2^52 leaves the fixed-point integer in the mantissa), a bias of 128 per digit that turns
+// the balanced base-256 digits into the plain BYTES of that integer (two's complement = byte ^ 0x80), and
+// byte permutes -- the FP64 pipe only sees the GEMMs, exp, and the mean accumulation.
 // ------------------------------------------------------------------------------------------------
 template <int S>
 __device__ __forceinline__ void oz_pack_digits4(const double (&e)[4], uint32_t (&out)[S]) {
-    constexpr double SC = (double)(1ull << (6 + 7 * (S - 1)));
+    constexpr double SC = (double)(1ull << (6 + 8 * (S - 1)));
     long long bias = 0;
 #pragma unroll
-    for (int i = 0; i < S; i++) bias += 64ll << (7 * i);
+    for (int i = 0; i < S; i++) bias += 128ll << (8 * i);
     bias -= 0x4338000000000000LL;
-    uint32_t lo[4], mid[4];
+    uint32_t lo[4], hi[4];
 #pragma unroll
     for (int v = 0; v < 4; v++) {
-        const long long b = __double_as_longlong(fma(e[v], SC, 6755399441055744.0)) + bias;   // sum_i (d_i + 64) 128^i
+        const long long b = __double_as_longlong(fma(e[v], SC, 6755399441055744.0)) + bias;   // sum_i (d_i + 128) 256^i
         lo[v] = (uint32_t)b;
-        mid[v] = (uint32_t)(b >> 21);
+        hi[v] = (uint32_t)(b >> 32);
     }
 #pragma unroll
-    for (int i = 0; i < S; i++) {                       // i = 0: least significant digit
-        const int sh = i < 3 ? 7 * i : 7 * (i - 3);
-        uint32_t x[4];
-#pragma unroll
-        for (int v = 0; v < 4; v++) x[v] = (i < 3 ? lo[v] : mid[v]) >> sh;
-        uint32_t u = __byte_perm(__byte_perm(x[0], x[1], 0x0040), __byte_perm(x[2], x[3], 0x0040), 0x5410);
-        if (i == S - 1) {
-            u -= 0x40404040u;                           // leading field holds d + 64 in [64, 128]: no borrow
-        } else {
-            u = (u & 0x7F7F7F7Fu) ^ 0x40404040u;        // 7-bit offset binary -> 7-bit two's complement
-            u |= (u & 0x40404040u) << 1;                // sign-extend each byte
-        }
-        out[S - 1 - i] = u;
+    for (int i = 0; i < S; i++) {                       // i = 0: least significant digit = byte i of the integer
+        const uint32_t sel = (uint32_t)((i & 3) | (((i & 3) + 4) << 4));
+        const uint32_t p01 = __byte_perm(i < 4 ? lo[0] : hi[0], i < 4 ? lo[1] : hi[1], sel);
+        const uint32_t p23 = __byte_perm(i < 4 ? lo[2] : hi[2], i < 4 ? lo[3] : hi[3], sel);
+        out[S - 1 - i] = __byte_perm(p01, p23, 0x5410) ^ 0x80808080u;
     }
 }
 
@@ -410,7 +402,7 @@ __device__ __forceinline__ double oz_ll2d(long long v) {
     // exact int64 -> double for |v| < 2^51 without the conversion pipe: bit pattern of 1.5 * 2^52 + v, minus the bias
     return __longlong_as_double(0x4338000000000000LL + v) - 6755399441055744.0;
 }
-// R = sum_g 128^-g D_g: digit groups are combined three at a time in exact int64 arithmetic (integer pipe),
+// R = sum_g 256^-g D_g: digit groups are combined three at a time in exact int64 arithmetic (integer pipe),
 // so the FP64 pipe only sees one conversion add per triple and the Horner steps between triples
 template <int S>
 __device__ __forceinline__ double oz_recombine(const int32_t (&v)[S][8], int j) {
@@ -422,10 +414,10 @@ __device__ __forceinline__ double oz_recombine(const int32_t (&v)[S][8], int j) 
         const int cnt = (S - g0) < 3 ? (S - g0) : 3;
         long long t = v[g0][j];
 #pragma unroll
-        for (int u = 1; u < cnt; u++) t = t * 128 + v[g0 + u][j];
-        // t = sum_u D_{g0+u} 128^(cnt-1-u); its weight relative to the triple's leading digit is 128^-(cnt-1)
-        const double dv = oz_ll2d(t) * (cnt == 3 ? 1.0 / 16384.0 : cnt == 2 ? 1.0 / 128.0 : 1.0);
-        acc = (tr == NT - 1) ? dv : fma(acc, 1.0 / 2097152.0, dv);
+        for (int u = 1; u < cnt; u++) t = t * 256 + v[g0 + u][j];
+        // t = sum_u D_{g0+u} 256^(cnt-1-u); its weight relative to the triple's leading digit is 256^-(cnt-1)
+        const double dv = oz_ll2d(t) * (cnt == 3 ? 1.0 / 65536.0 : cnt == 2 ? 1.0 / 256.0 : 1.0);
+        acc = (tr == NT - 1) ? dv : fma(acc, 1.0 / 16777216.0, dv);
     }
     return acc;
 }
@@ -680,19 +672,19 @@ static int oz_front_dispatch(const OzFrontArgs& a, int S, bool mj, int n_split, 
 #define OZ_F(SV) \
     if (S == SV) return mj ? oz_launch_front<TZ, SV, true>(a, n_split, qtiles, batch, (TZ*)mean, stride_mean, (TZ*)jac, ldj, stride_jac, st) \
                            : oz_launch_front<TZ, SV, false>(a, n_split, qtiles, batch, nullptr, 0, nullptr, 0, 0, st);
-    OZ_F(5) OZ_F(6) OZ_F(7)
+    OZ_F(4) OZ_F(5) OZ_F(6)
 #undef OZ_F
-    return fail(-1, "digits must be 5, 6 or 7");
+    return fail(-1, "digits must be 4, 5 or 6");
 }
 
 extern "C" {
 
-int gpk_oz_default_digits(void) { return 6; }
+int gpk_oz_default_digits(void) { return 5; }
 int gpk_oz_query_tile(void) { return OZ_QT; }
 
-long gpk_oz_w_image_bytes(long npad, int S) { return (npad % TILE || S < 5 || S > OZ_MAX_S) ? -1 : (long)S * npad * npad; }
+long gpk_oz_w_image_bytes(long npad, int S) { return (npad % TILE || S < OZ_MIN_S || S > OZ_MAX_S) ? -1 : (long)S * npad * npad; }
 long gpk_oz_e_image_bytes(long qpad, long npad, int S) {
-    return (qpad % OZ_QT || npad % TILE || S < 5 || S > OZ_MAX_S) ? -1 : (long)S * qpad * npad;
+    return (qpad % OZ_QT || npad % TILE || S < OZ_MIN_S || S > OZ_MAX_S) ? -1 : (long)S * qpad * npad;
 }
 int gpk_oz_pieces(long qtiles_total, long npad) { return oz_num_pieces(qtiles_total, npad / (2 * OZ_WB)); }
 
@@ -700,15 +692,15 @@ int gpk_oz_pieces(long qtiles_total, long npad) { return oz_num_pieces(qtiles_to
 int gpk_oz_slice_w(const double* W, long ldw, long npad, int S, void* img, double* wscale, void* stream) {
     GPK_ARG(W && img && wscale, "null pointer");
     GPK_ARG(npad > 0 && npad % TILE == 0 && ldw >= npad, "npad / ldw");
-    GPK_ARG(S >= 5 && S <= OZ_MAX_S, "digits must be 5, 6 or 7");
+    GPK_ARG(S >= OZ_MIN_S && S <= OZ_MAX_S, "digits must be 4, 5 or 6");
     GPK_ARG(((uintptr_t)img % 16) == 0, "image must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
     oz_row_scale_kernel<<<(unsigned)((npad + 7) / 8), 256, 0, st>>>(W, ldw, (int)npad, wscale);
     GPK_LAUNCHED();
     dim3 grid((unsigned)(npad / OZ_BK), (unsigned)(npad / OZ_WB));
-    if (S == 5) oz_slice_w_kernel<5><<<grid, 256, 0, st>>>(W, ldw, (int)npad, wscale, (int8_t*)img);
-    else if (S == 6) oz_slice_w_kernel<6><<<grid, 256, 0, st>>>(W, ldw, (int)npad, wscale, (int8_t*)img);
-    else oz_slice_w_kernel<7><<<grid, 256, 0, st>>>(W, ldw, (int)npad, wscale, (int8_t*)img);
+    if (S == 4) oz_slice_w_kernel<4><<<grid, 256, 0, st>>>(W, ldw, (int)npad, wscale, (int8_t*)img);
+    else if (S == 5) oz_slice_w_kernel<5><<<grid, 256, 0, st>>>(W, ldw, (int)npad, wscale, (int8_t*)img);
+    else oz_slice_w_kernel<6><<<grid, 256, 0, st>>>(W, ldw, (int)npad, wscale, (int8_t*)img);
     GPK_LAUNCHED();
     return 0;
 }
@@ -721,7 +713,7 @@ int gpk_oz_cross(int dtype, const void* Z, long ldz, long q, long strideZ, const
     GPK_ARG(Z && X && hyp && img, "null pointer");
     GPK_ARG(d >= 1 && d <= HYP_MAXD && n > 0 && batch >= 1, "n / d / batch");
     GPK_ARG(npad % TILE == 0 && npad >= n && qpad % OZ_QT == 0 && qpad >= q && q > 0, "npad / qpad");
-    GPK_ARG(S >= 5 && S <= OZ_MAX_S, "digits must be 5, 6 or 7");
+    GPK_ARG(S >= OZ_MIN_S && S <= OZ_MAX_S, "digits must be 4, 5 or 6");
     GPK_ARG(((uintptr_t)img % 16) == 0 && strideE % 16 == 0, "image alignment");
     OzFrontArgs a{};
     a.Z = Z; a.ldz = ldz; a.q = q; a.strideZ = strideZ;
@@ -743,9 +735,9 @@ int gpk_oz_var_partials(const void* Eimg, long strideE, const void* Wimg, long s
                         long stride_part, int n_pieces, int batch, int* dbg, void* stream) {
     GPK_ARG(Wimg && wscale && Eimg && hyp && part, "null pointer");
     GPK_ARG(npad > 0 && npad % TILE == 0 && qpad > 0 && qpad % OZ_QT == 0 && ld_part >= qpad && batch >= 1, "sizes");
-    GPK_ARG(S >= 5 && S <= OZ_MAX_S, "digits must be 5, 6 or 7");
+    GPK_ARG(S >= OZ_MIN_S && S <= OZ_MAX_S, "digits must be 4, 5 or 6");
     GPK_ARG(((uintptr_t)Wimg % 16) == 0 && ((uintptr_t)Eimg % 16) == 0 && strideW % 16 == 0 && strideE % 16 == 0, "alignment");
-    GPK_ARG(npad <= 65536, "npad too large for the int32 accumulators");
+    GPK_ARG((long)S * npad * 16384 < (1L << 31), "npad too large for exact int32 accumulation with this many digits");
     const long nib = npad / (2 * OZ_WB);     // W row-block pairs
     GPK_ARG(n_pieces >= 1 && n_pieces <= OZ_MAX_PIECES && n_pieces <= nib, "n_pieces");
     OzArgs a{};
@@ -771,9 +763,9 @@ int gpk_oz_var_partials(const void* Eimg, long strideE, const void* Wimg, long s
     a.dbg = dbg;
     a.flags = getenv("GPK_OZ_FLAGS") ? atoi(getenv("GPK_OZ_FLAGS")) : 0;
     cudaStream_t st = (cudaStream_t)stream;
+    if (S == 4) return oz_launch_var<4>(a, st);
     if (S == 5) return oz_launch_var<5>(a, st);
-    if (S == 6) return oz_launch_var<6>(a, st);
-    return oz_launch_var<7>(a, st);
+    return oz_launch_var<6>(a, st);
 }
 
 // ---- (6+7) fused posterior mean + Jacobian + variance ----------------------------------------------------
@@ -802,7 +794,7 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
     GPK_ARG(mean == nullptr || (alpha != nullptr && ldj >= d), "alpha / ldj");
     GPK_ARG(d >= 1 && d <= HYP_MAXD, "d must be in [1, 32]");
     GPK_ARG(npad % TILE == 0 && npad >= n && n > 0 && batch >= 1, "n / npad / batch");
-    GPK_ARG(S >= 5 && S <= OZ_MAX_S, "digits must be 5, 6 or 7");
+    GPK_ARG(S >= OZ_MIN_S && S <= OZ_MAX_S, "digits must be 4, 5 or 6");
     GPK_ARG(((uintptr_t)work % 16) == 0, "work must be 16-byte aligned");
     if (q == 0) return 0;
     const bool mj = mean != nullptr;

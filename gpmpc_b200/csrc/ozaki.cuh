@@ -4,12 +4,13 @@
 // int8 x int8 -> int32 accumulation is exact, so a product of two S-digit fixed-point operands needs
 // S(S+1)/2 exact int8 GEMMs and one fp64 recombination:
 //
-//   W[i][k]  = 2^ew_i * sum_s a_s[i][k] * 2^(-6-7s)         a_s in [-64, 64]  (signed digits, int8)
-//   E[q][k]  =          sum_t b_t[q][k] * 2^(-6-7t)         E = exp(-r^2/2) in (0, 1]
-//   V[i][q]  = sf2 * 2^ew_i * 2^-12 * sum_g 2^(-7g) D_g[i][q],   D_g = sum_{s+t=g} a_s b_t^T   (int32, exact)
+//   W[i][k]  = 2^ew_i * sum_s a_s[i][k] * 2^(-6-8s)         a_s in [-128, 127]  (balanced base-256 digits, int8;
+//   E[q][k]  =          sum_t b_t[q][k] * 2^(-6-8t)          leading digit in [-64, 64]);  E = exp(-r^2/2) in (0, 1]
+//   V[i][q]  = sf2 * 2^ew_i * 2^-12 * sum_g 2^(-8g) D_g[i][q],   D_g = sum_{s+t=g} a_s b_t^T   (int32, exact)
 //
-// truncated at g < S (S = 5/6/7: |error| ~ 2^(-7S) relative to max|W_i| -- S = 6 reproduces the fp64
-// variance to ~2e-10 relative at N = 2048, see tests).  Everything but the final Horner sum is exact.
+// truncated at g < S (S = 4/5/6 digits = 30/38/46 bits: |error| ~ 2^(-8S+2) relative to max|W_i| -- S = 5
+// reproduces the fp64 variance to ~2e-9 relative at N = 2048, see tests).  Everything but the final
+// recombination is exact; the int32 accumulators cannot overflow while S * N * 2^14 < 2^31.
 //
 // Shared-memory / HBM operand layout ("tile images"): operands are stored in HBM exactly as the tensor core
 // wants them in shared memory (K-major, no swizzle: 8-row x 16-byte core matrices), so a pipeline stage is
@@ -29,7 +30,7 @@ constexpr int OZ_WB = 64;             // rows of W per CTA tile (MMA N per digit
 constexpr int OZ_BK = 64;             // k bytes per pipeline stage (2 MMA k-steps of 32)
 constexpr int OZ_A_SLICE = OZ_QT * OZ_BK;   // 8 KB  (E digit tile)
 constexpr int OZ_B_SLICE = OZ_WB * OZ_BK;   // 4 KB  (W digit tile)
-constexpr int OZ_MAX_S = 7;
+constexpr int OZ_MIN_S = 4, OZ_MAX_S = 6;
 constexpr int OZ_MAX_PIECES = 8;
 constexpr int OZ_SMEM_LIMIT = 227 * 1024;
 

@@ -174,7 +174,7 @@ def slice_w(W: torch.Tensor, npad: int, digits: int | None = None, wimg_out=None
     digits = lib.gpk_oz_default_digits() if digits is None else digits
     dev = W.device
     nbytes = lib.gpk_oz_w_image_bytes(npad, digits)
-    assert nbytes > 0, "digits must be 5, 6 or 7"
+    assert nbytes > 0, "digits must be 4, 5 or 6"
     wimg = wimg_out if wimg_out is not None else torch.empty(nbytes, dtype=torch.int8, device=dev)
     wscale = wscale_out if wscale_out is not None else torch.empty(npad, dtype=F64, device=dev)
     call("gpk_oz_slice_w", ptr(W), W.stride(0), npad, digits, ptr(wimg), ptr(wscale), _lib.stream_ptr(dev))

@@ -3,7 +3,7 @@ sys.path.insert(0,'.')
 from gpmpc_b200 import engine as E, _lib
 from oracle import gp_oracle as o
 dev=torch.device('cuda',0)
-for S in (5,6,7):
+for S in (4,5,6):
     p=o.synthetic_problem(2048,16,8192,p=3,seed=1337)
     gb=E.fit_batch(p["X"].to(dev),p["Y"].to(dev),p["ell"],p["sf2"],p["noise"],digits=S)
     Z=p["Z"].to(dev)
