@@ -11,6 +11,7 @@
 //                         issuer, 4 epilogue warps (TMEM -> fp64 Horner recombination -> column sums of squares)
 #include "ozaki.cuh"
 #include <cstdlib>
+#include <type_traits>
 
 namespace gpk {
 
@@ -359,12 +360,12 @@ __global__ void oz_mj_finalize_kernel(const OzFrontArgs a, int n_split, TZ* __re
 
 // ------------------------------------------------------------------------------------------------
 // the GEMM: persistent CTAs (one per SM), 10 warps
-//   warp 0      producer: per stage two 1-D bulk TMA copies (all S digit slices of the E and of the W k-block)
-//   warp 1      TMEM allocation + MMA issue (one thread).  For E digit t one instruction multiplies against the
+//   warp 8      producer: per stage two 1-D bulk TMA copies (all S digit slices of the E and of the W k-block)
+//   warp 9      TMEM allocation + MMA issue (one thread).  For E digit t one instruction multiplies against the
 //               CONCATENATION of W digits 0..S-1-t (N = 64 (S-t), split at 256) and accumulates into digit
 //               groups t..S-1, which sit side by side in TMEM: S+2 instructions per k-step instead of
 //               S(S+1)/2, and each E slice is read from shared memory once per k-step
-//   warps 2..9  epilogue: tcgen05.ld the S int32 accumulators, Horner in fp64, row scale, square, and add into
+//   warps 0..7  epilogue: tcgen05.ld the S int32 accumulators, Horner in fp64, row scale, square, and add into
 //               the per-query running sum (one query per TMEM lane = per thread; two warps per lane quarter
 //               split the 64 columns)
 // CTA pairs (cluster of 2): both CTAs work on the SAME query tile and on W row blocks 2j and 2j+1, so each
@@ -388,6 +389,9 @@ struct OzArgs {
 
 constexpr int OZ_EPI_WARPS = 8;
 constexpr int OZ_THREADS = 64 + 32 * OZ_EPI_WARPS;
+// the two single-thread roles get the HIGHEST warp ids: the SM's issue arbiter prefers higher warp ids, and the
+// MMA issuer must never queue behind the epilogue warps that share its scheduler
+constexpr int OZ_PRODUCER_WARP = OZ_EPI_WARPS, OZ_MMA_WARP = OZ_EPI_WARPS + 1;
 
 __device__ __forceinline__ void oz_item_coords(const OzArgs& a, int item, int& qt, int& gp, int& jp0, int& jp1) {
     const int col = item / a.n_pieces;            // consecutive items share the query tile (its E image stays in L2)
@@ -427,6 +431,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
     constexpr int NST = oz_stages(S);
     constexpr uint32_t STAGE_BYTES = oz_stage_bytes(S);
     constexpr uint32_t A_BYTES = S * OZ_A_SLICE, B_BYTES = S * OZ_B_SLICE;
+    // TMEM: a tile's S digit groups take 64 S of the 512 columns.  Two buffers at columns 0 and SPARE = 512 - 64 S
+    // alternate between tiles; they share NOV = 2 S - 8 groups (the last ones of buffer 0 = the first ones of
+    // buffer 1).  The epilogue pulls those shared groups into registers first and releases the MMA issuer, so the
+    // next tile's main loop overlaps with the rest of the epilogue.  With more than 2 shared groups (S = 6) the
+    // registers do not suffice and one buffer is used.
+    constexpr int NOV = 2 * S - 8;
+    constexpr bool DB = NOV <= 2;
+    constexpr uint32_t SPARE = 512 - 64 * S;
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[NST], empty_bar[NST], tmem_full_bar, tmem_empty_bar;
     __shared__ uint32_t tmem_base_smem;
@@ -442,14 +454,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
         mbar_init(&tmem_empty_bar, 32 * OZ_EPI_WARPS);
         mbar_fence_init();
     }
-    if (warp == 1) tmem_alloc(&tmem_base_smem, 512);
+    if (warp == OZ_MMA_WARP) tmem_alloc(&tmem_base_smem, 512);
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();                      // the peer's barriers are initialised before anything is multicast
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
 
-    if (warp == 0) {
+    if (warp == OZ_PRODUCER_WARP) {
         // ===== producer (warp-uniform, elected lane issues) =====
         const uint32_t leader = elect_one() ? 1u : 0u;
         int st = 0; uint32_t ph = 0;
@@ -470,16 +482,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == OZ_MMA_WARP) {
         // ===== MMA issuer: the whole warp runs the loops (warp-uniform), the elected lane issues =====
         const uint32_t leader = elect_one() ? 1u : 0u;
-        int st = 0; uint32_t ph = 0, tph = 0;
+        int st = 0; uint32_t ph = 0, tph = 0, par = 0;
         for (int item = pair_id; item < a.total_items; item += n_pairs) {
             int qt, gp, jp0, jp1;
             oz_item_coords(a, item, qt, gp, jp0, jp1);
             for (int jp = jp1 - 1; jp >= jp0; jp--) {
-                mbar_wait(&tmem_empty_bar, tph ^ 1);          // epilogue has drained the accumulators
+                // the epilogue of the previous tile has drained the columns this tile's buffer shares with it
+                mbar_wait(&tmem_empty_bar, tph ^ 1);
                 tc_fence_after();
+                const uint32_t dbase = tmem_base + (DB ? par * SPARE : 0u);
+                par ^= 1;
                 for (int kb = 0; kb <= 2 * jp + 1; kb++) {
                     mbar_wait(&full_bar[st], ph);
                     tc_fence_after();
@@ -501,7 +516,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
                             for (int h = 0; h < nparts; h++) {
                                 // rows [h npart, (h+1) npart) of the concatenation: byte offset = rows * 64
                                 const uint64_t bdesc = umma_smem_desc(b_base + h * npart * OZ_BK + j * 256, 128, OZ_BK * 8);
-                                umma_i8_pred(tmem_base + (uint32_t)(t * OZ_WB + h * npart), adesc, bdesc, umma_idesc_i8(npart), acc, leader);
+                                umma_i8_pred(dbase + (uint32_t)(t * OZ_WB + h * npart), adesc, bdesc, umma_idesc_i8(npart), acc, leader);
                             }
                         }
                     }
@@ -513,12 +528,59 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
             }
         }
     } else {
-        // ===== epilogue: warps 2..9; lane quarter = warp % 4, column half = (warp - 2) / 4 =====
+        // ===== epilogue: warps 0..7; lane quarter = warp % 4, column half = warp / 4 =====
         const int quarter = warp & 3;
-        const int half = (warp - 2) >> 2;
+        const int half = warp >> 2;
         const int row = quarter * 32 + lane;                   // query within the tile
         const uint32_t tbase = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32);
-        uint32_t tph = 0;
+        uint32_t tph = 0, par = 0;
+        // one tile through the double-buffered path; PAR = which TMEM buffer holds it
+        auto tile_db = [&](auto par_tag, const double* wsb, int32_t* dp, double& sum) {
+            constexpr int PAR = decltype(par_tag)::value;
+            constexpr int NREST = S - NOV;
+            constexpr int OV0 = PAR == 0 ? S - NOV : 0;           // first shared group (in this buffer's numbering)
+            constexpr int RS0 = PAR == 0 ? 0 : NOV;               // first non-shared group
+            const uint32_t tb = tbase + (PAR ? SPARE : 0u);
+            int32_t vo[NOV > 0 ? NOV : 1][4][8];
+            int32_t v[2][NREST][8];
+#pragma unroll
+            for (int g = 0; g < NOV; g++)
+#pragma unroll
+                for (int c = 0; c < 4; c++) tmem_ld8(tb + (uint32_t)((OV0 + g) * OZ_WB + c * 8), vo[g][c]);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(&tmem_empty_bar);                          // the next tile may start accumulating
+#pragma unroll
+            for (int g = 0; g < NREST; g++) tmem_ld8(tb + (uint32_t)((RS0 + g) * OZ_WB), v[0][g]);
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                tmem_ld_wait();
+                if (c < 3) {
+#pragma unroll
+                    for (int g = 0; g < NREST; g++) tmem_ld8(tb + (uint32_t)((RS0 + g) * OZ_WB + (c + 1) * 8), v[(c + 1) & 1][g]);
+                }
+                int32_t vv[S][8];
+#pragma unroll
+                for (int g = 0; g < S; g++)
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        const bool shared = g >= OV0 && g < OV0 + NOV;
+                        vv[g][j] = shared ? vo[shared ? g - OV0 : 0][c][j] : v[c & 1][shared ? 0 : g - RS0][j];
+                    }
+                if (dp) {
+#pragma unroll
+                    for (int g = 0; g < S; g++)
+#pragma unroll
+                        for (int j = 0; j < 8; j++) dp[(long)g * OZ_QT * OZ_WB + c * 8 + j] = vv[g][j];
+                }
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    double acc = oz_recombine<S>(vv, j);
+                    acc *= __ldg(wsb + c * 8 + j);
+                    sum = fma(acc, acc, sum);
+                }
+            }
+        };
         for (int item = pair_id; item < a.total_items; item += n_pairs) {
             int qt, gp, jp0, jp1;
             oz_item_coords(a, item, qt, gp, jp0, jp1);
@@ -536,6 +598,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
                     mbar_arrive(&tmem_empty_bar);
                     continue;
                 }
+                int32_t* dp = a.dbg ? a.dbg + ((((long)(gp * a.qtiles + qt) * a.kb_total + ib) * S) * OZ_QT + row) * OZ_WB + half * 32
+                                    : nullptr;
+                if constexpr (DB) {
+                    if (par) tile_db(std::integral_constant<int, 1>{}, wsb, dp, sum);
+                    else tile_db(std::integral_constant<int, 0>{}, wsb, dp, sum);
+                    par ^= 1;
+                    continue;
+                }
                 int32_t v[2][S][8];
 #pragma unroll
                 for (int g = 0; g < S; g++) tmem_ld8(tbase + (uint32_t)(g * OZ_WB), v[0][g]);
@@ -549,12 +619,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
                         tc_fence_before();
                         mbar_arrive(&tmem_empty_bar);
                     }
-                    if (a.dbg) {
-                        int32_t* dp = a.dbg + ((((long)(gp * a.qtiles + qt) * a.kb_total + ib) * S) * OZ_QT + row) * OZ_WB + half * 32 + c * 8;
+                    if (dp) {
 #pragma unroll
                         for (int g = 0; g < S; g++)
 #pragma unroll
-                            for (int j = 0; j < 8; j++) dp[(long)g * OZ_QT * OZ_WB + j] = v[c & 1][g][j];
+                            for (int j = 0; j < 8; j++) dp[(long)g * OZ_QT * OZ_WB + c * 8 + j] = v[c & 1][g][j];
                     }
 #pragma unroll
                     for (int j = 0; j < 8; j++) {
@@ -577,7 +646,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
     tc_fence_before();
     __syncthreads();
     cluster_sync_all();                      // the peer may still be multicasting into / arriving on this CTA
-    if (warp == 1) {
+    if (warp == OZ_MMA_WARP) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
     }

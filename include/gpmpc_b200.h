@@ -1,6 +1,6 @@
 /* gpmpc_b200 -- C ABI of the B200-native Gaussian-process hot path of gp-mpc.
  *
- * One shared library (gpmpc_b200/libgpmpc_b200.so, sm_100a only).  Every entry point takes raw DEVICE
+ * One shared library (gpmpc_b200/libgpmpc_b200.so, sm_100a only).  Every compute entry point takes raw DEVICE
  * pointers, explicit sizes / leading dimensions (in elements), an explicit cudaStream_t (passed as
  * void*), and returns int:  0 = ok,  < 0 = bad argument (-1) or CUDA error (-(1000 + cudaError_t));
  * numerical failure of the Cholesky is reported LAPACK-style through the device-side `info` word
@@ -112,6 +112,42 @@ int gpk_var_colsq(const double* W, long ldw, long strideW, const double* kzx, lo
                   void* stream);
 int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,
                      const double* hyp, void* var, long stride_var, int batch, void* stream);
+
+/* ---- (6+7) fused prediction on the tensor pipes: mean + Jacobian + variance in one pass ---------------
+ * The default prediction path.  The kernel k(z, X) (gpmpc/gp.py:12-14) is evaluated ONCE per (query, training
+ * point) pair by DMMA GEMMs + exp and feeds
+ *   - mean(z) = k(z,X) alpha (gpmpc/gp.py:85) and jac(z) = d mean / d z (CasADi AD inside acados,
+ *     gpmpc/gpmpc.py:189-211), and
+ *   - var_f(z) = sf2 - || W k(X,z) ||^2, the diagonal gpmpc/gpmpc.py:443-445 keeps of
+ *     gp.likelihood(gp(z)).covariance_matrix (without the noise), whose contraction runs on the tcgen05 int8
+ *     tensor cores: fp64 operands are split error-free into `digits` balanced base-256 int8 slices ("Ozaki
+ *     scheme"), the S(S+1)/2 slice products accumulate exactly in int32 (TMEM) and are recombined in fp64.
+ *     digits = 4 / 5 / 6 keep 30 / 38 / 46 bits (5: ~2e-9 relative variance error at N = 2048).
+ * gpk_oz_slice_w builds the digit image of W = L^-1 once per fit (image layout: csrc/ozaki.cuh).
+ * mean / jac may both be NULL (variance only).  Scratch: gpk_predict_i8_work_bytes(q_chunk, ...); queries are
+ * processed in chunks that fit the scratch given. */
+int gpk_oz_default_digits(void);
+int gpk_oz_query_tile(void);                               /* queries per tile of the E image (128) */
+long gpk_oz_w_image_bytes(long npad, int digits);          /* -1 if unsupported */
+long gpk_oz_e_image_bytes(long qpad, long npad, int digits);
+int gpk_oz_pieces(long qtiles_total, long npad);           /* partial-sum pieces per query tile used by the GEMM */
+int gpk_oz_slice_w(const double* W, long ldw, long npad, int digits, void* img, double* wscale, void* stream);
+long gpk_predict_i8_work_bytes(long q_chunk, long npad, int d, int digits, int batch);
+int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                   const double* X, long ldx, long n, long strideX, const double* alpha, long stride_alpha,
+                   const void* Wimg, long strideW, const double* wscale, long stride_ws, long npad, int digits,
+                   void* mean, long stride_mean, void* jac, long ldj, long stride_jac, void* var, long stride_var,
+                   void* work, long work_bytes, int batch, void* stream);
+/* the two stages of (6+7) on their own, for tests and bench.py:
+ *   gpk_oz_cross         queries -> int8 digit image of E = exp(-r^2/2), [batch][qpad/128][npad/64][digits][128x64]
+ *   gpk_oz_var_partials  part[gp][slot][q], slot < 2 n_pieces: sums of (W k)_i^2 over disjoint sets of rows i;
+ *                        dbg (optional) receives the raw int32 accumulators [tile][row block][digit group][128][64] */
+int gpk_oz_cross(int dtype, const void* Z, long ldz, long q, long strideZ, const double* X, long ldx, long n,
+                 long strideX, int d, const double* hyp, void* img, long strideE, long npad, long qpad, int digits,
+                 int batch, void* stream);
+int gpk_oz_var_partials(const void* Eimg, long strideE, const void* Wimg, long strideW, const double* wscale,
+                        long stride_ws, const double* hyp, long npad, long qpad, int digits, double* part,
+                        long ld_part, long stride_part, int n_pieces, int batch, int* dbg, void* stream);
 
 /* ---- building block exposed for tests ---------------------------------------------------------
  * C = beta C + alpha A B^T on the FP64 DMMA pipe; M, N multiples of 128, K of 16.
