@@ -10,6 +10,7 @@
 //   alpha   : t = W y, alpha = U t (two triangular GEMVs, HBM-bound), quad = |t|^2, logdet = 2 sum log L_ii
 // All matrices are row-major, padded to a multiple of 128 with an identity block (see engine.py).
 #include "dgemm_nt.cuh"
+#include <type_traits>
 
 namespace gpk {
 
@@ -84,71 +85,139 @@ static GemmParams gemm_args(const double* A, long lda, const double* B, long ldb
 // 128x128 leaf: Cholesky of a diagonal block in shared memory + inverse of its factor
 // ------------------------------------------------------------------------------------------------
 constexpr int P_N = 128, P_LD = 129;
-constexpr int P_SMEM = (P_N * P_LD + 256) * 8;
+// call f(std::integral_constant<int, v>) for the run-time v in [0, 8): keeps register arrays statically indexed
+#define P_DISPATCH8(v, f)                                                         \
+    switch (v) {                                                                  \
+        case 0: f(std::integral_constant<int, 0>{}); break;                       \
+        case 1: f(std::integral_constant<int, 1>{}); break;                       \
+        case 2: f(std::integral_constant<int, 2>{}); break;                       \
+        case 3: f(std::integral_constant<int, 3>{}); break;                       \
+        case 4: f(std::integral_constant<int, 4>{}); break;                       \
+        case 5: f(std::integral_constant<int, 5>{}); break;                       \
+        case 6: f(std::integral_constant<int, 6>{}); break;                       \
+        default: f(std::integral_constant<int, 7>{}); break;                      \
+    }
+constexpr int P_SMEM = (P_N * P_LD + 3 * P_N) * 8;
 
+// 256 threads as a 16 x 16 grid; thread (ty, tx) keeps the 8 x 8 block rows 8ty.., columns 8tx.. in REGISTERS.
+// Both phases are right-looking with two barriers per column and 64 FMAs per thread in between:
+//   phase 1  Cholesky:  column j is scaled by 1/sqrt(a_jj) and published, every block below/right of it does
+//            a[r][c] -= l_rj l_cj; the thread that owns a_(j+1)(j+1) publishes the next pivot in the same step
+//   phase 2  inverse by forward elimination of [L | I]:  row j of X is divided by l_jj and published, every
+//            row R > j does x[R][c] -= l_Rj x[j][c]   (X = L^-1 stays lower triangular)
 __global__ void __launch_bounds__(256, 1)
 potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, int* __restrict__ info, int row_offset) {
-    extern __shared__ __align__(16) double S[];
-    double* scratch = S + P_N * P_LD;
+    extern __shared__ __align__(16) double S[];          // L, row-major with leading dimension P_LD
+    double* col = S + P_N * P_LD;                        // published column j of L / row j of X
+    double* piv = col + P_N;                             // next pivot (double-buffered by column parity)
     const int tid = threadIdx.x;
-    for (int idx = tid; idx < P_N * (P_N / 2); idx += 256) {
-        const int r = idx >> 6, c = (idx & 63) * 2;
-        const double2 v = *reinterpret_cast<const double2*>(A + (long)r * lda + c);
-        S[r * P_LD + c] = v.x;
-        S[r * P_LD + c + 1] = v.y;
-    }
+    const int ty = tid >> 4, tx = tid & 15;
+    const int r0 = ty * 8, c0 = tx * 8;
+    double a[8][8];
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+        for (int c = 0; c < 8; c += 2) {
+            const double2 v = *reinterpret_cast<const double2*>(A + (long)(r0 + r) * lda + c0 + c);
+            a[r][c] = v.x;
+            a[r][c + 1] = v.y;
+        }
+    if (tid == 0) piv[0] = a[0][0];
     __syncthreads();
-    const int row = tid & 127, half = tid >> 7;
 
-    // --- right-looking Cholesky, one column per step (lower triangle) ---
+    // ---- phase 1: Cholesky (lower) ----
+#pragma unroll 1
     for (int j = 0; j < P_N; j++) {
-        double d = S[j * P_LD + j];
-        if (!(d > 0.0) || isinf(d)) {           // also catches NaN
-            if (tid == 0) atomicCAS(info, 0, row_offset + j + 1);
-            d = 1.0;
+        const int bj = j >> 3, jj = j & 7;
+        if (tx == bj && ty >= bj) {                      // owners of column j
+            double d = piv[j & 1];
+            if (!(d > 0.0) || isinf(d)) {                // also catches NaN
+                if (ty == bj) atomicCAS(info, 0, row_offset + j + 1);
+                d = 1.0;
+            }
+            const double rt = sqrt(d), rinv = 1.0 / rt;
+            auto scale_col = [&](auto JJ) {
+                constexpr int Q = decltype(JJ)::value;
+#pragma unroll
+                for (int r = 0; r < 8; r++) {
+                    const int R = r0 + r;
+                    double v = a[r][Q];
+                    v = R > j ? v * rinv : (R == j ? rt : v);
+                    if (R >= j) a[r][Q] = v;
+                    col[R] = R > j ? v : 0.0;
+                }
+            };
+            P_DISPATCH8(jj, scale_col);
         }
-        const double r = sqrt(d), rinv = 1.0 / r;
-        __syncthreads();                        // pivot read by everyone before it is overwritten
-        double lij = 0.0;
-        if (row > j) {
-            lij = S[row * P_LD + j] * rinv;
-            if (half == 0) S[row * P_LD + j] = lij;
+        __syncthreads();
+        if (ty >= bj && tx >= bj && ty >= tx) {          // trailing update of the lower blocks
+            double lr[8], lc[8];
+#pragma unroll
+            for (int r = 0; r < 8; r++) lr[r] = col[r0 + r];
+#pragma unroll
+            for (int c = 0; c < 8; c++) lc[c] = col[c0 + c];
+#pragma unroll
+            for (int r = 0; r < 8; r++)
+#pragma unroll
+                for (int c = 0; c < 8; c++) a[r][c] = fma(-lr[r], lc[c], a[r][c]);   // rows/cols <= j: col == 0
+            if (ty == tx && ty == ((j + 1) >> 3)) {      // publish the next pivot
+                auto pub = [&](auto JJ) { piv[(j + 1) & 1] = a[decltype(JJ)::value][decltype(JJ)::value]; };
+                P_DISPATCH8((j + 1) & 7, pub);
+            }
         }
-        if (tid == j) S[j * P_LD + j] = r;
-        __syncthreads();                        // column j is final
-        if (row > j)
-            for (int c = j + 1 + half; c <= row; c += 2) S[row * P_LD + c] -= lij * S[c * P_LD + j];
         __syncthreads();
     }
-    // L (lower incl. diagonal) back to global; the strict upper part of the block is left untouched
-    for (int idx = tid; idx < P_N * P_N; idx += 256) {
-        const int r = idx >> 7, c = idx & 127;
-        if (c <= r) A[(long)r * lda + c] = S[r * P_LD + c];
-    }
-    for (int idx = tid; idx < P_N * P_N; idx += 256) {
-        const int r = idx >> 7, c = idx & 127;
-        if (c > r) S[r * P_LD + c] = 0.0;
-    }
+    // L (lower incl. diagonal) to shared and global memory; the strict upper part of the block stays untouched
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            const int R = r0 + r, C = c0 + c;
+            const double v = C <= R ? a[r][c] : 0.0;
+            S[R * P_LD + C] = v;
+            if (C <= R) A[(long)R * lda + C] = v;
+        }
+    // ---- phase 2: X = L^-1 ----
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+        for (int c = 0; c < 8; c++) a[r][c] = (r0 + r == c0 + c) ? 1.0 : 0.0;
     __syncthreads();
-
-    // --- in-place inverse of the lower-triangular factor (column sweep from the right, LAPACK dtrti2) ---
-    for (int j = P_N - 1; j >= 0; j--) {
-        const double ajj = 1.0 / S[j * P_LD + j];
-        double part = 0.0;
-        if (row > j)
-            for (int c = j + 1 + half; c <= row; c += 2) part = fma(S[row * P_LD + c], S[c * P_LD + j], part);
-        scratch[half * P_N + row] = part;
-        __syncthreads();                        // column j fully read; partial sums visible
-        if (half == 0) {
-            if (row > j) S[row * P_LD + j] = -ajj * (scratch[row] + scratch[P_N + row]);
-            else if (row == j) S[j * P_LD + j] = ajj;
+#pragma unroll 1
+    for (int j = 0; j < P_N; j++) {
+        const int bj = j >> 3, jj = j & 7;
+        if (ty == bj && tx <= bj) {                      // owners of row j: divide by l_jj and publish
+            const double inv = 1.0 / S[j * P_LD + j];
+            auto scale_row = [&](auto JJ) {
+                constexpr int Q = decltype(JJ)::value;
+#pragma unroll
+                for (int c = 0; c < 8; c++) {
+                    const double v = a[Q][c] * inv;
+                    a[Q][c] = v;
+                    col[c0 + c] = v;
+                }
+            };
+            P_DISPATCH8(jj, scale_row);
+        }
+        __syncthreads();
+        if (ty >= bj && tx <= bj) {
+            double lr[8], xr[8];
+#pragma unroll
+            for (int r = 0; r < 8; r++) lr[r] = (r0 + r > j) ? S[(r0 + r) * P_LD + j] : 0.0;
+#pragma unroll
+            for (int c = 0; c < 8; c++) xr[c] = col[c0 + c];
+#pragma unroll
+            for (int r = 0; r < 8; r++)
+#pragma unroll
+                for (int c = 0; c < 8; c++) a[r][c] = fma(-lr[r], xr[c], a[r][c]);
         }
         __syncthreads();
     }
-    for (int idx = tid; idx < P_N * P_N; idx += 256) {
-        const int r = idx >> 7, c = idx & 127;
-        Dinv[r * P_N + c] = S[r * P_LD + c];
-    }
+#pragma unroll
+    for (int r = 0; r < 8; r++)
+#pragma unroll
+        for (int c = 0; c < 8; c += 2)
+            *reinterpret_cast<double2*>(Dinv + (r0 + r) * P_N + c0 + c) = make_double2(a[r][c], a[r][c + 1]);
 }
 
 static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_offset, cudaStream_t st) {

@@ -840,7 +840,8 @@ int gpk_oz_var_partials(const void* Eimg, long strideE, const void* Wimg, long s
 // ---- (6+7) fused posterior mean + Jacobian + variance ----------------------------------------------------
 // One pass over the (query, training point) pairs evaluates the kernel once: it feeds the mean / Jacobian sums
 // and the int8 digit image for the tcgen05 variance contraction  var_f(z) = sf2 - || W k(X,z) ||^2.
-// mean / jac may be NULL (variance only).  Queries go through in chunks that fit `work`.
+// mean / jac may be NULL (variance only).  Queries go through in chunks that fit `work`.  mj_done_event
+// (cudaEvent_t or NULL) is recorded once mean and jac are complete.
 constexpr int OZ_SLOTS = 2 * OZ_MAX_PIECES;
 constexpr int OZ_MAX_SPLITS = 16;
 
@@ -856,7 +857,7 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
                    const double* X, long ldx, long n, long strideX, const double* alpha, long stride_alpha,
                    const void* Wimg, long strideW, const double* wscale, long stride_ws, long npad, int S,
                    void* mean, long stride_mean, void* jac, long ldj, long stride_jac, void* var, long stride_var,
-                   void* work, long work_bytes, int batch, void* stream) {
+                   void* work, long work_bytes, int batch, void* mj_done_event, void* stream) {
     GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
     GPK_ARG(Z && hyp && X && Wimg && wscale && var && work, "null pointer");
     GPK_ARG((mean == nullptr) == (jac == nullptr), "mean and jac must both be given or both be NULL");
@@ -898,6 +899,9 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
         void* jout = mj ? (char*)jac + q0 * ldj * esz : nullptr;
         if (dtype == 0) GPK_TRY(oz_front_dispatch<float>(a, S, mj, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
         else GPK_TRY(oz_front_dispatch<double>(a, S, mj, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
+        // mean and Jacobian are final here: a caller that passed an event can start copying them out while the
+        // variance contraction of the last chunk runs
+        if (mj && mj_done_event && q0 + qc >= q) GPK_CUDA(cudaEventRecord((cudaEvent_t)mj_done_event, st));
         GPK_TRY(gpk_oz_var_partials(eimg, a.strideE, Wimg, strideW, wscale, stride_ws, hyp, npad, qp, S, part, qc,
                                     (long)OZ_SLOTS * qc, pieces, batch, nullptr, stream));
         void* vout = (char*)var + q0 * esz;

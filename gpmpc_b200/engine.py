@@ -168,6 +168,13 @@ def _as_device_f64(t: torch.Tensor, device) -> torch.Tensor:
     return t.detach().to(device=device, dtype=F64).contiguous()
 
 
+def i8_supported(npad: int, digits: int | None = None) -> bool:
+    """The int32 accumulators of the tcgen05 variance path are exact while digits * npad * 2^14 < 2^31
+    (npad <= 26214 at the default 5 digits); larger training sets use the DMMA path (var_path="f64")."""
+    digits = _lib.load().gpk_oz_default_digits() if digits is None else digits
+    return digits * npad * 16384 < 2 ** 31
+
+
 def slice_w(W: torch.Tensor, npad: int, digits: int | None = None, wimg_out=None, wscale_out=None):
     """int8 digit image + power-of-two row scales of W = L^-1 (operand of the tcgen05 variance contraction)."""
     lib = _lib.load()
@@ -228,7 +235,7 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
     if want_kinv:
         call("gpk_kinv", ptr(ws.U), npad, npad, ptr(ws.need_kinv()), npad, st)
     wimg = wscale = None
-    if want_image:
+    if want_image and i8_supported(npad, digits):
         wimg, wscale, digits = slice_w(W, npad, digits, wimg_out, wscale_out)
     quad, logdet = ws.scal.tolist()
     fit = GPFit(X=X, y=y, n=n, d=d, npad=npad, center=center_h, ell=ell_t, sf2=float(sf2), noise=float(noise),
@@ -369,7 +376,8 @@ def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise, digits: int | N
     Wall = torch.empty(P, npad, npad, dtype=F64, device=dev)
     lib = _lib.load()
     digits = lib.gpk_oz_default_digits() if digits is None else digits
-    Iall = torch.empty(P, lib.gpk_oz_w_image_bytes(npad, digits), dtype=torch.int8, device=dev)
+    Iall = (torch.empty(P, lib.gpk_oz_w_image_bytes(npad, digits), dtype=torch.int8, device=dev)
+            if i8_supported(npad, digits) else [None] * P)
     ell = torch.as_tensor(ell, dtype=F64)
     fits = []
     for p in range(P):
@@ -385,7 +393,7 @@ VAR_WORK_BYTES = 4 << 30   # default scratch budget for the K_ZX chunks of the v
 
 
 def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_work_bytes: int | None = None,
-            var_path: str = "i8"):
+            var_path: str = "i8", mj_event: torch.cuda.Event | None = None):
     """Posterior mean (B,Q), latent variance var_f (B,Q) and input-Jacobian (B,Q,d) at queries Z.
 
     Z: (Q,d) shared by all GPs or (B,Q,d); float64 or float32 selects the prediction path.  The batched
@@ -413,6 +421,8 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
     var = torch.empty(B, q, dtype=dt, device=dev) if want_var else None
     if q == 0:
         return mean, var, jac
+    if var_path == "i8" and gp.wimg is None and not i8_supported(npad, gp.digits or None):
+        var_path = "f64"                     # training set too large for exact int32 accumulation
     if want_var and var_path == "i8":
         # fused front end (kernel evaluated once for mean, Jacobian and the digit image) + variance contraction
         # on the tcgen05 int8 pipe (exact digit products, fp64 recombination)
@@ -426,7 +436,7 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
         call("gpk_predict_i8", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(gp.X), gp.X.stride(1), n,
              strideX, ptr(alpha), alpha.stride(0), ptr(gp.wimg), gp.wimg.stride(0) if B > 1 else 0, ptr(gp.wscale),
              gp.wscale.stride(0) if B > 1 else 0, npad, gp.digits, ptr(mean), q, ptr(jac), d, q * d, ptr(var), q,
-             ptr(vwork), vbytes, B, st)
+             ptr(vwork), vbytes, B, mj_event.cuda_event if mj_event is not None else None, st)
         return mean, var, jac
     pack = gp.pack(dt)
     wbytes = min(lib.gpk_mean_jac_work_bytes(code, q, n, d, B), 1 << 30)

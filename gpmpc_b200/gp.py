@@ -429,19 +429,36 @@ def predict_callable(gp: GaussianProcess):
     return pred
 
 
+_copy_streams: dict = {}
+
+
 @torch.no_grad()
 def predict_host(batch, Z_host: torch.Tensor, out: tuple | None = None):
     """End-to-end prediction from HOST buffers: copies the (pinned) queries to the GPU, runs the batched
     mean + variance + Jacobian path and returns (mean, var, jac) in pinned host memory; blocks until the
-    results are on the host.  `batch` is an engine.GPBatch / GPFit or a list of fitted GaussianProcess."""
+    results are on the host.  `batch` is an engine.GPBatch / GPFit or a list of fitted GaussianProcess.
+    The mean and Jacobian (94 % of the result bytes) are copied out on a second stream while the variance
+    contraction still runs."""
     if isinstance(batch, (list, tuple)):
         batch = E.GPBatch.from_fits([gp._prediction_fit() for gp in batch])
     dev = batch.device
+    main = torch.cuda.current_stream(dev)
+    side = _copy_streams.get(dev.index)
+    if side is None:
+        side = _copy_streams[dev.index] = torch.cuda.Stream(dev)
     Zd = Z_host.to(dev, non_blocking=True)
-    res = E.predict(batch, Zd)
+    ev = torch.cuda.Event()
+    ev.record(main)                      # creates the CUDA event; re-recorded by the library when mean/jac are final
+    mean, var, jac = E.predict(batch, Zd, mj_event=ev)
     if out is None:
-        out = tuple(torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in res)
-    for o_, r in zip(out, res):
-        o_.copy_(r, non_blocking=True)
-    torch.cuda.current_stream(dev).synchronize()
+        out = tuple(torch.empty(r.shape, dtype=r.dtype, pin_memory=True) for r in (mean, var, jac))
+    with torch.cuda.stream(side):
+        side.wait_event(ev)
+        out[0].copy_(mean, non_blocking=True)
+        out[2].copy_(jac, non_blocking=True)
+    out[1].copy_(var, non_blocking=True)
+    mean.record_stream(side)
+    jac.record_stream(side)
+    main.synchronize()
+    side.synchronize()
     return out

@@ -125,7 +125,8 @@ int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq,
  *     digits = 4 / 5 / 6 keep 30 / 38 / 46 bits (5: ~2e-9 relative variance error at N = 2048).
  * gpk_oz_slice_w builds the digit image of W = L^-1 once per fit (image layout: csrc/ozaki.cuh).
  * mean / jac may both be NULL (variance only).  Scratch: gpk_predict_i8_work_bytes(q_chunk, ...); queries are
- * processed in chunks that fit the scratch given. */
+ * processed in chunks that fit the scratch given.  mj_done_event (cudaEvent_t as void*, may be NULL) is
+ * recorded on `stream` as soon as mean and jac are final, before the variance contraction of the last chunk. */
 int gpk_oz_default_digits(void);
 int gpk_oz_query_tile(void);                               /* queries per tile of the E image (128) */
 long gpk_oz_w_image_bytes(long npad, int digits);          /* -1 if unsupported */
@@ -137,7 +138,7 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
                    const double* X, long ldx, long n, long strideX, const double* alpha, long stride_alpha,
                    const void* Wimg, long strideW, const double* wscale, long stride_ws, long npad, int digits,
                    void* mean, long stride_mean, void* jac, long ldj, long stride_jac, void* var, long stride_var,
-                   void* work, long work_bytes, int batch, void* stream);
+                   void* work, long work_bytes, int batch, void* mj_done_event, void* stream);
 /* the two stages of (6+7) on their own, for tests and bench.py:
  *   gpk_oz_cross         queries -> int8 digit image of E = exp(-r^2/2), [batch][qpad/128][npad/64][digits][128x64]
  *   gpk_oz_var_partials  part[gp][slot][q], slot < 2 n_pieces: sums of (W k)_i^2 over disjoint sets of rows i;
