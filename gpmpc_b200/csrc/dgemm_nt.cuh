@@ -34,7 +34,8 @@ struct GemmParams {
     int M, N, K;
     double alpha, beta;
     int a_tri;       // 0 full, 1 lower, 2 upper
-    int c_lower;     // 1: skip tiles with tile_m < tile_n
+    int c_lower;     // 1: skip tiles entirely above the diagonal
+    int c_inplace;   // 1: C aliases A (one CTA owns all columns of its rows)
     int tiles_m, tiles_n;
     int group_m, group_n;   // super-tile for L2 reuse across the ~148 concurrently resident CTAs
     int order, nbatch;      // tile enumeration (see tile_coords)
@@ -80,50 +81,65 @@ __device__ __forceinline__ void tile_coords(const GemmParams& p, int id, int& tm
     tn = sc * p.group_n + rem2 / gm;
 }
 
-template <int EPI>
+// Tile configurations: BM x BN CTA tile, WM x WN warps, warp tile (BM/WM) x (BN/WN) = FM x FN DMMA fragments.
+//   128 x 128 (2 x 4 warps, 64 x 32 warp tiles): the throughput configuration
+//    64 x  64 (2 x 2 warps, 32 x 32): 4x the CTAs for the many small GEMMs of the recursive factorisations --
+//              one SM only sustains ~0.25 TFLOP/s of DMMA, so a GEMM with a handful of tiles is bound by that
+//    32 x 128 (1 x 4 warps, 32 x 32): for the in-place TRSM leaves (C aliases A; a CTA must own all 128
+//              columns of its rows), 4x the CTAs along M
+template <int EPI, int BM, int BN, int WM, int WN>
 __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
     extern __shared__ __align__(16) double smem[];
+    constexpr int THREADS = 32 * WM * WN;
+    constexpr int FM = BM / WM / 8, FN = BN / WN / 8;
+    constexpr int STAGE_ELEMS = (BM + BN) * G_ROW;
+    constexpr int NCH = (BM + BN) * 8 / THREADS;         // 16-byte chunks per thread per k-block
+    static_assert((BM + BN) * 8 % THREADS == 0, "chunk count must divide");
 
     int tm, tn, batch_i;
     tile_coords(p, blockIdx.x, tm, tn, batch_i);
-    if (p.c_lower && tm < tn) return;
+    if (p.c_lower && (tm + 1) * BM <= tn * BN) return;   // tile entirely above the diagonal
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const int g = lane >> 2, t = lane & 3;
-    const int wm = warp >> 2, wn = warp & 3;     // 2 x 4 warps
+    const int wm = warp / WN, wn = warp % WN;
 
     const long batch = batch_i;
-    const double* __restrict__ A = p.A + batch * p.strideA + (long)tm * G_BM * p.lda;
-    const double* __restrict__ B = p.B + batch * p.strideB + (long)tn * G_BN * p.ldb;
+    const double* __restrict__ A = p.A + batch * p.strideA + (long)tm * BM * p.lda;
+    const double* __restrict__ B = p.B + batch * p.strideB + (long)tn * BN * p.ldb;
 
     int kbeg = 0, kend = p.K;
-    if (p.a_tri == 1) kend = min(p.K, (tm + 1) * G_BM);
-    if (p.a_tri == 2) kbeg = min(p.K, tm * G_BM);
+    if (p.a_tri == 1) kend = min(p.K, (tm + 1) * BM);
+    if (p.a_tri == 2) kbeg = min(p.K, tm * BM) / G_BK * G_BK;
+    kend = (kend + G_BK - 1) / G_BK * G_BK;
     const int nk = (kend - kbeg) / G_BK;
 
-    // each thread copies 4 + 4 16-byte chunks per k-block: chunk c -> row c/8, k-chunk c%8.  The copies of
-    // one k-block are issued in 4 parts, one per k-step, so the LDGSTS never queue up in front of the
-    // fragment LDS of the compute loop (MIO is in-order).
+    // chunk c -> row c/8 of the stacked [A rows | B rows] stage, k-chunk c%8.  The copies of one k-block are
+    // issued in 4 parts, one per k-step, so the LDGSTS never queue up in front of the fragment LDS of the
+    // compute loop (MIO is in-order).
     auto load_part = [&](int stage, int kb, int part) {
-        double* As = smem + stage * G_STAGE_ELEMS;
-        double* Bs = As + G_BM * G_ROW;
+        double* As = smem + stage * STAGE_ELEMS;
         const long k0 = kbeg + (long)kb * G_BK;
-        const int c = tid + part * G_THREADS;
-        const int row = c >> 3, kc = (c & 7) * 2;
-        cp_async16(As + row * G_ROW + kc, A + (long)row * p.lda + k0 + kc);
-        cp_async16(Bs + row * G_ROW + kc, B + (long)row * p.ldb + k0 + kc);
+#pragma unroll
+        for (int i = 0; i < NCH; i++) {
+            if ((i & 3) != part) continue;
+            const int c = tid + i * THREADS;
+            const int row = c >> 3, kc = (c & 7) * 2;
+            const double* src = row < BM ? A + (long)row * p.lda + k0 + kc : B + (long)(row - BM) * p.ldb + k0 + kc;
+            cp_async16(As + row * G_ROW + kc, src);
+        }
     };
     auto load_stage = [&](int stage, int kb) {
 #pragma unroll
         for (int i = 0; i < 4; i++) load_part(stage, kb, i);
     };
 
-    double acc[8][4][2];
+    double acc[FM][FN][2];
 #pragma unroll
-    for (int i = 0; i < 8; i++)
+    for (int i = 0; i < FM; i++)
 #pragma unroll
-        for (int j = 0; j < 4; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
+        for (int j = 0; j < FN; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
 
 #pragma unroll
     for (int s = 0; s < G_STAGES - 1; s++) {
@@ -131,8 +147,8 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
         cp_async_commit();
     }
 
-    const int a_off = (wm * 64 + g) * G_ROW + t;
-    const int b_off = G_BM * G_ROW + (wn * 32 + g) * G_ROW + t;
+    const int a_off = (wm * (BM / WM) + g) * G_ROW + t;
+    const int b_off = BM * G_ROW + (wn * (BN / WN) + g) * G_ROW + t;
 
     for (int kb = 0; kb < nk; kb++) {
         cp_async_wait<G_STAGES - 2>();
@@ -141,32 +157,33 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
         const int nxt = kb + G_STAGES - 1;
         const bool refill = nxt < nk;
         const int nstage = nxt % G_STAGES;
-        const double* st = smem + (kb % G_STAGES) * G_STAGE_ELEMS;
+        const double* st = smem + (kb % G_STAGES) * STAGE_ELEMS;
 #pragma unroll
         for (int ks = 0; ks < G_BK / 4; ks++) {
-            double a[8], b[4];
+            double a[FM], b[FN];
 #pragma unroll
-            for (int f = 0; f < 8; f++) a[f] = st[a_off + f * 8 * G_ROW + ks * 4];
+            for (int f = 0; f < FM; f++) a[f] = st[a_off + f * 8 * G_ROW + ks * 4];
 #pragma unroll
-            for (int f = 0; f < 4; f++) b[f] = st[b_off + f * 8 * G_ROW + ks * 4];
+            for (int f = 0; f < FN; f++) b[f] = st[b_off + f * 8 * G_ROW + ks * 4];
             if (refill) load_part(nstage, nxt, ks);
 #pragma unroll
-            for (int i = 0; i < 8; i++)
+            for (int i = 0; i < FM; i++)
 #pragma unroll
-                for (int j = 0; j < 4; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                for (int j = 0; j < FN; j++) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
         }
         cp_async_commit();
     }
     cp_async_wait<0>();
 
     if constexpr (EPI == 0) {
-        double* __restrict__ C = p.C + batch * p.strideC + ((long)tm * G_BM + wm * 64 + g) * p.ldc +
-                                 (long)tn * G_BN + wn * 32 + 2 * t;
+        if (p.c_inplace) __syncthreads();                // every warp has read its A rows before C (= A) is written
+        double* __restrict__ C = p.C + batch * p.strideC + ((long)tm * BM + wm * (BM / WM) + g) * p.ldc +
+                                 (long)tn * BN + wn * (BN / WN) + 2 * t;
         const double alpha = p.alpha, beta = p.beta;
 #pragma unroll
-        for (int i = 0; i < 8; i++)
+        for (int i = 0; i < FM; i++)
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
+            for (int j = 0; j < FN; j++) {
                 double2* ptr = reinterpret_cast<double2*>(C + (long)i * 8 * p.ldc + j * 8);
                 double2 v;
                 v.x = alpha * acc[i][j][0];
@@ -179,15 +196,16 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
                 *ptr = v;
             }
     } else {
+        static_assert(EPI == 0 || (BM == 128 && BN == 128 && WM == 2 && WN == 4), "column-norm epilogue: 128 x 128 only");
         // column sums of squares over the 128 rows of this tile
         __syncthreads();                       // all warps are done with the pipeline smem
         double* red = smem;                    // [2 (wm)][128 columns]
         const double alpha2 = p.alpha * p.alpha;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
+        for (int j = 0; j < FN; j++) {
             double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
+            for (int i = 0; i < FM; i++) {
                 s0 = fma(acc[i][j][0], acc[i][j][0], s0);
                 s1 = fma(acc[i][j][1], acc[i][j][1], s1);
             }
@@ -198,22 +216,24 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
                 s1 += __shfl_xor_sync(0xffffffffu, s1, o);
             }
             if (g == 0) {
-                red[wm * G_BN + wn * 32 + j * 8 + 2 * t] = s0;
-                red[wm * G_BN + wn * 32 + j * 8 + 2 * t + 1] = s1;
+                red[wm * BN + wn * 32 + j * 8 + 2 * t] = s0;
+                red[wm * BN + wn * 32 + j * 8 + 2 * t + 1] = s1;
             }
         }
         __syncthreads();
-        if (tid < G_BN) {
-            double* out = p.colsq + batch * p.stride_colsq + (long)tm * p.ld_colsq + (long)tn * G_BN;
-            out[tid] = alpha2 * (red[tid] + red[G_BN + tid]);
+        if (tid < BN) {
+            double* out = p.colsq + batch * p.stride_colsq + (long)tm * p.ld_colsq + (long)tn * BN;
+            out[tid] = alpha2 * (red[tid] + red[BN + tid]);
         }
     }
 }
 
 // EPI 0: C = beta C + alpha A B^T (potrf / trtri / K^-1 building block)
-__global__ void __launch_bounds__(G_THREADS, 1) dgemm_nt_kernel(const GemmParams p) { dgemm_nt_body<0>(p); }
-// EPI 1: posterior-variance contraction, column sums of squares of W K_ZX^T (the dominant predict kernel)
-__global__ void __launch_bounds__(G_THREADS, 1) var_colsq_kernel(const GemmParams p) { dgemm_nt_body<1>(p); }
+__global__ void __launch_bounds__(G_THREADS, 1) dgemm_nt_kernel(const GemmParams p) { dgemm_nt_body<0, 128, 128, 2, 4>(p); }
+__global__ void __launch_bounds__(128, 2) dgemm_nt64_kernel(const GemmParams p) { dgemm_nt_body<0, 64, 64, 2, 2>(p); }
+__global__ void __launch_bounds__(128, 2) dgemm_nt32x128_kernel(const GemmParams p) { dgemm_nt_body<0, 32, 128, 1, 4>(p); }
+// EPI 1: posterior-variance contraction, column sums of squares of W K_ZX^T (DMMA variance path)
+__global__ void __launch_bounds__(G_THREADS, 1) var_colsq_kernel(const GemmParams p) { dgemm_nt_body<1, 128, 128, 2, 4>(p); }
 
 // host-side launcher (defined in linalg.cu)
 int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st);

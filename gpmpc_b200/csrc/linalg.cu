@@ -35,11 +35,20 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
     GPK_ARG(((uintptr_t)p.A % 16) == 0 && ((uintptr_t)p.B % 16) == 0, "A/B must be 16-byte aligned");
     if (epilogue == 0) GPK_ARG(p.ldc % 2 == 0 && ((uintptr_t)p.C % 16) == 0, "C must be 16-byte aligned with even ldc");
     if (epilogue == 1) GPK_ARG(p.colsq != nullptr, "colsq output missing");
-    p.tiles_m = p.M / G_BM;
-    p.tiles_n = p.N / G_BN;
     p.nbatch = batch;
+    p.c_inplace = (epilogue == 0 && p.C == p.A) ? 1 : 0;
+    // tile configuration: the 128 x 128 tiles need ~one wave of CTAs to pay off (see dgemm_nt.cuh)
+    const long tiles128 = (long)(p.M / G_BM) * (p.N / G_BN) * batch / (p.c_lower ? 2 : 1);
+    int bm = G_BM, bn = G_BN;
+    if (epilogue == 0 && tiles128 < 100) {
+        if (p.c_inplace) { bm = 32; bn = 128; }
+        else { bm = 64; bn = 64; }
+    }
+    GPK_ARG(!p.c_inplace || p.N == bn, "in-place GEMM needs a single tile column");
+    p.tiles_m = p.M / bm;
+    p.tiles_n = p.N / bn;
     dim3 grid((unsigned)(p.tiles_m * p.tiles_n), 1, (unsigned)batch);
-    if (p.a_tri == 1 && !p.c_lower) {
+    if (epilogue == 1 && p.a_tri == 1 && !p.c_lower) {
         // LPT order inside L2-sized column chunks (B panel of one column tile = 128 x K doubles)
         p.order = 1;
         const long panel = (long)G_BN * p.K * 8;
@@ -54,18 +63,23 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
         p.group_m = p.tiles_m <= 18 ? p.tiles_m : 12;
         p.group_n = 148 / p.group_m > 0 ? 148 / p.group_m : 1;
     }
-    static bool attr_done[2] = {false, false};
-    if (!attr_done[epilogue]) {
-        if (epilogue == 0)
-            GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
-        else
-            GPK_CUDA(cudaFuncSetAttribute(var_colsq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
-        attr_done[epilogue] = true;
+    static bool attr_done = false;
+    if (!attr_done) {
+        GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+        GPK_CUDA(cudaFuncSetAttribute(var_colsq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+        GPK_CUDA(cudaFuncSetAttribute(dgemm_nt64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+        GPK_CUDA(cudaFuncSetAttribute(dgemm_nt32x128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+        attr_done = true;
     }
-    if (epilogue == 0)
-        dgemm_nt_kernel<<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
+    const int smem = G_STAGES * (bm + bn) * G_ROW * 8;
+    if (epilogue == 1)
+        var_colsq_kernel<<<grid, G_THREADS, smem, st>>>(p);
+    else if (bm == 128)
+        dgemm_nt_kernel<<<grid, G_THREADS, smem, st>>>(p);
+    else if (bm == 64)
+        dgemm_nt64_kernel<<<grid, 128, smem, st>>>(p);
     else
-        var_colsq_kernel<<<grid, G_THREADS, G_SMEM_BYTES, st>>>(p);
+        dgemm_nt32x128_kernel<<<grid, 128, smem, st>>>(p);
     GPK_LAUNCHED();
     return 0;
 }
