@@ -111,7 +111,7 @@ constexpr int P_N = 128, P_LD = 129;
         case 6: f(std::integral_constant<int, 6>{}); break;                       \
         default: f(std::integral_constant<int, 7>{}); break;                      \
     }
-constexpr int P_SMEM = (P_N * P_LD + 3 * P_N) * 8;
+constexpr int P_SMEM = (P_N * P_LD + 4 * P_N) * 8;
 
 // 256 threads as a 16 x 16 grid; thread (ty, tx) keeps the 8 x 8 block rows 8ty.., columns 8tx.. in REGISTERS.
 // Both phases are right-looking with two barriers per column and 64 FMAs per thread in between:
@@ -124,6 +124,7 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
     extern __shared__ __align__(16) double S[];          // L, row-major with leading dimension P_LD
     double* col = S + P_N * P_LD;                        // published column j of L / row j of X
     double* piv = col + P_N;                             // next pivot (double-buffered by column parity)
+    double* dinv = piv + P_N;                            // 1 / l_jj, reused by phase 2
     const int tid = threadIdx.x;
     const int ty = tid >> 4, tx = tid & 15;
     const int r0 = ty * 8, c0 = tx * 8;
@@ -149,7 +150,12 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
                 if (ty == bj) atomicCAS(info, 0, row_offset + j + 1);
                 d = 1.0;
             }
-            const double rt = sqrt(d), rinv = 1.0 / rt;
+            // 1/sqrt(d) (MUFU seed + Newton, ~1 ulp) and l_jj = d / sqrt(d) with one correction step: no
+            // sqrt followed by a division on the critical path of every column
+            const double rinv = rsqrt(d);
+            double rt = d * rinv;
+            rt = fma(fma(-rt, rt, d), 0.5 * rinv, rt);
+            if (ty == bj) dinv[j] = rinv;
             auto scale_col = [&](auto JJ) {
                 constexpr int Q = decltype(JJ)::value;
 #pragma unroll
@@ -201,7 +207,7 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
     for (int j = 0; j < P_N; j++) {
         const int bj = j >> 3, jj = j & 7;
         if (ty == bj && tx <= bj) {                      // owners of row j: divide by l_jj and publish
-            const double inv = 1.0 / S[j * P_LD + j];
+            const double inv = dinv[j];
             auto scale_row = [&](auto JJ) {
                 constexpr int Q = decltype(JJ)::value;
 #pragma unroll
