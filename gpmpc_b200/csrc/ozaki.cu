@@ -10,6 +10,7 @@
 //   oz_var_kernel<S>      persistent, warp-specialised: 1-D bulk-TMA producer warp, one-thread tcgen05.mma
 //                         issuer, 4 epilogue warps (TMEM -> fp64 Horner recombination -> column sums of squares)
 #include "ozaki.cuh"
+#include <cmath>
 #include <cstdlib>
 #include <type_traits>
 
@@ -123,31 +124,25 @@ __device__ __forceinline__ void oz_pack_digits4(const double (&e)[4], uint32_t (
     }
 }
 
-// exp(a) for a <= 0 to ~2^-51 relative error, branch-free: Cody-Waite reduction by ln 2, the degree-12 Taylor
-// polynomial on |r| <= ln2/2, and 2^n added straight into the exponent field (normal results down to
-// a = -708; below that the result is 0, where the library exp is subnormal or 0).
-__device__ __forceinline__ double oz_exp_neg(double a0) {
+// exp(a) for a <= 0 to ~2^-51 relative error, branch-free, 10 FP64 operations: a log2(e) 1024 = m + f with
+// m = 1024 n + j, so exp(a) = 2^n * T[j] * exp(r), T[j] = 2^(j/1024) from a shared-memory table, r = a - m ln2/1024
+// (Cody-Waite, |r| <= 3.4e-4) and a degree-4 polynomial; 2^n goes straight into the exponent field (normal
+// results down to a = -708; below that the result is 0, where the library exp is subnormal or 0).
+constexpr int OZ_EXP_TAB = 1024;
+__device__ __forceinline__ double oz_exp_neg(double a0, const double* __restrict__ tab) {
     const double a = fmax(a0, -708.0);
     const double MAGIC = 6755399441055744.0;             // 1.5 * 2^52
-    const double tn = fma(a, 1.4426950408889634074, MAGIC);
-    const double nd = tn - MAGIC;
-    double r = fma(nd, -6.93147180369123816490e-01, a);  // ln2 hi
-    r = fma(nd, -1.90821492927058770002e-10, r);         // ln2 lo
-    double p = 2.08767569878680989792e-09;               // 1/12!
-    p = fma(p, r, 2.50521083854417187751e-08);
-    p = fma(p, r, 2.75573192239858906526e-07);
-    p = fma(p, r, 2.75573192239858906526e-06);
-    p = fma(p, r, 2.48015873015873015873e-05);
-    p = fma(p, r, 1.98412698412698412698e-04);
-    p = fma(p, r, 1.38888888888888888889e-03);
-    p = fma(p, r, 8.33333333333333333333e-03);
-    p = fma(p, r, 4.16666666666666666667e-02);
-    p = fma(p, r, 1.66666666666666666667e-01);
+    const double tm = fma(a, 1477.3197218702985, MAGIC); // 1024 / ln 2
+    const double md = tm - MAGIC;
+    double r = fma(md, -0.0006769015433292225, a);  // ln2/1024 hi (32 significant bits: exact products)
+    r = fma(md, -1.8634911418658083e-13, r);            // ln2/1024 lo
+    double p = fma(r, 4.16666666666666666667e-02, 1.66666666666666666667e-01);
     p = fma(p, r, 0.5);
     p = fma(p, r, 1.0);
     p = fma(p, r, 1.0);
-    const int n = __double2loint(tn);                     // integer part of tn sits in the low mantissa word
-    const double e = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+    const int m = __double2loint(tm);                     // integer part of tm sits in the low mantissa word
+    p *= tab[m & (OZ_EXP_TAB - 1)];
+    const double e = __hiloint2double(__double2hiint(p) + ((m >> 10) << 20), __double2loint(p));
     return a0 < -708.0 ? 0.0 : e;
 }
 
@@ -160,6 +155,7 @@ struct OzFrontArgs {
     int8_t* img; long strideE;               // digit image of E, [gp][qtile][kb][S][128 x 64]
     int kb_total, kb_per_cta;
     double* mj_part; long stride_mj;         // [gp][split][q][DP + 1] partial (m, S_j)
+    const double* exp_tab;                   // 2^(j/1024), j < 1024 (device, built once per process)
 };
 
 __device__ __forceinline__ void oz_dmma(double (&c)[2], double a, double b) {
@@ -183,12 +179,14 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
     __shared__ __align__(16) double XsA[OZ_BK * LDA];    // rows in fragment-column order (see above)
     __shared__ __align__(16) double XsB[MJ ? OZ_BK * LDB : 1];   // rows in natural order
     __shared__ __align__(16) double ex[OZ_BK], as[OZ_BK];
+    __shared__ double exp_tab[OZ_EXP_TAB];
     const long gp = blockIdx.z;
     const int qt = blockIdx.y;
     const double* hyp = a.hyp + gp * HYP_STRIDE;
     const TZ* Z = reinterpret_cast<const TZ*>(a.Z) + gp * a.strideZ;
     const double* X = a.X + gp * a.strideX;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < OZ_EXP_TAB; i += 256) exp_tab[i] = a.exp_tab[i];   // visible after the first barrier below
     const int g = lane >> 2, t = lane & 3;
 
     // A fragments of GEMM 1 (scaled queries) for the two 8-query blocks of this warp
@@ -292,7 +290,7 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
                 }
                 double e[4];
 #pragma unroll
-                for (int i = 0; i < 4; i++) e[i] = qv[mb] ? oz_exp_neg(fmin(c[i >> 1][i & 1], 0.0)) : 0.0;
+                for (int i = 0; i < 4; i++) e[i] = qv[mb] ? oz_exp_neg(fmin(c[i >> 1][i & 1], 0.0), exp_tab) : 0.0;
                 uint32_t w[S];
                 oz_pack_digits4<S>(e, w);
                 int8_t* dst = out + oz_tile_off(qrow[mb], unit * 16 + 4 * t);
@@ -670,6 +668,24 @@ static int oz_sm_count() {
     return sms;
 }
 
+// 2^(j/1024) table of the front kernel's exp: computed once per device on the host in long double, rounded to double
+static const double* oz_exp_table(cudaStream_t st) {
+    static double* dev_tab[64] = {nullptr};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return nullptr;
+    if (!dev_tab[dev]) {
+        static double host_tab[OZ_EXP_TAB];
+        for (int j = 0; j < OZ_EXP_TAB; j++) host_tab[j] = (double)exp2l((long double)j / OZ_EXP_TAB);
+        double* p = nullptr;
+        if (cudaMalloc(&p, sizeof(host_tab)) != cudaSuccess) return nullptr;
+        if (cudaMemcpyAsync(p, host_tab, sizeof(host_tab), cudaMemcpyHostToDevice, st) != cudaSuccess) return nullptr;
+        cudaStreamSynchronize(st);
+        dev_tab[dev] = p;
+    }
+    return dev_tab[dev];
+}
+
 static int oz_pad_dim(int d) { return d <= 4 ? 4 : d <= 8 ? 8 : d <= 16 ? 16 : 32; }
 
 // pieces per query tile: the count (<= 8, <= number of W row-block pairs) that wastes the least in the last
@@ -736,8 +752,11 @@ static int oz_launch_front(const OzFrontArgs& a, int n_split, long qtiles, int b
 }
 
 template <typename TZ>
-static int oz_front_dispatch(const OzFrontArgs& a, int S, bool mj, int n_split, long qtiles, int batch, void* mean,
+static int oz_front_dispatch(const OzFrontArgs& a_in, int S, bool mj, int n_split, long qtiles, int batch, void* mean,
                              long stride_mean, void* jac, long ldj, long stride_jac, cudaStream_t st) {
+    OzFrontArgs a = a_in;
+    a.exp_tab = oz_exp_table(st);
+    GPK_ARG(a.exp_tab != nullptr, "could not allocate the exp table");
 #define OZ_F(SV) \
     if (S == SV) return mj ? oz_launch_front<TZ, SV, true>(a, n_split, qtiles, batch, (TZ*)mean, stride_mean, (TZ*)jac, ldj, stride_jac, st) \
                            : oz_launch_front<TZ, SV, false>(a, n_split, qtiles, batch, nullptr, 0, nullptr, 0, 0, st);
