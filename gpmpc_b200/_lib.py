@@ -53,6 +53,7 @@ SIGNATURES = {
     "gpk_oz_var_partials": (_i, [_p, _l, _p, _l, _p, _l, _p, _l, _l, _i, _p, _l, _l, _i, _i, _p, _p]),
     "gpk_oz_query_tile": (_i, []),
     "gpk_oz_pieces": (_i, [_l, _l]),
+    "gpk_tighten_constraints": (_i, [_p, _l, _i, _p, _l, _i, _i, _p, _p, _p, _p, _p, _i, _i, _i, _l, _d, _d, _p, _p, _p]),
 }
 
 _lib = None

@@ -318,7 +318,7 @@ class GPBatch:
         assert all(f.n == f0.n and f.d == f0.d and f.device == f0.device for f in fits), "GPs must share (N, d, device)"
         has_img = all(f.wimg is not None and f.digits == f0.digits for f in fits)
         if len(fits) == 1:
-            return cls(fits, f0.X[None], f0.W[None], f0.hyp[None], f0.wimg[None] if has_img else None,
+            return cls(fits, f0.X[None], f0.W[None] if f0.W is not None else None, f0.hyp[None], f0.wimg[None] if has_img else None,
                        f0.wscale[None] if has_img else None, f0.digits if has_img else 0)
         # W tensors allocated by fit_batch are already slices of one (B, npad, npad) buffer
         base = fits[0].W._base if fits[0].W._base is not None else None

@@ -150,6 +150,24 @@ int gpk_oz_var_partials(const void* Eimg, long strideE, const void* Wimg, long s
                         long stride_ws, const double* hyp, long npad, long qpad, int digits, double* part,
                         long ld_part, long stride_part, int n_pieces, int batch, int* dbg, void* stream);
 
+/* ---- (f2) chance-constraint tightening, batched over rollouts ------------------------------------
+ * Replaces GPMPC.propagate_constraint_limits (gpmpc/gpmpc.py:425-498) for `rollouts` independent rollouts of T
+ * stages: stage disturbance covariance from the three GPs' variances and the roll / pitch angles of the stage
+ * input z (gpmpc.py:447-470), the LQR-closed-loop covariance recursion (gpmpc.py:478-495) and the limits
+ * -inverse_cdf |A| sqrt(diag cov) for A = [-I; I] (gpmpc.py:472-476, 487-488, 497).
+ *   var   [3][rollouts*T] (GP g at var + g*stride_var): latent var_f as gpk_predict_i8 returns it
+ *         (var_has_noise = 0; the likelihood noise of hyp is added twice, as gpmpc.py:444 + 485 do) or the
+ *         predictive variance gp.likelihood(gp(z)) (var_has_noise = 1; noise added once more)
+ *   Z     [rollouts*T][ldz] stage inputs; only columns idx_phi, idx_theta are read (6, 7 in gpmpc.py:449)
+ *   hyp   3 hyper-parameter blocks;  A (nx x nx), B (nx x nu), K (nu x nx), Bd (nx x 5) row-major:
+ *         discrete_dfdx, discrete_dfdu, lqr_gain, Bd of gpmpc.py:69, 84
+ *   state_constraint [rollouts][2 nx][T+1], input_constraint [rollouts][2 nu][T]  (the reference's arrays per
+ *         rollout).  nx <= 16, nu <= min(8, nx).  A variance rounded below zero gives 0, not NaN. */
+int gpk_tighten_constraints(const double* var, long stride_var, int var_has_noise, const double* Z, long ldz,
+                            int idx_phi, int idx_theta, const double* hyp, const double* A, const double* B,
+                            const double* K, const double* Bd, int nx, int nu, int T, long rollouts, double dt,
+                            double inverse_cdf, double* state_constraint, double* input_constraint, void* stream);
+
 /* ---- building block exposed for tests ---------------------------------------------------------
  * C = beta C + alpha A B^T on the FP64 DMMA pipe; M, N multiples of 128, K of 16.
  * a_tri: 0 full, 1 A lower triangular, 2 A upper triangular; c_lower: only tiles on/below the diagonal. */

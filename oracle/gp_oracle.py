@@ -277,6 +277,45 @@ def fitc_posterior_mean(X, y, S, ell, sf2, noise):
 
 
 # ----------------------------------------------------------------------------------------------
+# chance-constraint tightening (restates gpmpc/gpmpc.py:425-498)
+# PINNED: tests/golden/tighten_*.npz hold outputs of the reference's own GPMPC.propagate_constraint_limits
+# executed here (tests/golden/make_golden_mpc.py loads gpmpc/gpmpc.py with its absent third-party imports
+# stubbed and feeds it GP objects that return prescribed variances); tests/test_oracle.py checks this
+# restatement against them.
+# ----------------------------------------------------------------------------------------------
+def propagate_constraint_limits(var_y, z, noise, dfdx, dfdu, lqr_gain, Bd, dt, inverse_cdf, idx_phi=6, idx_theta=7):
+    """One rollout.  var_y (3, T): predictive variances diag(gp.likelihood(gp(z)).covariance_matrix) of the
+    thrust / roll / pitch GPs [gpmpc.py:441-445]; z (T, >= 8) stage inputs; noise (3,) likelihood noises.
+    Returns state_constraint (2 nx, T+1), input_constraint (2 nu, T)."""
+    var_y = np.asarray(var_y, dtype=np.float64)
+    z = np.asarray(z, dtype=np.float64)
+    T = z.shape[0]
+    nx, nu = dfdx.shape[0], dfdu.shape[1]
+    state_constraint = np.zeros((2 * nx, T + 1))
+    input_constraint = np.zeros((2 * nu, T))
+    cps2 = np.cos(z[:, idx_phi]) * np.sin(z[:, idx_theta]) ** 2                 # [gpmpc.py:448-450]
+    sp2 = (-np.sin(z[:, idx_phi])) ** 2
+    cpct2 = (np.cos(z[:, idx_phi]) * np.cos(z[:, idx_theta])) ** 2
+    fac = np.stack([cps2, sp2, cpct2, np.ones(T), np.ones(T)], axis=1)          # (T, 5)
+    gp_of = [0, 0, 0, 1, 2]
+    cov_d = np.stack([var_y[g] for g in gp_of], axis=1) * fac * dt**2           # [gpmpc.py:452-457, 469]
+    cov_n = np.stack([np.full(T, float(noise[g])) for g in gp_of], axis=1) * fac * dt**2   # [gpmpc.py:459-468]
+    absA_x = np.abs(np.concatenate([-np.eye(nx), np.eye(nx)], axis=0))          # [gpmpc.py:472-476]
+    absA_u = np.abs(np.concatenate([-np.eye(nu), np.eye(nu)], axis=0))
+    cov_x = np.zeros((nx, nx))                                                  # [gpmpc.py:436]
+    for i in range(T):                                                          # [gpmpc.py:478-495]
+        cov_xu = cov_x @ lqr_gain.T
+        cov_u = lqr_gain @ cov_x @ lqr_gain.T
+        cd = np.diag(cov_d[i] + cov_n[i])
+        state_constraint[:, i] = -inverse_cdf * absA_x @ np.sqrt(np.diag(cov_x))
+        input_constraint[:, i] = -inverse_cdf * absA_u @ np.sqrt(np.diag(cov_u))
+        cov_x = (dfdx @ cov_x @ dfdx.T + dfdx @ cov_xu @ dfdu.T + dfdu @ cov_xu.T @ dfdx.T
+                 + dfdu @ cov_u @ dfdu.T + Bd @ cd @ Bd.T)
+    state_constraint[:, -1] = -inverse_cdf * absA_x @ np.sqrt(np.diag(cov_x))   # [gpmpc.py:497]
+    return state_constraint, input_constraint
+
+
+# ----------------------------------------------------------------------------------------------
 # synthetic data recipe shared by tests and bench (SURVEY.md 8d)
 # ----------------------------------------------------------------------------------------------
 def synthetic_problem(n: int, d: int, q: int, p: int = 1, seed: int = 1337):

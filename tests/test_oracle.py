@@ -169,7 +169,7 @@ def test_fitc_reduces_to_exact_when_all_points_are_inducing():
 def test_golden_fixtures_reproduce():
     """tests/golden/*.npz were written by tests/golden/make_golden.py from this oracle; a change in the
     oracle's arithmetic shows up here."""
-    files = sorted(f for f in os.listdir(GOLD) if f.endswith(".npz"))
+    files = sorted(f for f in os.listdir(GOLD) if f.endswith(".npz") and f.startswith(("ref_", "syn_")))
     assert files, "no golden fixtures committed"
     for f in files:
         g = np.load(os.path.join(GOLD, f))
@@ -185,3 +185,40 @@ def test_golden_fixtures_reproduce():
         loss, gn, gs, gl = o.loss_and_grad(X, y, g["raw_noise"], g["raw_sf2"], g["raw_ell"])
         assert abs(float(loss) - float(g["loss_raw"])) < 1e-11 * abs(float(g["loss_raw"])), f
         assert o.rel_err(gl, g["g_raw_ell"]) < 1e-8 and o.rel_err(gn, g["g_raw_noise"]) < 1e-8, f
+
+
+# ---- MPC-side rows: fixtures written by the reference's own methods (make_golden_mpc.py) ------
+@pytest.mark.parametrize("name", ["tighten_T25", "tighten_T40"])
+def test_tightening_restatement_matches_reference_output(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    for r in range(g["x_prev"].shape[0]):
+        z = np.hstack((g["x_prev"][r][:, :-1].T, g["u_prev"][r].T))          # gpmpc/gpmpc.py:437
+        sc, ic = o.propagate_constraint_limits(g["var_y"][r], z, g["noise"], g["dfdx"], g["dfdu"], g["lqr_gain"],
+                                               g["Bd"], float(g["dt"]), float(g["inverse_cdf"]))
+        assert sc.shape == g["state_constraint"][r].shape and ic.shape == g["input_constraint"][r].shape
+        assert o.rel_err(sc, g["state_constraint"][r]) < 1e-12
+        assert o.rel_err(ic, g["input_constraint"][r]) < 1e-12
+        assert np.all(sc[:, 0] == 0.0) and np.all(sc <= 0.0)                  # cov_x starts at 0; limits only tighten
+
+
+@pytest.mark.parametrize("name", ["tighten_T25", "tighten_T40"])
+def test_tightening_fixture_variances_come_from_the_gp_oracle(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    gp_idx = [[0], [1, 2, 3], [4, 5, 6]]
+    z = torch.tensor(np.hstack((g["x_prev"][0][:, :-1].T, g["u_prev"][0].T)))
+    for k, idx in enumerate(gp_idx):
+        X, y, ell = (torch.tensor(g[f"gp{k}_{f}"]) for f in ("X", "y", "ell"))
+        st = o.fit_state(X, y, ell, float(g[f"gp{k}_sf2"]), float(g["noise"][k]))
+        _, var, _ = o.predict(z[:, idx], X, ell, float(g[f"gp{k}_sf2"]), st["L"], st["alpha"])
+        assert o.rel_err(var + float(g["noise"][k]), g["var_y"][0][k]) < 1e-12
+
+
+@pytest.mark.parametrize("name", ["fitc_n45_m10", "fitc_n200_m25"])
+def test_fitc_restatement_matches_reference_output(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    gp_idx = [[0], [1, 2, 3], [4, 5, 6]]
+    S = torch.tensor(g["sparse_inputs"])
+    for k, idx in enumerate(gp_idx):
+        X, y, ell = (torch.tensor(g[f"gp{k}_{f}"]) for f in ("X", "y", "ell"))
+        w = o.fitc_posterior_mean(X, y, S[:, idx], ell, float(g[f"gp{k}_sf2"]), float(g["noise"][k]))
+        assert o.rel_err(w, g["posterior_mean"][k]) < 1e-9
