@@ -333,10 +333,27 @@ def measure_roofline(gb, Z, flush, dev, steps):
     return {"kernel": f"oz_var_kernel<{S}> (variance contraction W K_ZX^T, {S}-digit int8 slices on tcgen05, int32 TMEM "
                       "accumulators, fp64 recombination)",
             "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TOP/s (int8)", "frac": achieved / peak,
-            "traffic": None, "ms_per_launch": ms, "algorithmic_int8_ops_per_launch": int8_ops,
+            "traffic": ncu_dram_bytes("ncu_oz_var_kernel_S5_r01_v3.csv") if S == 5 else None,
+            "traffic_unit": "bytes per launch (dram read + write, ncu --set full, profiles/ncu_oz_var_kernel_S5_r01_v3.csv)",
+            "algorithmic_bytes_per_launch": float(B) * S * npad * (qp + npad),
+            "ms_per_launch": ms, "algorithmic_int8_ops_per_launch": int8_ops,
             "fp64_equivalent_tflops": fp64_flops / (ms * 1e-3) / 1e12, "fp64_dmma_peak_tflops": DMMA_PEAK_TFLOPS,
             "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops (burst, of measured)" if bf16 else
                             "2 x 1590 TFLOP/s bf16 (of fallback)") + "; nominal int8 dense 4500 TOP/s"}
+
+
+def ncu_dram_bytes(name):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the committed ncu capture profiles/<name> (same workload), or None."""
+    try:
+        tot = 0.0
+        with open(os.path.join(ROOT, "profiles", name)) as f:
+            for line in f:
+                k = line.split(",")
+                if k[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    tot += float(k[2]) * {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}[k[1]]
+        return tot or None
+    except (OSError, KeyError, ValueError, IndexError):
+        return None
 
 
 def measure_extras(gb, problem, Z, flush, dev):
