@@ -53,6 +53,8 @@ SIGNATURES = {
     "gpk_oz_var_partials": (_i, [_p, _l, _p, _l, _p, _l, _p, _l, _l, _i, _p, _l, _l, _i, _i, _p, _p]),
     "gpk_oz_query_tile": (_i, []),
     "gpk_oz_pieces": (_i, [_l, _l]),
+    "gpk_stage_rk4_work_bytes": (_l, [_l, _l, _i]),
+    "gpk_stage_rk4": (_i, [_p, _l, _p, _l, _l, _p, _i, _d, _p, _p, _l, _l, _p, _p, _p, _p, _l, _p]),
     "gpk_tighten_constraints": (_i, [_p, _l, _i, _p, _l, _i, _i, _p, _p, _p, _p, _p, _i, _i, _i, _l, _d, _d, _p, _p, _p]),
 }
 

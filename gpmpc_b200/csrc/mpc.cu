@@ -16,6 +16,11 @@
 // off the recursion's critical path.
 #include "common.cuh"
 
+extern "C" long gpk_mean_jac_work_bytes(int dtype, long q, long n, int d, int batch);
+extern "C" int gpk_predict_mean_jac(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                                    const void* pack, long stride_pack, long n, void* mean, long stride_mean, void* jac,
+                                    long ldj, long stride_jac, void* work, long work_bytes, int batch, void* stream);
+
 namespace gpk {
 
 constexpr int TC_ND = 5;        // uncertain directions: dx, dy, dz from the thrust GP, dphi, dtheta (gpmpc.py:68)
@@ -237,6 +242,157 @@ static int launch_tighten(const TightenArgs& a, cudaStream_t st) {
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Batched discrete stage dynamics with sensitivities: what acados evaluates per stage for the
+// model built by GPMPC.setup_acados_model (gpmpc/gpmpc.py:166-224),
+//   f_cont(x, u) = prior(x, u) + res_dyn(x, u),    res_dyn = (0, T c(phi) s(theta), 0, -T s(phi), 0, T c(phi) c(theta),
+//                  0, 0, 0, R, P, 0)                                                          [gpmpc.py:193-199]
+//   T, R, P      = GP means at z[idx_T] = (u0), z[idx_R] = (phi, dphi, u1), z[idx_P] = (theta, dtheta, u2)   [172, 187-191]
+//   f_disc       = x + dt/6 (k1 + 2 k2 + 2 k3 + k4), classical RK4 of f_cont with u held                  [201-206]
+// together with A = d f_disc / dx and B = d f_disc / du (CasADi AD inside acados), for q independent (x, u) pairs.
+// The prior is the attitude model the reference takes from crazyflow.sim.symbolic.symbolic_attitude (absent here;
+// restated from its use at gpmpc.py:128-146 and the parameter names of scripts/gp_mpc_config.yaml:9-17):
+//   acc = a u0 + b along the same rotation column as res_dyn, minus g on z;  ddphi = c phi + d dphi + e u1;
+//   ddtheta = f theta + h dtheta + l u2;  ddpsi = yc psi + yd dpsi + ye u3 (zero unless given).
+// Each of the four RK4 sub-steps is one launch of gpk_predict_mean_jac for the three GPs (the GP sums dominate) and
+// one launch of stage_step_kernel: sixteen threads per pair, thread c carrying column c of d k_s / d(x, u).
+// ------------------------------------------------------------------------------------------------------------
+constexpr int ST_NX = 12, ST_NU = 4, ST_NC = ST_NX + ST_NU, ST_GD = 3;
+enum { PR_A = 0, PR_B, PR_C, PR_D, PR_E, PR_F, PR_H, PR_L, PR_G, PR_YC, PR_YD, PR_YE, PR_COUNT };
+
+struct StageArgs {
+    const double* x; long ldx;      // [q][12]
+    const double* u; long ldu;      // [q][4]
+    long q;
+    double prior[PR_COUNT];
+    double dt;
+    const double* xs_in;            // [q][12]  sub-state of the current sub-step
+    double* xs_out;                 // [q][12]  sub-state of the next one (ping-pong: no intra-warp ordering needed)
+    double* Zg;                     // [3][q][3] GP queries of the current sub-step
+    const double* mean;             // [3][q]
+    const double* jac;              // [3][q][3]
+    double* D;                      // [q][12][16] d k_s / d(x, u) of the previous sub-step
+    double* Acc;                    // [q][12][16] weighted sum of the d k_s / d(x, u)
+    double* ksum;                   // [q][12] weighted sum of the k_s
+    double* x_next; double* A; double* B;
+};
+
+// S = 0: set up sub-step 1 (xs = x, GP queries).  S = 1..4: consume the GP output at xs_S, accumulate k_S and its
+// sensitivities, then prepare sub-step S + 1 or, for S = 4, write x_next, A, B.
+template <int S>
+__global__ void __launch_bounds__(256) stage_step_kernel(StageArgs a) {
+    const long gi = (long)blockIdx.x * 16 + (threadIdx.x >> 4);
+    const int c = threadIdx.x & 15;
+    if (gi >= a.q) return;
+    const double* x = a.x + gi * a.ldx;
+    const double* u = a.u + gi * a.ldu;
+    const long q = a.q;
+    if constexpr (S == 0) {
+        if (c < ST_NX) a.xs_out[gi * ST_NX + c] = x[c];
+        if (c < 9) {
+            // GP g, column j: T (u0, 0, 0); R (phi, dphi, u1); P (theta, dtheta, u2)
+            const int g = c / 3, j = c % 3;
+            double v = 0.0;
+            if (g == 0) v = j == 0 ? u[0] : 0.0;
+            else if (j == 2) v = u[g];
+            else v = x[(g == 1 ? 6 : 7) + 3 * j];
+            a.Zg[((long)g * q + gi) * ST_GD + j] = v;
+        }
+        return;
+    } else {
+        constexpr double cs_cur = S == 1 ? 0.0 : S == 4 ? 1.0 : 0.5;       // xs_S = x + cs_cur dt k_{S-1}
+        constexpr double cs_next = S == 3 ? 1.0 : 0.5;
+        constexpr double w = (S == 1 || S == 4) ? 1.0 : 2.0;
+        const double* xs = a.xs_in + gi * ST_NX;
+        const double* P_ = a.prior;
+        const double phi = xs[6], th = xs[7];
+        double sp, cp, st, ct;
+        sincos(phi, &sp, &cp);
+        sincos(th, &st, &ct);
+        const double mT = a.mean[gi], mR = a.mean[q + gi], mP = a.mean[2 * q + gi];
+        const double* jT = a.jac + gi * ST_GD;
+        const double* jR = a.jac + (q + gi) * ST_GD;
+        const double* jP = a.jac + (2 * q + gi) * ST_GD;
+        const double Tt = fma(P_[PR_A], u[0], P_[PR_B]) + mT;             // prior thrust acceleration + GP residual
+        const double dTt = P_[PR_A] + jT[0];
+
+        // column c of G = d xs_S / d(x, u) = [I | 0] + cs_cur dt D_{S-1}
+        double g[ST_NX];
+        double* Dq = a.D + gi * ST_NX * ST_NC;
+        double* Aq = a.Acc + gi * ST_NX * ST_NC;
+#pragma unroll
+        for (int r = 0; r < ST_NX; r++) {
+            double v = (r == c) ? 1.0 : 0.0;
+            if constexpr (S > 1) v = fma(cs_cur * a.dt, Dq[r * ST_NC + c], v);
+            g[r] = v;
+        }
+        // column c of D_S = F_x G + F_u, with the sparse F_x, F_u of the model above
+        double d[ST_NX];
+        d[0] = g[1]; d[2] = g[3]; d[4] = g[5]; d[6] = g[9]; d[7] = g[10]; d[8] = g[11];
+        d[1] = fma(-Tt * sp * st, g[6], (Tt * cp * ct) * g[7]);
+        d[3] = (-Tt * cp) * g[6];
+        d[5] = fma(-Tt * sp * ct, g[6], (-Tt * cp * st) * g[7]);
+        d[9] = fma(P_[PR_C] + jR[0], g[6], (P_[PR_D] + jR[1]) * g[9]);
+        d[10] = fma(P_[PR_F] + jP[0], g[7], (P_[PR_H] + jP[1]) * g[10]);
+        d[11] = fma(P_[PR_YC], g[8], P_[PR_YD] * g[11]);
+        if (c == ST_NX) { d[1] += dTt * cp * st; d[3] -= dTt * sp; d[5] += dTt * cp * ct; }
+        if (c == ST_NX + 1) d[9] += P_[PR_E] + jR[2];
+        if (c == ST_NX + 2) d[10] += P_[PR_L] + jP[2];
+        if (c == ST_NX + 3) d[11] += P_[PR_YE];
+#pragma unroll
+        for (int r = 0; r < ST_NX; r++) {
+            double acc = w * d[r];
+            if constexpr (S > 1) acc += Aq[r * ST_NC + c];
+            if constexpr (S < 4) {
+                Dq[r * ST_NC + c] = d[r];
+                Aq[r * ST_NC + c] = acc;
+            } else {
+                const double v = a.dt / 6.0 * acc;
+                if (c < ST_NX) a.A[(gi * ST_NX + r) * ST_NX + c] = (r == c ? 1.0 : 0.0) + v;
+                else a.B[(gi * ST_NX + r) * ST_NU + (c - ST_NX)] = v;
+            }
+        }
+        if (c < ST_NX) {
+            // component c of k_S = f_cont(xs_S, u)
+            double k;
+            switch (c) {
+                case 0: k = xs[1]; break;
+                case 1: k = Tt * cp * st; break;
+                case 2: k = xs[3]; break;
+                case 3: k = -Tt * sp; break;
+                case 4: k = xs[5]; break;
+                case 5: k = Tt * cp * ct - P_[PR_G]; break;
+                case 6: k = xs[9]; break;
+                case 7: k = xs[10]; break;
+                case 8: k = xs[11]; break;
+                case 9: k = fma(P_[PR_C], phi, fma(P_[PR_D], xs[9], P_[PR_E] * u[1])) + mR; break;
+                case 10: k = fma(P_[PR_F], th, fma(P_[PR_H], xs[10], P_[PR_L] * u[2])) + mP; break;
+                default: k = fma(P_[PR_YC], xs[8], fma(P_[PR_YD], xs[11], P_[PR_YE] * u[3])); break;
+            }
+            double ks = w * k;
+            if constexpr (S > 1) ks += a.ksum[gi * ST_NX + c];
+            if constexpr (S < 4) {
+                a.ksum[gi * ST_NX + c] = ks;
+                const double xn = fma(cs_next * a.dt, k, x[c]);
+                a.xs_out[gi * ST_NX + c] = xn;
+                if (c == 6) a.Zg[((long)1 * q + gi) * ST_GD + 0] = xn;
+                if (c == 9) a.Zg[((long)1 * q + gi) * ST_GD + 1] = xn;
+                if (c == 7) a.Zg[((long)2 * q + gi) * ST_GD + 0] = xn;
+                if (c == 10) a.Zg[((long)2 * q + gi) * ST_GD + 1] = xn;
+            } else {
+                a.x_next[gi * ST_NX + c] = fma(a.dt / 6.0, ks, x[c]);
+            }
+        }
+    }
+}
+
+template <int S>
+static int launch_stage_step(const StageArgs& a, cudaStream_t st) {
+    stage_step_kernel<S><<<(unsigned)((a.q + 15) / 16), 256, 0, st>>>(a);
+    GPK_LAUNCHED();
+    return 0;
+}
+
 }  // namespace gpk
 
 using namespace gpk;
@@ -260,4 +416,63 @@ extern "C" int gpk_tighten_constraints(const double* var, long stride_var, int v
     if (nx <= 8) return launch_tighten<2>(a, st);
     if (nx <= 12) return launch_tighten<3>(a, st);
     return launch_tighten<4>(a, st);
+}
+
+extern "C" long gpk_stage_rk4_work_bytes(long q_chunk, long n, int batch_unused) {
+    (void)batch_unused;
+    if (q_chunk <= 0 || n <= 0) return -1;
+    const long per_q = (2 * ST_NX + 3 * ST_GD + 3 + 3 * ST_GD + 2 * ST_NX * ST_NC + ST_NX) * (long)sizeof(double);
+    long mj = gpk_mean_jac_work_bytes(1, q_chunk, n, ST_GD, 3);
+    if (mj < 0) mj = 0;
+    return per_q * q_chunk + mj + 256;
+}
+
+extern "C" int gpk_stage_rk4(const double* x, long ldx, const double* u, long ldu, long q, const double* prior,
+                             int n_prior, double dt, const double* hyp, const void* pack, long stride_pack, long n,
+                             double* x_next, double* A, double* B, void* work, long work_bytes, void* stream) {
+    GPK_ARG(q >= 0 && ldx >= ST_NX && ldu >= ST_NU, "q / ldx / ldu");
+    if (q == 0) return 0;
+    GPK_ARG(x && u && prior && hyp && pack && x_next && A && B && work, "null pointer");
+    GPK_ARG(n_prior >= PR_G + 1 && n_prior <= PR_COUNT, "prior holds a, b, c, d, e, f, h, l, g [, yaw c, d, e]");
+    GPK_ARG(n > 0, "n");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // largest query chunk the scratch holds
+    long qc = q;
+    while (qc > 1 && gpk_stage_rk4_work_bytes(qc, n, 3) > work_bytes) qc = (qc + 1) / 2;
+    GPK_ARG(gpk_stage_rk4_work_bytes(qc, n, 3) <= work_bytes, "scratch too small for one query");
+    StageArgs a{};
+    for (int i = 0; i < PR_COUNT; i++) a.prior[i] = i < n_prior ? prior[i] : 0.0;
+    a.dt = dt; a.ldx = ldx; a.ldu = ldu;
+    double* w = static_cast<double*>(work);
+    double* xs0 = w;               w += qc * ST_NX;
+    double* xs1 = w;               w += qc * ST_NX;
+    double* Zg = w;                w += 3 * qc * ST_GD;
+    double* mean = w;              w += 3 * qc;
+    double* jac = w;               w += 3 * qc * ST_GD;
+    double* D = w;                 w += qc * ST_NX * ST_NC;
+    double* Acc = w;               w += qc * ST_NX * ST_NC;
+    double* ksum = w;              w += qc * ST_NX;
+    void* mj_work = reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(w) + 255) & ~uintptr_t(255));
+    const long mj_bytes = work_bytes - (static_cast<char*>(mj_work) - static_cast<char*>(work));
+    for (long q0 = 0; q0 < q; q0 += qc) {
+        const long qn = q - q0 < qc ? q - q0 : qc;
+        a.x = x + q0 * ldx; a.u = u + q0 * ldu; a.q = qn;
+        a.Zg = Zg; a.mean = mean; a.jac = jac; a.D = D; a.Acc = Acc; a.ksum = ksum;
+        a.x_next = x_next + q0 * ST_NX; a.A = A + q0 * ST_NX * ST_NX; a.B = B + q0 * ST_NX * ST_NU;
+        a.xs_in = xs1; a.xs_out = xs0;
+        GPK_TRY(launch_stage_step<0>(a, st));
+        for (int s = 1; s <= 4; s++) {
+            GPK_TRY(gpk_predict_mean_jac(1, Zg, ST_GD, qn, qn * ST_GD, ST_GD, hyp, pack, stride_pack, n, mean, qn, jac,
+                                         ST_GD, qn * ST_GD, mj_bytes > 0 ? mj_work : nullptr, mj_bytes > 0 ? mj_bytes : 0, 3, st));
+            a.xs_in = (s & 1) ? xs0 : xs1;
+            a.xs_out = (s & 1) ? xs1 : xs0;
+            switch (s) {
+                case 1: GPK_TRY(launch_stage_step<1>(a, st)); break;
+                case 2: GPK_TRY(launch_stage_step<2>(a, st)); break;
+                case 3: GPK_TRY(launch_stage_step<3>(a, st)); break;
+                default: GPK_TRY(launch_stage_step<4>(a, st)); break;
+            }
+        }
+    }
+    return 0;
 }

@@ -21,7 +21,7 @@ from ._lib import call, ptr
 F64 = torch.float64
 
 
-def stack_padded(gps: list, digits: int | None = None) -> tuple[E.GPBatch, int]:
+def stack_padded(gps: list, digits: int | None = None, dpad: int | None = None) -> tuple[E.GPBatch, int]:
     """One GPBatch from GPs with the same N but different input dimension (the reference's thrust / roll / pitch
     GPs have d = 1, 3, 3: gpmpc/gpmpc.py:59): inputs are padded with zero columns, which leaves every kernel
     value unchanged.  Elements are GaussianProcess objects or (X, y, ell, sf2, noise) tuples.  Returns
@@ -35,7 +35,7 @@ def stack_padded(gps: list, digits: int | None = None) -> tuple[E.GPBatch, int]:
             ell, sf2, noise = gp.hyperparameters()
             X, y = gp.train_inputs[0], gp.train_targets
         raw.append((X if X.dim() == 2 else X[:, None], y, ell, float(sf2), float(noise)))
-    dmax = max(X.shape[1] for X, *_ in raw)
+    dmax = max(max(X.shape[1] for X, *_ in raw), dpad or 0)
     fits = []
     for X, y, ell, sf2, noise in raw:
         dev = _lib.require_cuda(X.device if X.is_cuda else None)
@@ -206,3 +206,84 @@ def sparse_gp(gp, S: torch.Tensor, w: torch.Tensor) -> E.GPFit:
     alpha[:m] = torch.as_tensor(w, dtype=F64).to(dev)
     return E.GPFit(X=S, y=None, n=m, d=fx.d, npad=mp, center=fx.center, ell=fx.ell, sf2=fx.sf2, noise=fx.noise,
                    hyp=fx.hyp, W=None, alpha=alpha)
+
+
+# --------------------------------------------------------------------------------------------------
+# batched discrete stage dynamics of the acados model (gpmpc/gpmpc.py:166-209)
+# --------------------------------------------------------------------------------------------------
+PRIOR_KEYS = ("a", "b", "c", "d", "e", "f", "h", "l")     # scripts/gp_mpc_config.yaml:9-17
+
+
+class StageDynamics:
+    """f_disc and its Jacobians for batches of (x, u): the `disc_dyn_expr` GPMPC.setup_acados_model hands to acados
+    (gpmpc/gpmpc.py:166-209), evaluated on the GPU for every stage of every rollout at once.
+
+    gps: the thrust / roll / pitch GPs as GaussianProcess objects, (X, y, ell, sf2, noise) tuples, or engine.GPFit
+    objects with d <= 3 (e.g. mpc.sparse_gp(...) for the FITC model, gpmpc.py:175-186); prior_params: dict with the
+    keys a..l of the config (or a sequence a, b, c, d, e, f, h, l[, g, yaw c, d, e]); dt: the control period."""
+
+    def __init__(self, gps: list, prior_params, dt: float, g: float = 9.81):
+        assert len(gps) == 3, "thrust, roll and pitch GPs"
+        if all(isinstance(f, E.GPFit) for f in gps):
+            fits = [self._pad_fit(f) for f in gps]
+        else:
+            fits = stack_padded(gps, dpad=3)[0].fits
+        assert all(f.n == fits[0].n for f in fits), "the three GPs share the number of (inducing) points"
+        self.fits = fits
+        dev = fits[0].device
+        self.device = dev
+        self.n = fits[0].n
+        self.pack = torch.stack([f.pack(F64) for f in fits])
+        self.hyp = torch.stack([f.hyp for f in fits])
+        if isinstance(prior_params, dict):
+            p = [float(prior_params[k]) for k in PRIOR_KEYS] + [float(g)]
+            p += [float(prior_params.get(k, 0.0)) for k in ("yaw_c", "yaw_d", "yaw_e")]
+        else:
+            p = [float(v) for v in prior_params]
+            if len(p) == 8:
+                p.append(float(g))
+        self.prior = torch.tensor(p, dtype=F64)
+        self.dt = float(dt)
+
+    @staticmethod
+    def _pad_fit(f: E.GPFit) -> E.GPFit:
+        if f.d == 3:
+            return f
+        assert f.d < 3
+        X = torch.zeros(f.n, 3, dtype=F64, device=f.device)
+        X[:, : f.d] = f.X
+        ell = torch.ones(3, dtype=F64)
+        ell[: f.d] = f.ell
+        center = torch.zeros(3, dtype=F64)
+        center[: f.d] = f.center
+        return E.GPFit(X=X, y=f.y, n=f.n, d=3, npad=f.npad, center=center, ell=ell, sf2=f.sf2, noise=f.noise,
+                       hyp=E.make_hyp(center, ell, f.sf2, f.noise, 3, f.device), W=None, alpha=f.alpha)
+
+    @torch.no_grad()
+    def disc_dyn(self, x, u, work_bytes: int = 2 << 30):
+        """x (Q, 12), u (Q, 4) -> x_next (Q, 12), A (Q, 12, 12), B (Q, 12, 4); numpy in, numpy out; torch in, device
+        tensors out."""
+        as_numpy = isinstance(x, np.ndarray)
+        dev = self.device
+        x = torch.as_tensor(x, dtype=F64).to(dev).contiguous()
+        u = torch.as_tensor(u, dtype=F64).to(dev).contiguous()
+        single = x.dim() == 1
+        if single:
+            x, u = x[None], u[None]
+        q = x.shape[0]
+        assert x.shape == (q, 12) and u.shape == (q, 4), "x (Q, 12), u (Q, 4)"
+        xn = torch.empty(q, 12, dtype=F64, device=dev)
+        A = torch.empty(q, 12, 12, dtype=F64, device=dev)
+        B = torch.empty(q, 12, 4, dtype=F64, device=dev)
+        lib = _lib.load()
+        need = lib.gpk_stage_rk4_work_bytes(max(q, 1), self.n, 3)
+        wbytes = max(min(need, work_bytes), lib.gpk_stage_rk4_work_bytes(1, self.n, 3))
+        work = E.get_work("stage_rk4", wbytes, dev)
+        call("gpk_stage_rk4", ptr(x), x.stride(0), ptr(u), u.stride(0), q, self.prior.data_ptr(),
+             self.prior.numel(), self.dt, ptr(self.hyp), ptr(self.pack), self.pack.stride(0),
+             self.n, ptr(xn), ptr(A), ptr(B), ptr(work), wbytes, _lib.stream_ptr(dev))
+        if single:
+            xn, A, B = xn[0], A[0], B[0]
+        if as_numpy:
+            return xn.cpu().numpy(), A.cpu().numpy(), B.cpu().numpy()
+        return xn, A, B

@@ -168,6 +168,24 @@ int gpk_tighten_constraints(const double* var, long stride_var, int var_has_nois
                             const double* K, const double* Bd, int nx, int nu, int T, long rollouts, double dt,
                             double inverse_cdf, double* state_constraint, double* input_constraint, void* stream);
 
+/* ---- (f1) batched discrete stage dynamics with sensitivities -----------------------------------------
+ * For q independent (x, u) pairs: x_next = f_disc(x, u), A = d f_disc/dx (12 x 12), B = d f_disc/du (12 x 4) of the
+ * acados model GPMPC.setup_acados_model builds (gpmpc/gpmpc.py:166-209): classical RK4 (gpmpc.py:201-206) of
+ * f_cont = prior + res_dyn (gpmpc.py:193-199) with the thrust / roll / pitch GP means at z[idx_T], z[idx_R], z[idx_P]
+ * (gpmpc.py:172, 187-191).  What acados evaluates per stage and SQP iteration, batched over stages and rollouts.
+ *   x [q][ldx >= 12], u [q][ldu >= 4] row-major (state order x, dx, y, dy, z, dz, phi, theta, psi, dphi, dtheta, dpsi)
+ *   prior[n_prior] (HOST memory): a, b, c, d, e, f, h, l (scripts/gp_mpc_config.yaml:9-17), g [, yaw c, d, e]: the attitude model
+ *         of crazyflow.sim.symbolic.symbolic_attitude as the reference uses it (gpmpc.py:128-146); 9 <= n_prior <= 12
+ *   hyp, pack: three GPs (thrust, roll, pitch) with inputs padded to d = 3 (zero columns for the thrust GP) and the
+ *         same n; pack from gpk_pack_train in float64, GP g at pack + g*stride_pack elements.  For the FITC model
+ *         (gpmpc.py:175-186) pack the inducing inputs with the weights of precompute_sparse_posterior_mean.
+ *   x_next [q][12], A [q][12][12], B [q][12][4];  work: gpk_stage_rk4_work_bytes(q_chunk, n, 3) bytes, pairs are
+ *         processed in chunks that fit. */
+long gpk_stage_rk4_work_bytes(long q_chunk, long n, int batch);
+int gpk_stage_rk4(const double* x, long ldx, const double* u, long ldu, long q, const double* prior, int n_prior,
+                  double dt, const double* hyp, const void* pack, long stride_pack, long n, double* x_next,
+                  double* A, double* B, void* work, long work_bytes, void* stream);
+
 /* ---- building block exposed for tests ---------------------------------------------------------
  * C = beta C + alpha A B^T on the FP64 DMMA pipe; M, N multiples of 128, K of 16.
  * a_tri: 0 full, 1 A lower triangular, 2 A upper triangular; c_lower: only tiles on/below the diagonal. */

@@ -316,6 +316,62 @@ def propagate_constraint_limits(var_y, z, noise, dfdx, dfdu, lqr_gain, Bd, dt, i
 
 
 # ----------------------------------------------------------------------------------------------
+# discrete stage dynamics of the acados model (restates gpmpc/gpmpc.py:166-209)
+# PARITY UNPINNED for the prior: `prior_dynamics` is crazyflow.sim.symbolic.symbolic_attitude(...).fc_func
+# (scripts/run_gp_mpc.py:146; crazyflow ^0.0.1, pyproject.toml:11), a third-party package that is absent here.
+# It is restated from how the reference uses it -- acc_prior(thrust) = a T + b along the body z axis with the
+# rotation column of gpmpc.py:194-196, attitude rates c phi + d dphi + e cmd etc. (gpmpc.py:128-146,
+# scripts/gp_mpc_config.yaml:9-17).  The GP residual, its placement and the RK4 are the reference's own lines.
+# Jacobians come from torch autograd here (CasADi AD in the reference).
+# ----------------------------------------------------------------------------------------------
+def attitude_prior_dynamics(x, u, p):
+    """p = (a, b, c, d, e, f, h, l, g[, yaw c, d, e]); x (12,) = (x, dx, y, dy, z, dz, phi, theta, psi, dphi, dtheta,
+    dpsi); u (4,) = (thrust, roll, pitch, yaw commands)."""
+    p = list(p) + [0.0] * (12 - len(p))
+    a, b, c, d, e, f, h, l, g, yc, yd, ye = p
+    acc = a * u[0] + b
+    cp, sp, ct, st = torch.cos(x[6]), torch.sin(x[6]), torch.cos(x[7]), torch.sin(x[7])
+    return torch.stack([
+        x[1], acc * cp * st, x[3], acc * (-sp), x[5], acc * cp * ct - g, x[9], x[10], x[11],
+        c * x[6] + d * x[9] + e * u[1], f * x[7] + h * x[10] + l * u[2], yc * x[8] + yd * x[11] + ye * u[3]])
+
+
+def gp_mean_fn(X, ell, sf2, alpha):
+    """z -> k(z, X) alpha as a differentiable torch expression (gpmpc/gp.py:85)."""
+    return lambda z: (se_kernel(z.reshape(1, -1), X, ell, sf2) @ alpha).reshape(())
+
+
+def stage_f_disc(x, u, prior, gp_means, dt):
+    """One RK4 step of f_cont = prior + res_dyn [gpmpc.py:172-206]; gp_means = (T, R, P) mean functions."""
+    nx = 12
+    zero = torch.zeros((), dtype=x.dtype)
+
+    def f_cont(xx):
+        z = torch.cat([xx, u])
+        T_pred = gp_means[0](z[[0 + nx]])                                  # idx_T  [gpmpc.py:172]
+        R_pred = gp_means[1](z[[6, 9, 1 + nx]])                            # idx_R
+        P_pred = gp_means[2](z[[7, 10, 2 + nx]])                           # idx_P
+        ax = T_pred * (torch.cos(xx[6]) * torch.sin(xx[7]))               # [gpmpc.py:194-196]
+        ay = T_pred * (-torch.sin(xx[6]))
+        az = T_pred * (torch.cos(xx[6]) * torch.cos(xx[7]))
+        res = torch.stack([zero, ax, zero, ay, zero, az, zero, zero, zero, R_pred, P_pred, zero])   # [197]
+        return attitude_prior_dynamics(xx, u, prior) + res                # [199]
+
+    k1 = f_cont(x)                                                         # [gpmpc.py:202-206]
+    k2 = f_cont(x + dt / 2 * k1)
+    k3 = f_cont(x + dt / 2 * k2)
+    k4 = f_cont(x + dt * k3)
+    return x + dt / 6 * (k1 + 2 * k2 + 2 * k3 + k4)
+
+
+def stage_linearisation(x, u, prior, gp_means, dt):
+    """(f_disc, A = d f_disc/dx, B = d f_disc/du) for one (x, u)."""
+    fx = stage_f_disc(x, u, prior, gp_means, dt)
+    A, B = torch.autograd.functional.jacobian(lambda xx, uu: stage_f_disc(xx, uu, prior, gp_means, dt), (x, u))
+    return fx, A, B
+
+
+# ----------------------------------------------------------------------------------------------
 # synthetic data recipe shared by tests and bench (SURVEY.md 8d)
 # ----------------------------------------------------------------------------------------------
 def synthetic_problem(n: int, d: int, q: int, p: int = 1, seed: int = 1337):

@@ -164,3 +164,90 @@ def test_precompute_sparse_posterior_mean_surface():
     for k, (X, y, ell, sf2, noise) in enumerate(_gps(g)):
         ell32, sf32, n32 = gps[k].hyperparameters()
         assert o.rel_err(alpha[k], o.fit_state(X, y, ell32, sf32, n32)["alpha"]) < 1e-9
+
+
+# ---- batched stage dynamics -------------------------------------------------------------
+PRIOR = dict(a=12.1432, b=1.8118, c=-72.08, d=-7.5755, e=39.8653, f=-72.08, h=-7.5755, l=39.8653)   # config yaml:9-17
+
+
+def _stage_reference(gps, x, u, prior_list, dt):
+    means = []
+    for X, y, ell, sf2, noise in gps:
+        st = o.fit_state(X, y, ell, sf2, noise)
+        means.append(o.gp_mean_fn(X, ell, sf2, st["alpha"]))
+    out = [o.stage_linearisation(x[i], u[i], prior_list, means, dt) for i in range(x.shape[0])]
+    return (torch.stack([t[k] for t in out]) for k in range(3))
+
+
+@pytest.mark.parametrize("name,dt", [("tighten_T25", 1.0 / 50.0), ("tighten_T40", 1.0 / 60.0)])
+def test_stage_dynamics_match_oracle(name, dt):
+    from gpmpc_b200.mpc import StageDynamics
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    gps = _gps(g)
+    sd = StageDynamics(gps, PRIOR, dt)
+    gen = torch.Generator().manual_seed(3)
+    Q = 19
+    x = (torch.rand(Q, 12, generator=gen, dtype=torch.float64) - 0.5) * 0.8
+    u = (torch.rand(Q, 4, generator=gen, dtype=torch.float64) - 0.3) * 0.6
+    prior_list = [PRIOR[k] for k in "abcdefhl"] + [9.81]
+    xr, Ar, Br = _stage_reference(gps, x, u, prior_list, dt)
+    xn, A, B = sd.disc_dyn(x.cuda(), u.cuda())
+    assert xn.is_cuda and A.shape == (Q, 12, 12) and B.shape == (Q, 12, 4)
+    assert o.rel_err(xn.cpu(), xr) < 1e-12
+    assert o.rel_err(A.cpu(), Ar) < 1e-11 and o.rel_err(B.cpu(), Br) < 1e-11
+    # the GP residual matters in these numbers: without it the step differs visibly
+    x0, *_ = _stage_reference([(X, torch.zeros_like(y), ell, sf2, noise) for X, y, ell, sf2, noise in gps], x, u, prior_list, dt)
+    assert o.rel_err(x0, xr) > 1e-6
+    # numpy in, numpy out, single pair; small scratch forces the chunk loop
+    x1, A1, B1 = sd.disc_dyn(x[3].numpy(), u[3].numpy())
+    assert isinstance(A1, np.ndarray) and np.array_equal(x1, xn[3].cpu().numpy())
+    from gpmpc_b200 import _lib
+    small = _lib.load().gpk_stage_rk4_work_bytes(4, sd.n, 3)
+    xs, As, Bs = sd.disc_dyn(x.cuda(), u.cuda(), work_bytes=small)
+    assert torch.equal(xs, xn) and torch.equal(As, A) and torch.equal(Bs, B)
+
+
+def test_stage_dynamics_yaw_terms_and_larger_training_set():
+    from gpmpc_b200.mpc import StageDynamics
+    gen = torch.Generator().manual_seed(9)
+    n = 700
+    gps = []
+    for k, d in enumerate((1, 3, 3)):
+        X = torch.rand(n, d, generator=gen, dtype=torch.float64) - 0.5
+        y = 0.3 * torch.sin(4.0 * X.sum(dim=1)) + 0.01 * torch.randn(n, generator=gen, dtype=torch.float64)
+        gps.append((X, y, torch.full((d,), 0.3 + 0.1 * k, dtype=torch.float64), 0.5, 1e-3))
+    prior_list = [PRIOR[k] for k in "abcdefhl"] + [9.81, -3.0, -1.5, 2.0]
+    sd = StageDynamics(gps, prior_list, 0.02)
+    Q = 7
+    x = (torch.rand(Q, 12, generator=gen, dtype=torch.float64) - 0.5)
+    u = (torch.rand(Q, 4, generator=gen, dtype=torch.float64) - 0.5)
+    xr, Ar, Br = _stage_reference(gps, x, u, prior_list, 0.02)
+    xn, A, B = sd.disc_dyn(x.numpy(), u.numpy())
+    assert o.rel_err(xn, xr) < 1e-12 and o.rel_err(A, Ar) < 1e-10 and o.rel_err(B, Br) < 1e-10
+    assert np.abs(A[:, 11, 8] - 0.02 * -3.0).max() < 1e-2                         # the yaw row is live
+
+
+def test_stage_dynamics_fitc_model():
+    """The sparse model of gpmpc.py:175-186: inducing inputs + FITC weights in place of (X, alpha)."""
+    from gpmpc_b200 import GaussianProcess
+    from gpmpc_b200 import engine as E
+    from gpmpc_b200.mpc import StageDynamics, sparse_gp
+    g = np.load(os.path.join(GOLD, "fitc_n45_m10.npz"))
+    S = torch.tensor(g["sparse_inputs"])
+    fits, means = [], []
+    for k, (X, y, ell, sf2, noise) in enumerate(_gps(g)):
+        gp = GaussianProcess(X, y)
+        gp._pred_fit, _ = E.factorize(X, y, ell, sf2, noise)
+        w = torch.tensor(g["posterior_mean"][k])
+        fits.append(sparse_gp(gp, S[:, GP_IDX[k]], w))
+        means.append(o.gp_mean_fn(S[:, GP_IDX[k]], ell, sf2, w))
+    prior_list = [PRIOR[k] for k in "abcdefhl"] + [9.81]
+    sd = StageDynamics(fits, PRIOR, 0.02)
+    gen = torch.Generator().manual_seed(4)
+    x = (torch.rand(5, 12, generator=gen, dtype=torch.float64) - 0.5) * 0.6
+    u = (torch.rand(5, 4, generator=gen, dtype=torch.float64) - 0.3) * 0.5
+    out = [o.stage_linearisation(x[i], u[i], prior_list, means, 0.02) for i in range(5)]
+    xn, A, B = sd.disc_dyn(x.numpy(), u.numpy())
+    assert o.rel_err(xn, torch.stack([t[0] for t in out])) < 1e-12
+    assert o.rel_err(A, torch.stack([t[1] for t in out])) < 1e-11
+    assert o.rel_err(B, torch.stack([t[2] for t in out])) < 1e-11

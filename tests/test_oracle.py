@@ -222,3 +222,37 @@ def test_fitc_restatement_matches_reference_output(name):
         X, y, ell = (torch.tensor(g[f"gp{k}_{f}"]) for f in ("X", "y", "ell"))
         w = o.fitc_posterior_mean(X, y, S[:, idx], ell, float(g[f"gp{k}_sf2"]), float(g["noise"][k]))
         assert o.rel_err(w, g["posterior_mean"][k]) < 1e-9
+
+
+def test_stage_linearisation_matches_finite_differences_and_plain_rk4():
+    """The stage-dynamics restatement (gpmpc/gpmpc.py:193-206): autograd Jacobians against central differences, and
+    with zero GP residual the step is classical RK4 of the prior alone."""
+    gen = torch.Generator().manual_seed(0)
+    prior = [12.1432, 1.8118, -72.08, -7.5755, 39.8653, -72.08, -7.5755, 39.8653, 9.81]
+    means = []
+    for d in (1, 3, 3):
+        X = torch.rand(20, d, generator=gen, dtype=torch.float64) - 0.5
+        alpha = torch.randn(20, generator=gen, dtype=torch.float64)
+        means.append(o.gp_mean_fn(X, torch.full((d,), 0.4, dtype=torch.float64), 0.7, alpha))
+    x = (torch.rand(12, generator=gen, dtype=torch.float64) - 0.5) * 0.6
+    u = (torch.rand(4, generator=gen, dtype=torch.float64) - 0.5) * 0.6
+    dt = 0.02
+    fx, A, B = o.stage_linearisation(x, u, prior, means, dt)
+    h = 1e-6
+    for j in range(12):
+        e = torch.zeros(12, dtype=torch.float64)
+        e[j] = h
+        fd = (o.stage_f_disc(x + e, u, prior, means, dt) - o.stage_f_disc(x - e, u, prior, means, dt)) / (2 * h)
+        assert float((fd - A[:, j]).abs().max()) < 1e-7
+    for j in range(4):
+        e = torch.zeros(4, dtype=torch.float64)
+        e[j] = h
+        fd = (o.stage_f_disc(x, u + e, prior, means, dt) - o.stage_f_disc(x, u - e, prior, means, dt)) / (2 * h)
+        assert float((fd - B[:, j]).abs().max()) < 1e-7
+    zero = [lambda z: torch.zeros((), dtype=torch.float64)] * 3
+    f = lambda xx: o.attitude_prior_dynamics(xx, u, prior)   # noqa: E731
+    k1 = f(x); k2 = f(x + dt / 2 * k1); k3 = f(x + dt / 2 * k2); k4 = f(x + dt * k3)   # noqa: E702
+    assert torch.equal(o.stage_f_disc(x, u, prior, zero, dt), x + dt / 6 * (k1 + 2 * k2 + 2 * k3 + k4))
+    # hover: thrust command (g - b) / a keeps the vertical acceleration at zero
+    xh, uh = torch.zeros(12, dtype=torch.float64), torch.tensor([(9.81 - prior[1]) / prior[0], 0, 0, 0], dtype=torch.float64)
+    assert float(o.stage_f_disc(xh, uh, prior, zero, dt).abs().max()) < 1e-15
