@@ -392,6 +392,53 @@ def measure_extras(gb, problem, Z, flush, dev):
         mll_iter()
     torch.cuda.synchronize(dev)
     out["mll_grad_iters_per_s_n2048"] = 5 / (time.perf_counter() - t0)
+    out.update(measure_mpc_rows(gb, problem, flush, dev))
+    return out
+
+
+def measure_mpc_rows(gb, problem, flush, dev):
+    """The MPC-side rows of SURVEY.md 8(f) on the bench GPs' training set size: batched RK4 stage dynamics with
+    sensitivities (4 x [3-GP mean+Jacobian + stage kernel]) and the chance-constraint recursion, for 2048 rollouts of
+    32 stages (65536 stage evaluations)."""
+    from gpmpc_b200 import _lib
+    from gpmpc_b200._lib import call, ptr
+    from gpmpc_b200.mpc import StageDynamics
+
+    out = {}
+    R, T, nx, nu = 2048, 32, 12, 4
+    g = torch.Generator().manual_seed(7)
+    X, Y = problem["X"], problem["Y"]
+    gps = [(X[:, :dd].contiguous(), Y[:, k].contiguous(), torch.full((dd,), 0.6, dtype=torch.float64), 1.0, 1e-2)
+           for k, dd in enumerate((1, 3, 3))]
+    sd = StageDynamics(gps, [12.1432, 1.8118, -72.08, -7.5755, 39.8653, -72.08, -7.5755, 39.8653, 9.81], 0.02)
+    x = ((torch.rand(R * T, nx, generator=g, dtype=torch.float64) - 0.5) * 0.8).to(dev)
+    u = ((torch.rand(R * T, nu, generator=g, dtype=torch.float64) - 0.3) * 0.6).to(dev)
+    for _ in range(3):
+        sd.disc_dyn(x, u, work_bytes=8 << 30)
+    ms = timed_steps(lambda: sd.disc_dyn(x, u, work_bytes=8 << 30), 5, flush, dev) / 5
+    out["stage_rk4_evals_per_s_n2048"] = R * T / (ms * 1e-3)
+    out["stage_rk4_kernel_pairs_per_s"] = 4 * 3 * R * T * X.shape[0] / (ms * 1e-3)
+    # tightening recursion on its own, 65536 rollouts x 25 stages (variances resident)
+    R2, T2 = 65536, 25
+    A = (torch.eye(nx, dtype=torch.float64) + 0.02 * torch.randn(nx, nx, generator=g, dtype=torch.float64)).to(dev)
+    B = (0.1 * torch.randn(nx, nu, generator=g, dtype=torch.float64)).to(dev)
+    K = (-0.3 * torch.randn(nu, nx, generator=g, dtype=torch.float64)).to(dev)
+    Bd = torch.eye(nx, dtype=torch.float64)[:, [1, 3, 5, 9, 10]].contiguous().to(dev)
+    z = (torch.rand(R2 * T2, nx + nu, generator=g, dtype=torch.float64) - 0.5).to(dev)
+    var = (torch.rand(3, R2 * T2, generator=g, dtype=torch.float64) * 1e-2).to(dev)
+    sc = torch.empty(R2, 2 * nx, T2 + 1, dtype=torch.float64, device=dev)
+    ic = torch.empty(R2, 2 * nu, T2, dtype=torch.float64, device=dev)
+    st = _lib.stream_ptr(dev)
+
+    def tighten():
+        call("gpk_tighten_constraints", ptr(var), var.stride(0), 0, ptr(z), z.stride(0), 6, 7, ptr(gb.hyp), ptr(A),
+             ptr(B), ptr(K), ptr(Bd), nx, nu, T2, R2, 0.02, 2.0, ptr(sc), ptr(ic), st)
+
+    for _ in range(3):
+        tighten()
+    ms = timed_steps(tighten, 5, flush, dev) / 5
+    out["tighten_rollouts_per_s_T25"] = R2 / (ms * 1e-3)
+    out["tighten_fp64_tflops"] = R2 * T2 * (4 * nx**3 + 2 * nu * nx * nx) / (ms * 1e-3) / 1e12
     return out
 
 
