@@ -251,3 +251,51 @@ def test_stage_dynamics_fitc_model():
     assert o.rel_err(xn, torch.stack([t[0] for t in out])) < 1e-12
     assert o.rel_err(A, torch.stack([t[1] for t in out])) < 1e-11
     assert o.rel_err(B, torch.stack([t[2] for t in out])) < 1e-11
+
+
+def test_mpc_kernels_write_only_their_outputs():
+    """Outputs carved out of one sentinel-filled allocation: nothing before, between or after them changes."""
+    from gpmpc_b200 import _lib
+    from gpmpc_b200._lib import call, ptr
+    from gpmpc_b200.mpc import StageDynamics
+    dev = torch.device("cuda", 0)
+    R, T, nx, nu, pad = 5, 7, 12, 4, 64
+    sizes = [R * 2 * nx * (T + 1), R * 2 * nu * T]
+    big = torch.full((sum(sizes) + 3 * pad,), -7.25, dtype=torch.float64, device=dev)
+    sc = big[pad: pad + sizes[0]]
+    ic = big[2 * pad + sizes[0]: 2 * pad + sizes[0] + sizes[1]]
+    g = torch.Generator().manual_seed(1)
+    rnd = lambda *s: torch.rand(*s, generator=g, dtype=torch.float64).to(dev)   # noqa: E731
+    A, B, K, Bd = torch.eye(nx, dtype=torch.float64, device=dev), rnd(nx, nu), -rnd(nu, nx), rnd(nx, 5)
+    z, var = rnd(R * T, 16), rnd(3, R * T) * 1e-2
+    hyp = torch.zeros(3, _lib.load().gpk_hyp_stride(), dtype=torch.float64, device=dev)
+    call("gpk_tighten_constraints", ptr(var), var.stride(0), 1, ptr(z), 16, 6, 7, ptr(hyp), ptr(A), ptr(B), ptr(K),
+         ptr(Bd), nx, nu, T, R, 0.02, 2.0, sc.data_ptr(), ic.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    guard = torch.ones_like(big, dtype=torch.bool)
+    guard[pad: pad + sizes[0]] = False
+    guard[2 * pad + sizes[0]: 2 * pad + sizes[0] + sizes[1]] = False
+    assert bool((big[guard] == -7.25).all()) and not bool((sc == -7.25).any()) and not bool((ic == -7.25).any())
+
+    q = 21
+    gps = [(rnd(40, d).cpu() - 0.5, rnd(40).cpu(), torch.full((d,), 0.5, dtype=torch.float64), 0.5, 1e-2) for d in (1, 3, 3)]
+    sd = StageDynamics(gps, [PRIOR[k] for k in "abcdefhl"], 0.02)
+    sizes = [q * 12, q * 144, q * 48]
+    big = torch.full((sum(sizes) + 4 * pad,), -7.25, dtype=torch.float64, device=dev)
+    offs = [pad, 2 * pad + sizes[0], 3 * pad + sizes[0] + sizes[1]]
+    outs = [big[o_: o_ + s_] for o_, s_ in zip(offs, sizes)]
+    x, u = rnd(q, 12) - 0.5, rnd(q, 4) - 0.5
+    lib = _lib.load()
+    wb = lib.gpk_stage_rk4_work_bytes(8, sd.n, 3)                           # three chunks: 8 + 8 + 5
+    work = torch.empty(wb, dtype=torch.uint8, device=dev)
+    call("gpk_stage_rk4", ptr(x), 12, ptr(u), 4, q, sd.prior.data_ptr(), sd.prior.numel(), sd.dt, ptr(sd.hyp),
+         ptr(sd.pack), sd.pack.stride(0), sd.n, outs[0].data_ptr(), outs[1].data_ptr(), outs[2].data_ptr(), ptr(work),
+         wb, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    guard = torch.ones_like(big, dtype=torch.bool)
+    for o_, s_ in zip(offs, sizes):
+        guard[o_: o_ + s_] = False
+    assert bool((big[guard] == -7.25).all())
+    xr, Ar, Br = sd.disc_dyn(x, u)
+    assert torch.equal(outs[0].view(q, 12), xr) and torch.equal(outs[1].view(q, 12, 12), Ar)
+    assert torch.equal(outs[2].view(q, 12, 4), Br)
