@@ -98,33 +98,28 @@ static GemmParams gemm_args(const double* A, long lda, const double* B, long ldb
 // ------------------------------------------------------------------------------------------------
 // 128x128 leaf: Cholesky of a diagonal block in shared memory + inverse of its factor
 // ------------------------------------------------------------------------------------------------
-constexpr int P_N = 128, P_LD = 129;
-// call f(std::integral_constant<int, v>) for the run-time v in [0, 8): keeps register arrays statically indexed
-#define P_DISPATCH8(v, f)                                                         \
-    switch (v) {                                                                  \
-        case 0: f(std::integral_constant<int, 0>{}); break;                       \
-        case 1: f(std::integral_constant<int, 1>{}); break;                       \
-        case 2: f(std::integral_constant<int, 2>{}); break;                       \
-        case 3: f(std::integral_constant<int, 3>{}); break;                       \
-        case 4: f(std::integral_constant<int, 4>{}); break;                       \
-        case 5: f(std::integral_constant<int, 5>{}); break;                       \
-        case 6: f(std::integral_constant<int, 6>{}); break;                       \
-        default: f(std::integral_constant<int, 7>{}); break;                      \
-    }
-constexpr int P_SMEM = (P_N * P_LD + 4 * P_N) * 8;
+constexpr int P_N = 128, P_LD = 129, P_B = 8, P_NB = P_N / P_B;
+// shared memory: L (row-major, P_LD) | inverses of the 16 diagonal 8x8 factors | current panel (column-major,
+// permuted) | two published row blocks of X (permuted)
+constexpr int P_SMEM = (P_N * P_LD + P_NB * P_B * P_B + P_B * P_N + 2 * P_B * P_N) * 8;
+// position of element R = 8 t + c inside a 128-vector read as double2 pairs by 16 consecutive threads t:
+// pair p = c / 2 of thread t sits at doubles [32 p + 2 t, 32 p + 2 t + 1]  (conflict-free 16-byte reads)
+__device__ __forceinline__ int p_perm(int R) { return ((R & 7) >> 1) * 32 + (R >> 3) * 2 + (R & 1); }
 
-// 256 threads as a 16 x 16 grid; thread (ty, tx) keeps the 8 x 8 block rows 8ty.., columns 8tx.. in REGISTERS.
-// Both phases are right-looking with two barriers per column and 64 FMAs per thread in between:
-//   phase 1  Cholesky:  column j is scaled by 1/sqrt(a_jj) and published, every block below/right of it does
-//            a[r][c] -= l_rj l_cj; the thread that owns a_(j+1)(j+1) publishes the next pivot in the same step
-//   phase 2  inverse by forward elimination of [L | I]:  row j of X is divided by l_jj and published, every
-//            row R > j does x[R][c] -= l_Rj x[j][c]   (X = L^-1 stays lower triangular)
+// 256 threads as a 16 x 16 grid; thread (ty, tx) keeps the 8 x 8 block (rows 8 ty.., columns 8 tx..) in REGISTERS.
+// Blocked right-looking algorithms with block size 8, so the 128 sequential pivots cost 16 block steps:
+//   phase 1  Cholesky, step kb: (a) the owner of the diagonal block factors it in registers and inverts the 8 x 8
+//            factor; (b) the blocks below it become L_ik = A_ik L_kk^-T (a product with that inverse) and are
+//            published as the panel; (c) every lower block right of the panel does A_ic -= L_ik L_ck^T (512 FMAs)
+//   phase 2  X = L^-1 by blocked forward elimination of [L | I], step j: (a) block row j is finished by the 8 x 8
+//            inverse, X_jk = L_jj^-1 R_jk, and published; (b) rows below do R_ik -= L_ij X_jk (512 FMAs)
+// Two barriers per block step in phase 1, one in phase 2 (published rows are double-buffered).
 __global__ void __launch_bounds__(256, 1)
 potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, int* __restrict__ info, int row_offset) {
-    extern __shared__ __align__(16) double S[];          // L, row-major with leading dimension P_LD
-    double* col = S + P_N * P_LD;                        // published column j of L / row j of X
-    double* piv = col + P_N;                             // next pivot (double-buffered by column parity)
-    double* dinv = piv + P_N;                            // 1 / l_jj, reused by phase 2
+    extern __shared__ __align__(16) double S[];
+    double* D8 = S + P_N * P_LD;                         // [16][8][8] inverse of the diagonal factors (lower)
+    double* Pn = D8 + P_NB * P_B * P_B;                  // [8][128] panel, Pn[k][perm(R)] = L[R][8 kb + k]
+    double* Xs = Pn + P_B * P_N;                         // [2][8][128] row block j of X, Xs[j&1][r][perm(C)]
     const int tid = threadIdx.x;
     const int ty = tid >> 4, tx = tid & 15;
     const int r0 = ty * 8, c0 = tx * 8;
@@ -137,66 +132,104 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
             a[r][c] = v.x;
             a[r][c + 1] = v.y;
         }
-    if (tid == 0) piv[0] = a[0][0];
-    __syncthreads();
 
     // ---- phase 1: Cholesky (lower) ----
 #pragma unroll 1
-    for (int j = 0; j < P_N; j++) {
-        const int bj = j >> 3, jj = j & 7;
-        if (tx == bj && ty >= bj) {                      // owners of column j
-            double d = piv[j & 1];
-            if (!(d > 0.0) || isinf(d)) {                // also catches NaN
-                if (ty == bj) atomicCAS(info, 0, row_offset + j + 1);
-                d = 1.0;
+    for (int kb = 0; kb < P_NB; kb++) {
+        if (ty == kb && tx == kb) {
+            // (a) 8 x 8 Cholesky in registers; 1/sqrt(d) by MUFU seed + Newton, l_jj = d / sqrt(d) corrected once
+            double dl[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                double d = a[j][j];
+                if (!(d > 0.0) || isinf(d)) {            // also catches NaN
+                    atomicCAS(info, 0, row_offset + kb * 8 + j + 1);
+                    d = 1.0;
+                }
+                const double rinv = rsqrt(d);
+                double rt = d * rinv;
+                rt = fma(fma(-rt, rt, d), 0.5 * rinv, rt);
+                a[j][j] = rt;
+                dl[j] = rinv;
+#pragma unroll
+                for (int r = j + 1; r < 8; r++) a[r][j] *= rinv;
+#pragma unroll
+                for (int c = j + 1; c < 8; c++)
+#pragma unroll
+                    for (int r = c; r < 8; r++) a[r][c] = fma(-a[r][j], a[c][j], a[r][c]);
             }
-            // 1/sqrt(d) (MUFU seed + Newton, ~1 ulp) and l_jj = d / sqrt(d) with one correction step: no
-            // sqrt followed by a division on the critical path of every column
-            const double rinv = rsqrt(d);
-            double rt = d * rinv;
-            rt = fma(fma(-rt, rt, d), 0.5 * rinv, rt);
-            if (ty == bj) dinv[j] = rinv;
-            auto scale_col = [&](auto JJ) {
-                constexpr int Q = decltype(JJ)::value;
+            // inverse of the 8 x 8 factor, column by column
+            double x[8][8];
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
 #pragma unroll
                 for (int r = 0; r < 8; r++) {
-                    const int R = r0 + r;
-                    double v = a[r][Q];
-                    v = R > j ? v * rinv : (R == j ? rt : v);
-                    if (R >= j) a[r][Q] = v;
-                    col[R] = R > j ? v : 0.0;
+                    if (r < c) x[r][c] = 0.0;
+                    else if (r == c) x[r][c] = dl[c];
+                    else {
+                        double sacc = 0.0;
+#pragma unroll
+                        for (int m = c; m < r; m++) sacc = fma(a[r][m], x[m][c], sacc);
+                        x[r][c] = -dl[r] * sacc;
+                    }
                 }
-            };
-            P_DISPATCH8(jj, scale_col);
-        }
-        __syncthreads();
-        if (ty >= bj && tx >= bj && ty >= tx) {          // trailing update of the lower blocks
-            double lr[8], lc[8];
-#pragma unroll
-            for (int r = 0; r < 8; r++) lr[r] = col[r0 + r];
-#pragma unroll
-            for (int c = 0; c < 8; c++) lc[c] = col[c0 + c];
+            }
 #pragma unroll
             for (int r = 0; r < 8; r++)
 #pragma unroll
-                for (int c = 0; c < 8; c++) a[r][c] = fma(-lr[r], lc[c], a[r][c]);   // rows/cols <= j: col == 0
-            if (ty == tx && ty == ((j + 1) >> 3)) {      // publish the next pivot
-                auto pub = [&](auto JJ) { piv[(j + 1) & 1] = a[decltype(JJ)::value][decltype(JJ)::value]; };
-                P_DISPATCH8((j + 1) & 7, pub);
-            }
+                for (int c = 0; c < 8; c++) {
+                    D8[(kb * 8 + r) * 8 + c] = x[r][c];
+                    const double v = c <= r ? a[r][c] : 0.0;
+                    S[(r0 + r) * P_LD + c0 + c] = v;
+                    if (c <= r) A[(long)(r0 + r) * lda + c0 + c] = v;
+                }
         }
         __syncthreads();
-    }
-    // L (lower incl. diagonal) to shared and global memory; the strict upper part of the block stays untouched
+        if (tx == kb && ty > kb) {
+            // (b) L_ik = A_ik L_kk^-T:  l[r][c] = sum_{m <= c} a[r][m] x[c][m]
+            const double* x = D8 + kb * 64;
+            double l[8][8];
 #pragma unroll
-    for (int r = 0; r < 8; r++)
+            for (int c = 0; c < 8; c++) {
 #pragma unroll
-        for (int c = 0; c < 8; c++) {
-            const int R = r0 + r, C = c0 + c;
-            const double v = C <= R ? a[r][c] : 0.0;
-            S[R * P_LD + C] = v;
-            if (C <= R) A[(long)R * lda + C] = v;
+                for (int r = 0; r < 8; r++) l[r][c] = 0.0;
+#pragma unroll
+                for (int m = 0; m <= c; m++) {
+                    const double xv = x[c * 8 + m];
+#pragma unroll
+                    for (int r = 0; r < 8; r++) l[r][c] = fma(a[r][m], xv, l[r][c]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < 8; r++)
+#pragma unroll
+                for (int c = 0; c < 8; c++) {
+                    S[(r0 + r) * P_LD + c0 + c] = l[r][c];
+                    Pn[c * P_N + p_perm(r0 + r)] = l[r][c];
+                    A[(long)(r0 + r) * lda + c0 + c] = l[r][c];
+                }
         }
+        __syncthreads();
+        if (tx > kb && ty >= tx) {
+            // (c) trailing update of the lower blocks with the published panel
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                double lr[8], lc[8];
+#pragma unroll
+                for (int p2 = 0; p2 < 4; p2++) {
+                    const double2 v = *reinterpret_cast<const double2*>(Pn + k * P_N + p2 * 32 + ty * 2);
+                    lr[2 * p2] = v.x; lr[2 * p2 + 1] = v.y;
+                    const double2 w = *reinterpret_cast<const double2*>(Pn + k * P_N + p2 * 32 + tx * 2);
+                    lc[2 * p2] = w.x; lc[2 * p2 + 1] = w.y;
+                }
+#pragma unroll
+                for (int r = 0; r < 8; r++)
+#pragma unroll
+                    for (int c = 0; c < 8; c++) a[r][c] = fma(-lr[r], lc[c], a[r][c]);
+            }
+        }
+        // no barrier here: the panel is rewritten only after the next step's first barrier
+    }
     // ---- phase 2: X = L^-1 ----
 #pragma unroll
     for (int r = 0; r < 8; r++)
@@ -204,34 +237,50 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
         for (int c = 0; c < 8; c++) a[r][c] = (r0 + r == c0 + c) ? 1.0 : 0.0;
     __syncthreads();
 #pragma unroll 1
-    for (int j = 0; j < P_N; j++) {
-        const int bj = j >> 3, jj = j & 7;
-        if (ty == bj && tx <= bj) {                      // owners of row j: divide by l_jj and publish
-            const double inv = dinv[j];
-            auto scale_row = [&](auto JJ) {
-                constexpr int Q = decltype(JJ)::value;
+    for (int j = 0; j < P_NB; j++) {
+        double* xs = Xs + (j & 1) * P_B * P_N;
+        if (ty == j && tx <= j) {
+            // (a) X_jk = L_jj^-1 R_jk:  x[r][c] = sum_{m <= r} d[r][m] a[m][c]
+            const double* dd = D8 + j * 64;
+            double x[8][8];
 #pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    const double v = a[Q][c] * inv;
-                    a[Q][c] = v;
-                    col[c0 + c] = v;
+            for (int r = 0; r < 8; r++) {
+#pragma unroll
+                for (int c = 0; c < 8; c++) x[r][c] = 0.0;
+#pragma unroll
+                for (int m = 0; m <= r; m++) {
+                    const double dv = dd[r * 8 + m];
+#pragma unroll
+                    for (int c = 0; c < 8; c++) x[r][c] = fma(dv, a[m][c], x[r][c]);
                 }
-            };
-            P_DISPATCH8(jj, scale_row);
-        }
-        __syncthreads();
-        if (ty >= bj && tx <= bj) {
-            double lr[8], xr[8];
-#pragma unroll
-            for (int r = 0; r < 8; r++) lr[r] = (r0 + r > j) ? S[(r0 + r) * P_LD + j] : 0.0;
-#pragma unroll
-            for (int c = 0; c < 8; c++) xr[c] = col[c0 + c];
+            }
 #pragma unroll
             for (int r = 0; r < 8; r++)
 #pragma unroll
-                for (int c = 0; c < 8; c++) a[r][c] = fma(-lr[r], xr[c], a[r][c]);
+                for (int c = 0; c < 8; c++) {
+                    a[r][c] = x[r][c];
+                    xs[r * P_N + p_perm(c0 + c)] = x[r][c];
+                }
         }
         __syncthreads();
+        if (ty > j && tx <= j) {
+            // (b) R_ik -= L_ij X_jk
+#pragma unroll
+            for (int m = 0; m < 8; m++) {
+                double lr[8], xr[8];
+#pragma unroll
+                for (int r = 0; r < 8; r++) lr[r] = S[(r0 + r) * P_LD + j * 8 + m];
+#pragma unroll
+                for (int p2 = 0; p2 < 4; p2++) {
+                    const double2 v = *reinterpret_cast<const double2*>(xs + m * P_N + p2 * 32 + tx * 2);
+                    xr[2 * p2] = v.x; xr[2 * p2 + 1] = v.y;
+                }
+#pragma unroll
+                for (int r = 0; r < 8; r++)
+#pragma unroll
+                    for (int c = 0; c < 8; c++) a[r][c] = fma(-lr[r], xr[c], a[r][c]);
+            }
+        }
     }
 #pragma unroll
     for (int r = 0; r < 8; r++)
