@@ -98,47 +98,77 @@ static GemmParams gemm_args(const double* A, long lda, const double* B, long ldb
 // ------------------------------------------------------------------------------------------------
 // 128x128 leaf: Cholesky of a diagonal block in shared memory + inverse of its factor
 // ------------------------------------------------------------------------------------------------
-constexpr int P_N = 128, P_LD = 129, P_B = 8, P_NB = P_N / P_B;
-// shared memory: L (row-major, P_LD) | inverses of the 16 diagonal 8x8 factors | current panel (column-major,
-// permuted) | two published row blocks of X (permuted)
-constexpr int P_SMEM = (P_N * P_LD + P_NB * P_B * P_B + P_B * P_N + 2 * P_B * P_N) * 8;
-// position of element R = 8 t + c inside a 128-vector read as double2 pairs by 16 consecutive threads t:
-// pair p = c / 2 of thread t sits at doubles [32 p + 2 t, 32 p + 2 t + 1]  (conflict-free 16-byte reads)
-__device__ __forceinline__ int p_perm(int R) { return ((R & 7) >> 1) * 32 + (R >> 3) * 2 + (R & 1); }
+constexpr int P_N = 128, P_LD = 129, P_B = 8, P_NB = P_N / P_B, P_THREADS = 160;
+// shared memory: L (row-major, P_LD) | inverses of the 16 diagonal 8x8 factors | 1/l_jj | current panel
+// (column-major, permuted) | two published row blocks of X (permuted)
+constexpr int P_SMEM = (P_N * P_LD + P_NB * P_B * P_B + P_N + P_B * P_N + 2 * P_B * P_N) * 8;
+// position of element R = 8 t + c inside a 128-vector read as double2 pairs by 16 consecutive block indices t:
+// pair p = c / 2 of block t sits at doubles [32 p + 2 t, 32 p + 2 t + 1]
+__device__ __forceinline__ int p_perm(int R) { return ((R & 7) >> 1) * 32 + (R >> 3) * 2 + (R & 7 & 1); }
 
-// 256 threads as a 16 x 16 grid; thread (ty, tx) keeps the 8 x 8 block (rows 8 ty.., columns 8 tx..) in REGISTERS.
-// Blocked right-looking algorithms with block size 8, so the 128 sequential pivots cost 16 block steps:
-//   phase 1  Cholesky, step kb: (a) the owner of the diagonal block factors it in registers and inverts the 8 x 8
-//            factor; (b) the blocks below it become L_ik = A_ik L_kk^-T (a product with that inverse) and are
-//            published as the panel; (c) every lower block right of the panel does A_ic -= L_ik L_ck^T (512 FMAs)
-//   phase 2  X = L^-1 by blocked forward elimination of [L | I], step j: (a) block row j is finished by the 8 x 8
-//            inverse, X_jk = L_jj^-1 R_jk, and published; (b) rows below do R_ik -= L_ij X_jk (512 FMAs)
+// Thread -> 8x8 block of the lower triangle (136 blocks, 160 threads).  Warps 0-3 (one per SM sub-partition) share
+// the blocks that take part in the rank-8 updates, dealt round-robin so that every step keeps the four warps evenly
+// loaded; warp 4 holds the 16 blocks that never take part in them (phase 1: block column 0; phase 2: the diagonal).
+__device__ __forceinline__ void p_map1(int t, int& ty, int& tx) {
+    const int w = t >> 5, l = t & 31;
+    ty = tx = -1;
+    if (w == 4) { if (l < 16) { ty = l; tx = 0; } return; }
+    const int i = l * 4 + w;                  // index into the blocks with tx >= 1, ordered by tx descending
+    if (i >= 120) return;
+    int m = 0;
+    while ((m + 1) * (m + 2) / 2 <= i) m++;   // tx = 15 - m has m + 1 blocks
+    tx = 15 - m;
+    ty = tx + (i - m * (m + 1) / 2);
+}
+__device__ __forceinline__ void p_map2(int t, int& ty, int& tx) {
+    const int w = t >> 5, l = t & 31;
+    ty = tx = -1;
+    if (w == 4) { if (l < 16) { ty = l; tx = l; } return; }
+    const int i = l * 4 + w;                  // index into the off-diagonal blocks, ordered by (tx, ty) ascending
+    if (i >= 120) return;
+    int c = 0, before = 0;
+    while (before + (15 - c) <= i) { before += 15 - c; c++; }
+    tx = c;
+    ty = c + 1 + (i - before);
+}
+
+// Each thread keeps one 8 x 8 block of the lower triangle in REGISTERS.  Blocked right-looking algorithms with block
+// size 8, so the 128 sequential pivots cost 16 block steps:
+//   phase 1  Cholesky, step kb: (a) the owner of the diagonal block factors it in registers; (b) the blocks below it
+//            become L_ik = A_ik L_kk^-T by forward substitution and are published as the panel; (c) every lower block
+//            right of the panel does A_ic -= L_ik L_ck^T (512 FMAs)
+//   phase 2  X = L^-1 by blocked forward elimination of [L | I]: the 16 diagonal 8 x 8 factors are inverted at once,
+//            then step j: (a) block row j is finished, X_jk = L_jj^-1 R_jk, and published; (b) rows below do
+//            R_ik -= L_ij X_jk (512 FMAs)
 // Two barriers per block step in phase 1, one in phase 2 (published rows are double-buffered).
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(P_THREADS, 1)
 potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, int* __restrict__ info, int row_offset) {
     extern __shared__ __align__(16) double S[];
     double* D8 = S + P_N * P_LD;                         // [16][8][8] inverse of the diagonal factors (lower)
-    double* Pn = D8 + P_NB * P_B * P_B;                  // [8][128] panel, Pn[k][perm(R)] = L[R][8 kb + k]
+    double* dinv = D8 + P_NB * P_B * P_B;                // [128] 1 / l_jj
+    double* Pn = dinv + P_N;                             // [8][128] panel, Pn[k][perm(R)] = L[R][8 kb + k]
     double* Xs = Pn + P_B * P_N;                         // [2][8][128] row block j of X, Xs[j&1][r][perm(C)]
     const int tid = threadIdx.x;
-    const int ty = tid >> 4, tx = tid & 15;
-    const int r0 = ty * 8, c0 = tx * 8;
+    int ty, tx;
+    p_map1(tid, ty, tx);
+    int r0 = ty * 8, c0 = tx * 8;
     double a[8][8];
+    if (ty >= 0) {
 #pragma unroll
-    for (int r = 0; r < 8; r++)
+        for (int r = 0; r < 8; r++)
 #pragma unroll
-        for (int c = 0; c < 8; c += 2) {
-            const double2 v = *reinterpret_cast<const double2*>(A + (long)(r0 + r) * lda + c0 + c);
-            a[r][c] = v.x;
-            a[r][c + 1] = v.y;
-        }
+            for (int c = 0; c < 8; c += 2) {
+                const double2 v = *reinterpret_cast<const double2*>(A + (long)(r0 + r) * lda + c0 + c);
+                a[r][c] = v.x;
+                a[r][c + 1] = v.y;
+            }
+    }
 
     // ---- phase 1: Cholesky (lower) ----
 #pragma unroll 1
     for (int kb = 0; kb < P_NB; kb++) {
         if (ty == kb && tx == kb) {
             // (a) 8 x 8 Cholesky in registers; 1/sqrt(d) by MUFU seed + Newton, l_jj = d / sqrt(d) corrected once
-            double dl[8];
 #pragma unroll
             for (int j = 0; j < 8; j++) {
                 double d = a[j][j];
@@ -150,7 +180,7 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
                 double rt = d * rinv;
                 rt = fma(fma(-rt, rt, d), 0.5 * rinv, rt);
                 a[j][j] = rt;
-                dl[j] = rinv;
+                dinv[kb * 8 + j] = rinv;
 #pragma unroll
                 for (int r = j + 1; r < 8; r++) a[r][j] *= rinv;
 #pragma unroll
@@ -158,58 +188,55 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
 #pragma unroll
                     for (int r = c; r < 8; r++) a[r][c] = fma(-a[r][j], a[c][j], a[r][c]);
             }
-            // inverse of the 8 x 8 factor, column by column
-            double x[8][8];
-#pragma unroll
-            for (int c = 0; c < 8; c++) {
-#pragma unroll
-                for (int r = 0; r < 8; r++) {
-                    if (r < c) x[r][c] = 0.0;
-                    else if (r == c) x[r][c] = dl[c];
-                    else {
-                        double sacc = 0.0;
-#pragma unroll
-                        for (int m = c; m < r; m++) sacc = fma(a[r][m], x[m][c], sacc);
-                        x[r][c] = -dl[r] * sacc;
-                    }
-                }
-            }
 #pragma unroll
             for (int r = 0; r < 8; r++)
 #pragma unroll
                 for (int c = 0; c < 8; c++) {
-                    D8[(kb * 8 + r) * 8 + c] = x[r][c];
                     const double v = c <= r ? a[r][c] : 0.0;
                     S[(r0 + r) * P_LD + c0 + c] = v;
                     if (c <= r) A[(long)(r0 + r) * lda + c0 + c] = v;
                 }
         }
         __syncthreads();
-        if (tx == kb && ty > kb) {
-            // (b) L_ik = A_ik L_kk^-T:  l[r][c] = sum_{m <= c} a[r][m] x[c][m]
-            const double* x = D8 + kb * 64;
-            double l[8][8];
+        const bool panel = tx == kb && ty > kb;
+        if (panel) {
+            // (b) L_ik = A_ik L_kk^-T, column by column: l[r][c] = (a[r][c] - sum_{m<c} l[r][m] L_kk[c][m]) / L_kk[c][c]
+            // (the diagonal factor is fetched up front so that only the FMA chain is on the critical path)
+            const double* Lk = S + (kb * 8) * P_LD + kb * 8;
+            double lk[8][8], di[8];
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                di[c] = dinv[kb * 8 + c];
+#pragma unroll
+                for (int m = 0; m < c; m++) lk[c][m] = Lk[c * P_LD + m];
+            }
 #pragma unroll
             for (int c = 0; c < 8; c++) {
 #pragma unroll
-                for (int r = 0; r < 8; r++) l[r][c] = 0.0;
+                for (int m = 0; m < c; m++)
 #pragma unroll
-                for (int m = 0; m <= c; m++) {
-                    const double xv = x[c * 8 + m];
+                    for (int r = 0; r < 8; r++) a[r][c] = fma(-a[r][m], lk[c][m], a[r][c]);
 #pragma unroll
-                    for (int r = 0; r < 8; r++) l[r][c] = fma(a[r][m], xv, l[r][c]);
-                }
+                for (int r = 0; r < 8; r++) a[r][c] *= di[c];
             }
+            const int pr = (r0 >> 3) * 2;        // p_perm(r0 + r) = (r >> 1) * 32 + pr + (r & 1)
+#pragma unroll
+            for (int r = 0; r < 8; r += 2)
+#pragma unroll
+                for (int c = 0; c < 8; c++)
+                    *reinterpret_cast<double2*>(Pn + c * P_N + (r >> 1) * 32 + pr) = make_double2(a[r][c], a[r + 1][c]);
+        }
+        __syncthreads();
+        if (panel) {
+            // off the critical path: the finished block goes to shared memory (phase 2) and back to global memory
 #pragma unroll
             for (int r = 0; r < 8; r++)
 #pragma unroll
                 for (int c = 0; c < 8; c++) {
-                    S[(r0 + r) * P_LD + c0 + c] = l[r][c];
-                    Pn[c * P_N + p_perm(r0 + r)] = l[r][c];
-                    A[(long)(r0 + r) * lda + c0 + c] = l[r][c];
+                    S[(r0 + r) * P_LD + c0 + c] = a[r][c];
+                    A[(long)(r0 + r) * lda + c0 + c] = a[r][c];
                 }
         }
-        __syncthreads();
         if (tx > kb && ty >= tx) {
             // (c) trailing update of the lower blocks with the published panel
 #pragma unroll
@@ -230,16 +257,42 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
         }
         // no barrier here: the panel is rewritten only after the next step's first barrier
     }
+    __syncthreads();
     // ---- phase 2: X = L^-1 ----
+    p_map2(tid, ty, tx);
+    r0 = ty * 8; c0 = tx * 8;
+    if (ty >= 0 && ty == tx) {
+        // inverse of this diagonal 8 x 8 factor, column by column
+        const double* Lk = S + r0 * P_LD + c0;
+        double x[8][8];
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                if (r < c) x[r][c] = 0.0;
+                else if (r == c) x[r][c] = dinv[r0 + c];
+                else {
+                    double sacc = 0.0;
+#pragma unroll
+                    for (int m = c; m < r; m++) sacc = fma(Lk[r * P_LD + m], x[m][c], sacc);
+                    x[r][c] = -dinv[r0 + r] * sacc;
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+#pragma unroll
+            for (int c = 0; c < 8; c++) D8[(ty * 8 + r) * 8 + c] = x[r][c];
+    }
 #pragma unroll
     for (int r = 0; r < 8; r++)
 #pragma unroll
-        for (int c = 0; c < 8; c++) a[r][c] = (r0 + r == c0 + c) ? 1.0 : 0.0;
+        for (int c = 0; c < 8; c++) a[r][c] = (ty == tx && r == c) ? 1.0 : 0.0;
     __syncthreads();
 #pragma unroll 1
     for (int j = 0; j < P_NB; j++) {
         double* xs = Xs + (j & 1) * P_B * P_N;
-        if (ty == j && tx <= j) {
+        if (ty == j) {
             // (a) X_jk = L_jj^-1 R_jk:  x[r][c] = sum_{m <= r} d[r][m] a[m][c]
             const double* dd = D8 + j * 64;
             double x[8][8];
@@ -263,7 +316,7 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
                 }
         }
         __syncthreads();
-        if (ty > j && tx <= j) {
+        if (ty > j && tx >= 0 && tx <= j) {
             // (b) R_ik -= L_ij X_jk
 #pragma unroll
             for (int m = 0; m < 8; m++) {
@@ -282,11 +335,19 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
             }
         }
     }
+    if (ty >= 0) {
 #pragma unroll
-    for (int r = 0; r < 8; r++)
+        for (int r = 0; r < 8; r++)
 #pragma unroll
-        for (int c = 0; c < 8; c += 2)
-            *reinterpret_cast<double2*>(Dinv + (r0 + r) * P_N + c0 + c) = make_double2(a[r][c], a[r][c + 1]);
+            for (int c = 0; c < 8; c += 2)
+                *reinterpret_cast<double2*>(Dinv + (r0 + r) * P_N + c0 + c) = make_double2(a[r][c], a[r][c + 1]);
+    }
+    // the strict upper blocks of X are zero
+    for (int e = tid; e < P_NB * P_NB * 32; e += P_THREADS) {
+        const int blk = e >> 5, by = blk >> 4, bx = blk & 15, w = e & 31;
+        if (bx > by)
+            *reinterpret_cast<double2*>(Dinv + (by * 8 + (w >> 2)) * P_N + bx * 8 + (w & 3) * 2) = make_double2(0.0, 0.0);
+    }
 }
 
 static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_offset, cudaStream_t st) {
@@ -295,7 +356,7 @@ static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_of
         GPK_CUDA(cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
         attr_done = true;
     }
-    potf2_inv_kernel<<<1, 256, P_SMEM, st>>>(A, lda, Dinv, info, row_offset);
+    potf2_inv_kernel<<<1, P_THREADS, P_SMEM, st>>>(A, lda, Dinv, info, row_offset);
     GPK_LAUNCHED();
     return 0;
 }
