@@ -371,6 +371,18 @@ def measure_extras(gb, problem, Z, flush, dev):
         E.predict(gb, Z, var_path="f64")
     ms = timed_steps(lambda: E.predict(gb, Z, var_path="f64"), 10, flush, dev) / 10
     out["dmma_var_path_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
+    v_ref = E.predict(gb, Z, var_path="f64")[1]
+    out["var_rel_err_vs_dmma_path_digits5"] = float((E.predict(gb, Z)[1] - v_ref).abs().max() / v_ref.abs().max())
+    # the same step with 4 (30-bit) or 6 (46-bit) digits: 10 / 21 digit products instead of 15
+    for S in (4, 6):
+        gbs = E.fit_batch(problem["X"].to(dev), problem["Y"].to(dev), problem["ell"], problem["sf2"], problem["noise"],
+                          digits=S)
+        for _ in range(3):
+            E.predict(gbs, Z)
+        ms = timed_steps(lambda: E.predict(gbs, Z), 10, flush, dev) / 10
+        out[f"digits{S}_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
+        out[f"var_rel_err_vs_dmma_path_digits{S}"] = float((E.predict(gbs, Z)[1] - v_ref).abs().max() / v_ref.abs().max())
+        del gbs
     for name, zz in (("f64", Z), ("f32", Z32)):
         for _ in range(3):
             E.predict(gb, zz, want_var=False)
