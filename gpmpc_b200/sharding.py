@@ -1,7 +1,7 @@
 """Sharding layer (north-star subsystem d): one process per GPU under torch.distributed.
 
 The reference has no counterpart (single process, a Python loop over its three GPs, gpmpc/gpmpc.py:159-162);
-the three axes below are the ones SURVEY.md 8e names:
+the three axes below are the ones SURVEY.md 8e names (plus rollouts for the MPC-side rows of 8f):
 
   queries      embarrassingly parallel given the fitted state: contiguous Q/G blocks per rank, fitted state
                (X, hyp, W, alpha) replicated once after the fit -> NO collective during prediction;
@@ -81,6 +81,30 @@ def predict_sharded(predict_fn: Callable, Z: torch.Tensor, *, gather: bool = Fal
         dist.all_gather(parts, buf, group=group)
         gathered.append(torch.cat([p[:, : h - l] for p, (l, h) in zip(parts, sizes)], dim=1))
     return 0, Z.shape[0], tuple(gathered)
+
+
+def rollouts_sharded(fn: Callable, inputs: Sequence[torch.Tensor], *, gather: bool = False, group=None):
+    """Rollout / stage sharding for the MPC-side rows (mpc.ConstraintTightening.propagate_constraint_limits,
+    mpc.StageDynamics.disc_dyn): every input has the independent items (rollouts, or (x, u) pairs) on dim 0; each rank
+    processes its contiguous block, fn(*local_inputs) -> tuple of tensors with the items on dim 0.  No collective
+    unless gather=True (all_gather along dim 0, original order).  Returns (lo, hi, outputs)."""
+    rank, world = world_info(group)
+    n = inputs[0].shape[0]
+    assert all(t.shape[0] == n for t in inputs), "inputs disagree on the number of items"
+    lo, hi = shard_bounds(n, world, rank)
+    outs = fn(*[t[lo:hi] for t in inputs])
+    if not gather or world == 1:
+        return lo, hi, outs
+    sizes = [shard_bounds(n, world, r) for r in range(world)]
+    nmax = max(h - l for l, h in sizes)
+    gathered = []
+    for t in outs:
+        buf = t.new_zeros((nmax,) + tuple(t.shape[1:]))
+        buf[: t.shape[0]] = t
+        parts = [torch.empty_like(buf) for _ in range(world)]
+        dist.all_gather(parts, buf, group=group)
+        gathered.append(torch.cat([p[: h - l] for p, (l, h) in zip(parts, sizes)], dim=0))
+    return 0, n, tuple(gathered)
 
 
 def broadcast_tensors(tensors: Sequence[torch.Tensor], src: int = 0, group=None) -> None:

@@ -64,6 +64,26 @@ def _worker(rank, world, port):
 
         allp = S.fit_gps_sharded(fit_one, 3, 3, device=dev)
         assert allp.shape == (3, 3) and bool((allp > 0).all())
+        # rollout sharding of the MPC-side rows: tightening and stage dynamics per rank, gathered == single GPU
+        import numpy as np
+        from gpmpc_b200.mpc import ConstraintTightening, StageDynamics
+        g = np.load(os.path.join(os.path.dirname(__file__), "golden", "tighten_T25.npz"))
+        gps = [(torch.tensor(g[f"gp{k}_X"]), torch.tensor(g[f"gp{k}_y"]), torch.tensor(g[f"gp{k}_ell"]),
+                float(g[f"gp{k}_sf2"]), float(g["noise"][k])) for k in range(3)]
+        ct = ConstraintTightening(gps, [[0], [1, 2, 3], [4, 5, 6]], g["dfdx"], g["dfdu"], g["lqr_gain"], g["Bd"],
+                                  float(g["dt"]), float(g["inverse_cdf"]))
+        xp = torch.tensor(g["x_prev"]).repeat(3, 1, 1)[:11].to(dev)            # 11 rollouts: 6 + 5
+        up = torch.tensor(g["u_prev"]).repeat(3, 1, 1)[:11].to(dev)
+        full_sc, full_ic = ct.propagate_constraint_limits(xp, up)
+        lo, hi, (sc, ic) = S.rollouts_sharded(ct.propagate_constraint_limits, [xp, up], gather=True)
+        assert (lo, hi) == (0, 11) and o.rel_err(sc.cpu(), full_sc.cpu()) < 1e-12 and o.rel_err(ic.cpu(), full_ic.cpu()) < 1e-12
+        assert o.rel_err(sc[:4].cpu(), g["state_constraint"]) < 1e-7
+        sd = StageDynamics(gps, [12.1432, 1.8118, -72.08, -7.5755, 39.8653, -72.08, -7.5755, 39.8653], 0.02)
+        xq, uq = xp[:, :, 0].contiguous(), up[:, :, 0].contiguous()
+        full = sd.disc_dyn(xq, uq)
+        lo, hi, outs = S.rollouts_sharded(sd.disc_dyn, [xq, uq], gather=True)
+        for a, b in zip(outs, full):
+            assert torch.equal(a, b)
         dist.barrier()
     finally:
         dist.destroy_process_group()

@@ -35,6 +35,8 @@ def test_single_process_paths_need_no_process_group():
     assert (lo, hi) == (0, 6) and torch.equal(outs[0][0], Z.sum(1))
     part = S.allreduce_row_partials(lambda a, b: torch.tensor([float(b - a)], dtype=torch.float64), 10)
     assert float(part) == 10.0
+    lo, hi, outs = S.rollouts_sharded(lambda a, b: (a + b[:, :1],), [Z, Z * 2.0], gather=True)
+    assert (lo, hi) == (0, 6) and torch.equal(outs[0], Z + 2.0 * Z[:, :1])
 
 
 def _free_port():
@@ -98,6 +100,27 @@ def _worker(rank, world, port, q_total):
         assert calls == S.owned_gps(3, world, rank)
         assert torch.equal(allp[:, 0], torch.tensor([0.0, 1.0, 2.0], dtype=torch.float64))
         assert torch.equal(allp[:, 2], torch.tensor([float(S.gp_owner(i, world)) for i in range(3)], dtype=torch.float64))
+        # --- rollout sharding of the MPC-side rows: tightening recursion per rollout, ragged shards, gather order
+        import numpy as np
+        g = np.load(os.path.join(os.path.dirname(__file__), "golden", "tighten_T25.npz"))
+        xp, up = torch.tensor(g["x_prev"]), torch.tensor(g["u_prev"])
+        xp, up = torch.cat([xp, xp[:1] * 0.5]), torch.cat([up, up[:1] * 0.5])       # 5 rollouts over 2 ranks: 3 + 2
+
+        def tighten_fn(x_loc, u_loc):
+            sc, ic = [], []
+            for r in range(x_loc.shape[0]):
+                z = np.hstack((x_loc[r].numpy()[:, :-1].T, u_loc[r].numpy().T))
+                var_y = np.stack([np.full(z.shape[0], 1e-3 * (k + 1)) + z[:, k] ** 2 * 1e-3 for k in range(3)])
+                a, b = o.propagate_constraint_limits(var_y, z, g["noise"], g["dfdx"], g["dfdu"], g["lqr_gain"], g["Bd"],
+                                                     float(g["dt"]), float(g["inverse_cdf"]))
+                sc.append(torch.tensor(a)), ic.append(torch.tensor(b))
+            return torch.stack(sc), torch.stack(ic)
+
+        full_sc, full_ic = tighten_fn(xp, up)
+        lo, hi, (sc, ic) = S.rollouts_sharded(tighten_fn, [xp, up])
+        assert (lo, hi) == S.shard_bounds(5, world, rank) and torch.equal(sc, full_sc[lo:hi])
+        lo, hi, (sc, ic) = S.rollouts_sharded(tighten_fn, [xp, up], gather=True)
+        assert (lo, hi) == (0, 5) and torch.equal(sc, full_sc) and torch.equal(ic, full_ic)
         # --- state broadcast
         t = torch.full((4,), float(rank))
         S.broadcast_tensors([t], src=1)
