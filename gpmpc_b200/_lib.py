@@ -12,7 +12,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgpmpc_b200.so")
+LIB_PATH = os.environ.get("GPMPC_B200_LIB") or os.path.join(_HERE, "libgpmpc_b200.so")   # override: A/B builds
 
 _p, _l, _i, _d = C.c_void_p, C.c_long, C.c_int, C.c_double
 
