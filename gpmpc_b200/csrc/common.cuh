@@ -88,4 +88,28 @@ __device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_sr
                  : "memory");
 }
 
+// exp(a) for a <= 0 to ~2^-51 relative error, branch-free, 10 FP64 operations: a log2(e) 1024 = m + f with
+// m = 1024 n + j, so exp(a) = 2^n * T[j] * exp(r), T[j] = 2^(j/1024) from a shared-memory table, r = a - m ln2/1024
+// (Cody-Waite, |r| <= 3.4e-4) and a degree-4 polynomial; 2^n goes straight into the exponent field (normal
+// results down to a = -708; below that the result is 0, where the library exp is subnormal or 0).
+constexpr int EXP_TAB = 1024;
+__device__ __forceinline__ double exp_neg_tab(double a0, const double* __restrict__ tab) {
+    const double a = fmax(a0, -708.0);
+    const double MAGIC = 6755399441055744.0;             // 1.5 * 2^52
+    const double tm = fma(a, 1477.3197218702985, MAGIC); // 1024 / ln 2
+    const double md = tm - MAGIC;
+    double r = fma(md, -0.0006769015433292225, a);  // ln2/1024 hi (32 significant bits: exact products)
+    r = fma(md, -1.8634911418658083e-13, r);            // ln2/1024 lo
+    double p = fma(r, 4.16666666666666666667e-02, 1.66666666666666666667e-01);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    const int m = __double2loint(tm);                     // integer part of tm sits in the low mantissa word
+    p *= tab[m & (EXP_TAB - 1)];
+    const double e = __hiloint2double(__double2hiint(p) + ((m >> 10) << 20), __double2loint(p));
+    return a0 < -708.0 ? 0.0 : e;
+}
+// the table in device memory (built once per device on first use; defined in ozaki.cu)
+const double* exp_table(cudaStream_t st);
+
 }  // namespace gpk

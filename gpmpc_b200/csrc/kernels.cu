@@ -131,6 +131,13 @@ __device__ __forceinline__ float kexp(float x) {
     return y;
 }
 __device__ __forceinline__ double kexp(double x) { return exp(x); }
+// fp64 with few input dimensions: the exponential dominates the pair cost and the table version (common.cuh) is
+// ~10 % faster end to end; from d = 16 on its random shared-memory lookups cost more than the library polynomial
+// (measured: 142 vs 165 G pairs/s), so the library exp stays there
+template <bool TAB>
+__device__ __forceinline__ double kexp_sel(double x, const double* tab) { return TAB ? exp_neg_tab(fmin(x, 0.0), tab) : exp(x); }
+template <bool TAB>
+__device__ __forceinline__ float kexp_sel(float x, const double*) { return kexp(x); }
 
 template <typename T, int DP>
 __device__ __forceinline__ void load_row(const T* __restrict__ p, T (&x)[DP]) {
@@ -162,6 +169,7 @@ struct MeanJacArgs {
     void* mean; long stride_mean;                    // [batch][q]
     void* jac; long ldj; long stride_jac;            // [batch][q][ldj]
     void* work; long stride_work;                    // [batch][n_split][q][DP + 1] partial sums when n_split > 1
+    const double* exp_tab;                           // 2^(j/1024) table of the fp64 exponential (common.cuh)
 };
 
 constexpr int MJ_THREADS = 128;
@@ -174,10 +182,14 @@ mean_jac_kernel(const MeanJacArgs a) {
     constexpr uint32_t TILE_BYTES = TILE_ELEMS * sizeof(T);
     T* buf = reinterpret_cast<T*>(smem_raw);                        // 2 tiles
     __shared__ __align__(8) uint64_t bar[2];
+    constexpr bool TAB = sizeof(T) == 8 && DP <= 8;
+    __shared__ double etab[TAB ? EXP_TAB : 1];                      // table of exp_neg_tab
 
     const int tid = threadIdx.x;
     const long batch = blockIdx.z;
     const int split = blockIdx.y;
+    if constexpr (TAB)
+        for (int i = tid; i < EXP_TAB; i += MJ_THREADS) etab[i] = a.exp_tab[i];   // visible after the barrier below
     const double* hyp = a.hyp + batch * HYP_STRIDE;
     const T* __restrict__ Z = reinterpret_cast<const T*>(a.Z) + batch * a.strideZ;
     const T* __restrict__ pack = reinterpret_cast<const T*>(a.pack) + batch * a.stride_pack;
@@ -237,7 +249,7 @@ mean_jac_kernel(const MeanJacArgs a) {
                 T s = e + ez[r];
 #pragma unroll
                 for (int j = 0; j < DP; j++) s = fma(zl[r][j], x[j], s);
-                const T w = kexp(s) * al;
+                const T w = kexp_sel<TAB>(s, etab) * al;
                 m[r] += w;
 #pragma unroll
                 for (int j = 0; j < DP; j++) S[r][j] = fma(w, x[j], S[r][j]);
@@ -535,6 +547,11 @@ int gpk_predict_mean_jac(int dtype, const void* Z, long ldz, long q, long stride
     MeanJacArgs a{};
     a.Z = Z; a.ldz = ldz; a.q = q; a.strideZ = strideZ; a.d = d; a.hyp = hyp;
     a.pack = pack; a.stride_pack = stride_pack;
+    a.exp_tab = nullptr;
+    if (dtype == 1) {
+        a.exp_tab = exp_table((cudaStream_t)stream);
+        GPK_ARG(a.exp_tab != nullptr, "could not allocate the exp table");
+    }
     a.n_tiles = (int)((n + TP - 1) / TP);
     a.mean = mean; a.stride_mean = stride_mean; a.jac = jac; a.ldj = ldj; a.stride_jac = stride_jac;
     // split the training set over CTAs when the query count alone cannot fill the machine (~2 waves)

@@ -124,28 +124,6 @@ __device__ __forceinline__ void oz_pack_digits4(const double (&e)[4], uint32_t (
     }
 }
 
-// exp(a) for a <= 0 to ~2^-51 relative error, branch-free, 10 FP64 operations: a log2(e) 1024 = m + f with
-// m = 1024 n + j, so exp(a) = 2^n * T[j] * exp(r), T[j] = 2^(j/1024) from a shared-memory table, r = a - m ln2/1024
-// (Cody-Waite, |r| <= 3.4e-4) and a degree-4 polynomial; 2^n goes straight into the exponent field (normal
-// results down to a = -708; below that the result is 0, where the library exp is subnormal or 0).
-constexpr int OZ_EXP_TAB = 1024;
-__device__ __forceinline__ double oz_exp_neg(double a0, const double* __restrict__ tab) {
-    const double a = fmax(a0, -708.0);
-    const double MAGIC = 6755399441055744.0;             // 1.5 * 2^52
-    const double tm = fma(a, 1477.3197218702985, MAGIC); // 1024 / ln 2
-    const double md = tm - MAGIC;
-    double r = fma(md, -0.0006769015433292225, a);  // ln2/1024 hi (32 significant bits: exact products)
-    r = fma(md, -1.8634911418658083e-13, r);            // ln2/1024 lo
-    double p = fma(r, 4.16666666666666666667e-02, 1.66666666666666666667e-01);
-    p = fma(p, r, 0.5);
-    p = fma(p, r, 1.0);
-    p = fma(p, r, 1.0);
-    const int m = __double2loint(tm);                     // integer part of tm sits in the low mantissa word
-    p *= tab[m & (OZ_EXP_TAB - 1)];
-    const double e = __hiloint2double(__double2hiint(p) + ((m >> 10) << 20), __double2loint(p));
-    return a0 < -708.0 ? 0.0 : e;
-}
-
 struct OzFrontArgs {
     const void* Z; long ldz, q, strideZ;
     const double* X; long ldx, n, strideX;
@@ -179,14 +157,14 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
     __shared__ __align__(16) double XsA[OZ_BK * LDA];    // rows in fragment-column order (see above)
     __shared__ __align__(16) double XsB[MJ ? OZ_BK * LDB : 1];   // rows in natural order
     __shared__ __align__(16) double ex[OZ_BK], as[OZ_BK];
-    __shared__ double exp_tab[OZ_EXP_TAB];
+    __shared__ double exp_tab[EXP_TAB];
     const long gp = blockIdx.z;
     const int qt = blockIdx.y;
     const double* hyp = a.hyp + gp * HYP_STRIDE;
     const TZ* Z = reinterpret_cast<const TZ*>(a.Z) + gp * a.strideZ;
     const double* X = a.X + gp * a.strideX;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    for (int i = tid; i < OZ_EXP_TAB; i += 256) exp_tab[i] = a.exp_tab[i];   // visible after the first barrier below
+    for (int i = tid; i < EXP_TAB; i += 256) exp_tab[i] = a.exp_tab[i];   // visible after the first barrier below
     const int g = lane >> 2, t = lane & 3;
 
     // A fragments of GEMM 1 (scaled queries) for the two 8-query blocks of this warp
@@ -290,7 +268,7 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
                 }
                 double e[4];
 #pragma unroll
-                for (int i = 0; i < 4; i++) e[i] = qv[mb] ? oz_exp_neg(fmin(c[i >> 1][i & 1], 0.0), exp_tab) : 0.0;
+                for (int i = 0; i < 4; i++) e[i] = qv[mb] ? exp_neg_tab(fmin(c[i >> 1][i & 1], 0.0), exp_tab) : 0.0;
                 uint32_t w[S];
                 oz_pack_digits4<S>(e, w);
                 int8_t* dst = out + oz_tile_off(qrow[mb], unit * 16 + 4 * t);
@@ -669,14 +647,14 @@ static int oz_sm_count() {
 }
 
 // 2^(j/1024) table of the front kernel's exp: computed once per device on the host in long double, rounded to double
-static const double* oz_exp_table(cudaStream_t st) {
+const double* gpk::exp_table(cudaStream_t st) {
     static double* dev_tab[64] = {nullptr};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return nullptr;
     if (!dev_tab[dev]) {
-        static double host_tab[OZ_EXP_TAB];
-        for (int j = 0; j < OZ_EXP_TAB; j++) host_tab[j] = (double)exp2l((long double)j / OZ_EXP_TAB);
+        static double host_tab[EXP_TAB];
+        for (int j = 0; j < EXP_TAB; j++) host_tab[j] = (double)exp2l((long double)j / EXP_TAB);
         double* p = nullptr;
         if (cudaMalloc(&p, sizeof(host_tab)) != cudaSuccess) return nullptr;
         if (cudaMemcpyAsync(p, host_tab, sizeof(host_tab), cudaMemcpyHostToDevice, st) != cudaSuccess) return nullptr;
@@ -755,7 +733,7 @@ template <typename TZ>
 static int oz_front_dispatch(const OzFrontArgs& a_in, int S, bool mj, int n_split, long qtiles, int batch, void* mean,
                              long stride_mean, void* jac, long ldj, long stride_jac, cudaStream_t st) {
     OzFrontArgs a = a_in;
-    a.exp_tab = oz_exp_table(st);
+    a.exp_tab = exp_table(st);
     GPK_ARG(a.exp_tab != nullptr, "could not allocate the exp table");
 #define OZ_F(SV) \
     if (S == SV) return mj ? oz_launch_front<TZ, SV, true>(a, n_split, qtiles, batch, (TZ*)mean, stride_mean, (TZ*)jac, ldj, stride_jac, st) \
