@@ -429,7 +429,7 @@ def measure_mpc_rows(gb, problem, flush, dev):
         sd.disc_dyn(x, u, work_bytes=8 << 30)
     ms = timed_steps(lambda: sd.disc_dyn(x, u, work_bytes=8 << 30), 5, flush, dev) / 5
     out["stage_rk4_evals_per_s_n2048"] = R * T / (ms * 1e-3)
-    out["stage_rk4_kernel_pairs_per_s"] = 4 * 3 * R * T * X.shape[0] / (ms * 1e-3)
+    out["stage_rk4_kernel_pairs_per_s"] = 9 * R * T * X.shape[0] / (ms * 1e-3)   # 3 + 2 + 2 + 2 GP evaluations
     # tightening recursion on its own, 65536 rollouts x 25 stages (variances resident)
     R2, T2 = 65536, 25
     A = (torch.eye(nx, dtype=torch.float64) + 0.02 * torch.randn(nx, nx, generator=g, dtype=torch.float64)).to(dev)

@@ -254,8 +254,9 @@ static int launch_tighten(const TightenArgs& a, cudaStream_t st) {
 // restated from its use at gpmpc.py:128-146 and the parameter names of scripts/gp_mpc_config.yaml:9-17):
 //   acc = a u0 + b along the same rotation column as res_dyn, minus g on z;  ddphi = c phi + d dphi + e u1;
 //   ddtheta = f theta + h dtheta + l u2;  ddpsi = yc psi + yd dpsi + ye u3 (zero unless given).
-// Each of the four RK4 sub-steps is one launch of gpk_predict_mean_jac for the three GPs (the GP sums dominate) and
-// one launch of stage_step_kernel: sixteen threads per pair, thread c carrying column c of d k_s / d(x, u).
+// Each of the four RK4 sub-steps is one launch of gpk_predict_mean_jac (three GPs at the first sub-step, then only the
+// roll and pitch GPs: the thrust GP's input u0 is constant along the step; the GP sums dominate) and one launch of
+// stage_step_kernel: sixteen threads per pair, thread c carrying column c of d k_s / d(x, u).
 // ------------------------------------------------------------------------------------------------------------
 constexpr int ST_NX = 12, ST_NU = 4, ST_NC = ST_NX + ST_NU, ST_GD = 3;
 enum { PR_A = 0, PR_B, PR_C, PR_D, PR_E, PR_F, PR_H, PR_L, PR_G, PR_YC, PR_YD, PR_YE, PR_COUNT };
@@ -462,8 +463,14 @@ extern "C" int gpk_stage_rk4(const double* x, long ldx, const double* u, long ld
         a.xs_in = xs1; a.xs_out = xs0;
         GPK_TRY(launch_stage_step<0>(a, st));
         for (int s = 1; s <= 4; s++) {
-            GPK_TRY(gpk_predict_mean_jac(1, Zg, ST_GD, qn, qn * ST_GD, ST_GD, hyp, pack, stride_pack, n, mean, qn, jac,
-                                         ST_GD, qn * ST_GD, mj_bytes > 0 ? mj_work : nullptr, mj_bytes > 0 ? mj_bytes : 0, 3, st));
+            // the thrust GP's input z[idx_T] = u0 does not move along the RK4 sub-steps: it is evaluated once, the
+            // roll and pitch GPs (inputs phi / theta and their rates) at every sub-step
+            const int g0 = s == 1 ? 0 : 1;
+            const size_t esz = sizeof(double);
+            GPK_TRY(gpk_predict_mean_jac(1, Zg + g0 * qn * ST_GD, ST_GD, qn, qn * ST_GD, ST_GD, hyp + g0 * HYP_STRIDE,
+                                         static_cast<const char*>(pack) + g0 * stride_pack * esz, stride_pack, n,
+                                         mean + g0 * qn, qn, jac + g0 * qn * ST_GD, ST_GD, qn * ST_GD,
+                                         mj_bytes > 0 ? mj_work : nullptr, mj_bytes > 0 ? mj_bytes : 0, 3 - g0, st));
             a.xs_in = (s & 1) ? xs0 : xs1;
             a.xs_out = (s & 1) ? xs1 : xs0;
             switch (s) {

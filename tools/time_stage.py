@@ -30,6 +30,6 @@ for _ in range(reps):
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / reps
-pairs = 4 * 3 * Q * N
+pairs = 9 * Q * N   # three GPs at the first sub-step, two at the other three
 print(f"Q={Q} N={N}: {ms:.3f} ms/call  {Q / ms * 1e3:.3e} stage evals/s  {pairs / ms / 1e6:.1f} G kernel pairs/s  "
       f"launches/call {lib.gpk_launch_count() / reps:.0f}")
