@@ -50,6 +50,8 @@ SIGNATURES = {
     "gpk_predict_i8_work_bytes": (_l, [_l, _l, _i, _i, _i]),
     "gpk_predict_i8": (_i, [_i, _p, _l, _l, _l, _i, _p, _p, _l, _l, _l, _p, _l, _p, _l, _p, _l, _l, _i,
                             _p, _l, _p, _l, _l, _p, _l, _p, _l, _i, _p, _p]),
+    "gpk_mean_jac_dmma_work_bytes": (_l, [_l, _i, _i]),
+    "gpk_predict_mean_jac_dmma": (_i, [_i, _p, _l, _l, _l, _i, _p, _p, _l, _l, _l, _p, _l, _p, _l, _p, _l, _l, _p, _l, _i, _p]),
     "gpk_oz_var_partials": (_i, [_p, _l, _p, _l, _p, _l, _p, _l, _l, _i, _p, _l, _l, _i, _i, _p, _p]),
     "gpk_oz_query_tile": (_i, []),
     "gpk_oz_pieces": (_i, [_l, _l]),

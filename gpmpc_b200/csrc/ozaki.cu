@@ -166,6 +166,7 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     for (int i = tid; i < EXP_TAB; i += 256) exp_tab[i] = a.exp_tab[i];   // visible after the first barrier below
     const int g = lane >> 2, t = lane & 3;
+    const bool write_img = a.img != nullptr;             // mean + Jacobian only when no image is wanted
 
     // A fragments of GEMM 1 (scaled queries) for the two 8-query blocks of this warp
     double za[2][KS], ezq[2];
@@ -269,11 +270,13 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
                 double e[4];
 #pragma unroll
                 for (int i = 0; i < 4; i++) e[i] = qv[mb] ? exp_neg_tab(fmin(c[i >> 1][i & 1], 0.0), exp_tab) : 0.0;
-                uint32_t w[S];
-                oz_pack_digits4<S>(e, w);
-                int8_t* dst = out + oz_tile_off(qrow[mb], unit * 16 + 4 * t);
+                if (write_img) {
+                    uint32_t w[S];
+                    oz_pack_digits4<S>(e, w);
+                    int8_t* dst = out + oz_tile_off(qrow[mb], unit * 16 + 4 * t);
 #pragma unroll
-                for (int s_ = 0; s_ < S; s_++) *reinterpret_cast<uint32_t*>(dst + (long)s_ * OZ_A_SLICE) = w[s_];
+                    for (int s_ = 0; s_ < S; s_++) *reinterpret_cast<uint32_t*>(dst + (long)s_ * OZ_A_SLICE) = w[s_];
+                }
                 if (MJ) {
 #pragma unroll
                     for (int i = 0; i < 4; i++) {
@@ -743,6 +746,9 @@ static int oz_front_dispatch(const OzFrontArgs& a_in, int S, bool mj, int n_spli
     return fail(-1, "digits must be 4, 5 or 6");
 }
 
+constexpr int OZ_SLOTS = 2 * OZ_MAX_PIECES;
+constexpr int OZ_MAX_SPLITS = 16;
+
 extern "C" {
 
 int gpk_oz_default_digits(void) { return 5; }
@@ -794,6 +800,50 @@ int gpk_oz_cross(int dtype, const void* Z, long ldz, long q, long strideZ, const
     return oz_front_dispatch<double>(a, S, false, ns, qtiles, batch, nullptr, 0, nullptr, 0, 0, (cudaStream_t)stream);
 }
 
+// mean + Jacobian alone on the DMMA front kernel (no digit image, no variance): the want_var = false path for fp64
+long gpk_mean_jac_dmma_work_bytes(long q_chunk, int d, int batch) {
+    if (q_chunk <= 0 || d < 1 || d > HYP_MAXD || batch < 1) return -1;
+    const long qc = (q_chunk + OZ_QT - 1) / OZ_QT * OZ_QT;
+    return (long)OZ_MAX_SPLITS * qc * (oz_pad_dim(d) + 1) * 8 * batch;
+}
+
+int gpk_predict_mean_jac_dmma(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                              const double* X, long ldx, long n, long strideX, const double* alpha, long stride_alpha,
+                              void* mean, long stride_mean, void* jac, long ldj, long stride_jac, void* work,
+                              long work_bytes, int batch, void* stream) {
+    GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
+    GPK_ARG(Z && hyp && X && alpha && mean && jac && work, "null pointer");
+    GPK_ARG(d >= 1 && d <= HYP_MAXD && n > 0 && batch >= 1 && ldj >= d, "n / d / batch / ldj");
+    if (q == 0) return 0;
+    const int dp = oz_pad_dim(d);
+    const long per_q = (long)OZ_MAX_SPLITS * (dp + 1) * 8 * batch;
+    long qc = work_bytes / per_q / OZ_QT * OZ_QT;
+    GPK_ARG(qc >= OZ_QT, "scratch too small (see gpk_mean_jac_dmma_work_bytes)");
+    const long q_round = (q + OZ_QT - 1) / OZ_QT * OZ_QT;
+    if (qc > q_round) qc = q_round;
+    const int esz = dtype == 0 ? 4 : 8;
+    cudaStream_t st = (cudaStream_t)stream;
+    for (long q0 = 0; q0 < q; q0 += qc) {
+        const long qn = (q - q0 < qc) ? (q - q0) : qc;
+        const long qtiles = (qn + OZ_QT - 1) / OZ_QT;
+        OzFrontArgs a{};
+        a.Z = (const char*)Z + q0 * ldz * esz; a.ldz = ldz; a.q = qn; a.strideZ = strideZ;
+        a.X = X; a.ldx = ldx; a.n = n; a.strideX = strideX;
+        a.alpha = alpha; a.stride_alpha = stride_alpha;
+        a.d = d; a.hyp = hyp;
+        a.img = nullptr; a.strideE = 0;
+        a.kb_total = (int)((n + OZ_BK - 1) / OZ_BK);
+        const int ns = oz_front_splits(qtiles * batch, a.kb_total);
+        a.kb_per_cta = (a.kb_total + ns - 1) / ns;
+        a.mj_part = (double*)work; a.stride_mj = (long)OZ_MAX_SPLITS * qc * (dp + 1);
+        void* mout = (char*)mean + q0 * esz;
+        void* jout = (char*)jac + q0 * ldj * esz;
+        if (dtype == 0) GPK_TRY(oz_front_dispatch<float>(a, OZ_MIN_S, true, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
+        else GPK_TRY(oz_front_dispatch<double>(a, OZ_MIN_S, true, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
+    }
+    return 0;
+}
+
 // part[gp][slot][q], slot < 2 n_pieces: sums of V[i][q]^2 over disjoint sets of W rows (V = sf2 W E^T);
 // their sum over the slots is || W k(X, z_q) ||^2.  n_pieces = gpk_oz_pieces()
 int gpk_oz_var_partials(const void* Eimg, long strideE, const void* Wimg, long strideW, const double* wscale,
@@ -839,8 +889,6 @@ int gpk_oz_var_partials(const void* Eimg, long strideE, const void* Wimg, long s
 // and the int8 digit image for the tcgen05 variance contraction  var_f(z) = sf2 - || W k(X,z) ||^2.
 // mean / jac may be NULL (variance only).  Queries go through in chunks that fit `work`.  mj_done_event
 // (cudaEvent_t or NULL) is recorded once mean and jac are complete.
-constexpr int OZ_SLOTS = 2 * OZ_MAX_PIECES;
-constexpr int OZ_MAX_SPLITS = 16;
 
 long gpk_predict_i8_work_bytes(long q_chunk, long npad, int d, int S, int batch) {
     const long qc = (q_chunk + OZ_QT - 1) / OZ_QT * OZ_QT;

@@ -139,6 +139,13 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
                    const void* Wimg, long strideW, const double* wscale, long stride_ws, long npad, int digits,
                    void* mean, long stride_mean, void* jac, long ldj, long stride_jac, void* var, long stride_var,
                    void* work, long work_bytes, int batch, void* mj_done_event, void* stream);
+/* mean + Jacobian alone on the same DMMA front kernel (no digit image, no variance): the want_var = false path in
+ * float64 for d >= 9, where it is faster than the SIMT kernel of (6).  Takes X and alpha directly (no pack). */
+long gpk_mean_jac_dmma_work_bytes(long q_chunk, int d, int batch);
+int gpk_predict_mean_jac_dmma(int dtype, const void* Z, long ldz, long q, long strideZ, int d, const double* hyp,
+                              const double* X, long ldx, long n, long strideX, const double* alpha,
+                              long stride_alpha, void* mean, long stride_mean, void* jac, long ldj, long stride_jac,
+                              void* work, long work_bytes, int batch, void* stream);
 /* the two stages of (6+7) on their own, for tests and bench.py:
  *   gpk_oz_cross         queries -> int8 digit image of E = exp(-r^2/2), [batch][qpad/128][npad/64][digits][128x64]
  *   gpk_oz_var_partials  part[gp][slot][q], slot < 2 n_pieces: sums of (W k)_i^2 over disjoint sets of rows i;

@@ -201,3 +201,36 @@ def test_predict_host_roundtrip():
     ref = E.predict(gb, p["Z"].to(dev))
     assert all(not t.is_cuda and t.is_pinned() for t in out)
     assert all(torch.equal(a, b.cpu()) for a, b in zip(out, ref))
+
+
+@pytest.mark.parametrize("n,d,q,B", [(700, 16, 333, 1), (2048, 16, 1500, 3), (130, 9, 5, 2), (64, 32, 129, 1)])
+def test_mean_jacobian_only_dmma_path(n, d, q, B):
+    """want_var=False in float64 for d > 8 runs on the DMMA front kernel without the digit image; same numbers as the
+    SIMT kernel and the oracle, also with a scratch that forces several query chunks."""
+    from gpmpc_b200 import _lib
+    from gpmpc_b200 import engine as E
+    from gpmpc_b200._lib import call, ptr
+    p = o.synthetic_problem(n, d, q, p=B, seed=n + d)
+    gb = E.fit_batch(p["X"].cuda(), p["Y"].cuda(), p["ell"], p["sf2"], p["noise"])
+    Z = p["Z"].cuda()
+    m1, v1, j1 = E.predict(gb, Z, want_var=False)                       # DMMA
+    m2, v2, j2 = E.predict(gb, Z, want_var=False, mj_path="simt")
+    assert v1 is None and v2 is None
+    assert o.rel_err(m1.cpu(), m2.cpu()) < 1e-12 and o.rel_err(j1.cpu(), j2.cpu()) < 1e-12
+    for b in range(B):
+        st = o.fit_state(p["X"], p["Y"][:, b], p["ell"], p["sf2"], p["noise"])
+        mr, _, jr = o.predict(p["Z"], p["X"], p["ell"], p["sf2"], st["L"], st["alpha"])
+        assert o.rel_err(m1[b].cpu(), mr) < 1e-9 and o.rel_err(j1[b].cpu(), jr) < 1e-9
+    # straight through the C ABI with room for 128 queries per chunk only
+    lib = _lib.load()
+    wb = lib.gpk_mean_jac_dmma_work_bytes(128, d, B)
+    work = torch.empty(wb, dtype=torch.uint8, device="cuda")
+    mean = torch.full((B, q), float("nan"), dtype=torch.float64, device="cuda")
+    jac = torch.full((B, q, d), float("nan"), dtype=torch.float64, device="cuda")
+    alpha = gb.alpha
+    call("gpk_predict_mean_jac_dmma", 1, ptr(Z), Z.stride(0), q, 0, d, ptr(gb.hyp), ptr(gb.X), gb.X.stride(1), n,
+         gb.X.stride(0) if B > 1 else 0, ptr(alpha), alpha.stride(0), ptr(mean), q, ptr(jac), d, q * d, ptr(work), wb, B,
+         torch.cuda.current_stream().cuda_stream)
+    # (the k-split count follows the chunk size, so the summation order differs: equal to rounding, not bitwise)
+    assert o.rel_err(mean.cpu(), m1.cpu()) < 1e-13 and o.rel_err(jac.cpu(), j1.cpu()) < 1e-13
+    assert not torch.isnan(mean).any() and not torch.isnan(jac).any()
