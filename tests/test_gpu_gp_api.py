@@ -234,3 +234,29 @@ def test_mean_jacobian_only_dmma_path(n, d, q, B):
     # (the k-split count follows the chunk size, so the summation order differs: equal to rounding, not bitwise)
     assert o.rel_err(mean.cpu(), m1.cpu()) < 1e-13 and o.rel_err(jac.cpu(), j1.cpu()) < 1e-13
     assert not torch.isnan(mean).any() and not torch.isnan(jac).any()
+
+
+@pytest.mark.parametrize("n,d,q", [(300, 5, 77), (1000, 16, 400)])
+def test_variance_paths_agree(n, d, q, monkeypatch):
+    """The three variance paths -- tcgen05 int8 digits (default), FP64 DMMA (`var_path="f64"`), and the automatic
+    fallback to DMMA when the training set is too large for exact int32 accumulation -- against the oracle."""
+    from gpmpc_b200 import engine as E
+    p = o.synthetic_problem(n, d, q, p=1, seed=n)
+    X, y, Z = p["X"].cuda(), p["Y"][:, 0].cuda(), p["Z"].cuda()
+    st = o.fit_state(p["X"], p["Y"][:, 0], p["ell"], p["sf2"], p["noise"])
+    _, vr, _ = o.predict(p["Z"], p["X"], p["ell"], p["sf2"], st["L"], st["alpha"])
+    fit, _ = E.factorize(X, y, p["ell"], p["sf2"], p["noise"])
+    v_i8 = E.predict(fit, Z)[1][0].cpu()
+    v_f64 = E.predict(fit, Z, var_path="f64")[1][0].cpu()
+    assert o.rel_err(v_i8, vr) < 1e-7 and o.rel_err(v_f64, vr) < 1e-9
+    for S in (4, 6):
+        fs, _ = E.factorize(X, y, p["ell"], p["sf2"], p["noise"], digits=S)
+        assert o.rel_err(E.predict(fs, Z)[1][0].cpu(), vr) < {4: 1e-5, 6: 1e-9}[S]
+    # a fit without digit image at a size the int8 path cannot take: predict() switches to the DMMA path by itself
+    monkeypatch.setattr(E, "i8_supported", lambda npad, digits=None: False)
+    fit2, _ = E.factorize(X, y, p["ell"], p["sf2"], p["noise"])
+    assert fit2.wimg is None
+    m2, v2, j2 = E.predict(fit2, Z)
+    assert torch.equal(v2[0].cpu(), v_f64)
+    monkeypatch.undo()
+    assert E.i8_supported(26112) and not E.i8_supported(26240) and E.i8_supported(26240, 4) and not E.i8_supported(32768, 4)
