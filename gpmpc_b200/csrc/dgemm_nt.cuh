@@ -83,10 +83,12 @@ __device__ __forceinline__ void tile_coords(const GemmParams& p, int id, int& tm
 
 // Tile configurations: BM x BN CTA tile, WM x WN warps, warp tile (BM/WM) x (BN/WN) = FM x FN DMMA fragments.
 //   128 x 128 (2 x 4 warps, 64 x 32 warp tiles): the throughput configuration
-//    64 x  64 (2 x 2 warps, 32 x 32): 4x the CTAs for the many small GEMMs of the recursive factorisations --
-//              one SM only sustains ~0.25 TFLOP/s of DMMA, so a GEMM with a handful of tiles is bound by that
-//    32 x 128 (1 x 4 warps, 32 x 32): for the in-place TRSM leaves (C aliases A; a CTA must own all 128
-//              columns of its rows), 4x the CTAs along M
+//    32 x  32 (2 x 2 warps, 16 x 16): every GEMM with fewer than ~100 128-tiles, i.e. the many small GEMMs of the
+//              recursive factorisations -- one SM only sustains ~0.25 TFLOP/s of DMMA, so a GEMM with a handful of
+//              tiles is bound by that and wants as many CTAs as possible (measured at N=2048: MLL iteration
+//              3.65 ms with 64 x 64 tiles, 3.17 ms with 32 x 32)
+//    16 x 128 (1 x 4 warps, 16 x 32): for the in-place TRSM leaves (C aliases A; a CTA must own all 128
+//              columns of its rows), 8x the CTAs along M
 template <int EPI, int BM, int BN, int WM, int WN>
 __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
     extern __shared__ __align__(16) double smem[];
@@ -230,8 +232,8 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
 
 // EPI 0: C = beta C + alpha A B^T (potrf / trtri / K^-1 building block)
 __global__ void __launch_bounds__(G_THREADS, 1) dgemm_nt_kernel(const GemmParams p) { dgemm_nt_body<0, 128, 128, 2, 4>(p); }
-__global__ void __launch_bounds__(128, 2) dgemm_nt64_kernel(const GemmParams p) { dgemm_nt_body<0, 64, 64, 2, 2>(p); }
-__global__ void __launch_bounds__(128, 2) dgemm_nt32x128_kernel(const GemmParams p) { dgemm_nt_body<0, 32, 128, 1, 4>(p); }
+__global__ void __launch_bounds__(128, 4) dgemm_nt32_kernel(const GemmParams p) { dgemm_nt_body<0, 32, 32, 2, 2>(p); }
+__global__ void __launch_bounds__(128, 2) dgemm_nt16x128_kernel(const GemmParams p) { dgemm_nt_body<0, 16, 128, 1, 4>(p); }
 // EPI 1: posterior-variance contraction, column sums of squares of W K_ZX^T (DMMA variance path)
 __global__ void __launch_bounds__(G_THREADS, 1) var_colsq_kernel(const GemmParams p) { dgemm_nt_body<1, 128, 128, 2, 4>(p); }
 

@@ -9,6 +9,7 @@
 //   kinv    : K^-1 = U U^T (lower tiles on the tensor pipe, mirrored afterwards)
 //   alpha   : t = W y, alpha = U t (two triangular GEMVs, HBM-bound), quad = |t|^2, logdet = 2 sum log L_ii
 // All matrices are row-major, padded to a multiple of 128 with an identity block (see engine.py).
+#include <cstdlib>
 #include "dgemm_nt.cuh"
 #include <type_traits>
 
@@ -41,8 +42,8 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
     const long tiles128 = (long)(p.M / G_BM) * (p.N / G_BN) * batch / (p.c_lower ? 2 : 1);
     int bm = G_BM, bn = G_BN;
     if (epilogue == 0 && tiles128 < 100) {
-        if (p.c_inplace) { bm = 32; bn = 128; }
-        else { bm = 64; bn = 64; }
+        if (p.c_inplace) { bm = 16; bn = 128; }
+        else { bm = 32; bn = 32; }
     }
     GPK_ARG(!p.c_inplace || p.N == bn, "in-place GEMM needs a single tile column");
     p.tiles_m = p.M / bm;
@@ -67,8 +68,8 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
     if (!attr_done) {
         GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
         GPK_CUDA(cudaFuncSetAttribute(var_colsq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
-        GPK_CUDA(cudaFuncSetAttribute(dgemm_nt64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
-        GPK_CUDA(cudaFuncSetAttribute(dgemm_nt32x128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+        GPK_CUDA(cudaFuncSetAttribute(dgemm_nt32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
+        GPK_CUDA(cudaFuncSetAttribute(dgemm_nt16x128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
         attr_done = true;
     }
     const int smem = G_STAGES * (bm + bn) * G_ROW * 8;
@@ -76,10 +77,10 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
         var_colsq_kernel<<<grid, G_THREADS, smem, st>>>(p);
     else if (bm == 128)
         dgemm_nt_kernel<<<grid, G_THREADS, smem, st>>>(p);
-    else if (bm == 64)
-        dgemm_nt64_kernel<<<grid, 128, smem, st>>>(p);
+    else if (bn == 32)
+        dgemm_nt32_kernel<<<grid, 128, smem, st>>>(p);
     else
-        dgemm_nt32x128_kernel<<<grid, 128, smem, st>>>(p);
+        dgemm_nt16x128_kernel<<<grid, 128, smem, st>>>(p);
     GPK_LAUNCHED();
     return 0;
 }

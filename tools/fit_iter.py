@@ -7,7 +7,7 @@ N = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 D = 16
 g = torch.Generator().manual_seed(1337)
 X = (torch.rand(N, D, generator=g, dtype=torch.float64) * 2 - 1).to(dev)
-y = torch.sin(X @ torch.randn(D, dtype=torch.float64, device=dev))
+y = torch.sin(X @ torch.randn(D, generator=g, dtype=torch.float64).to(dev))
 ell = torch.full((D,), 2.0, dtype=torch.float64)
 def it():
     fit, ws = E.factorize(X, y, ell, 1.0, 1e-2, want_kinv=True, want_image=False)
