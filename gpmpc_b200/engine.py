@@ -223,17 +223,19 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
         call("gpk_cross_kernel", 1, ptr(X), X.stride(0), n, 0, ptr(X), X.stride(0), n, 0, d, ptr(hyp), ptr(ws.L),
              npad, 0, npad, npad, 1, 1, st)
         call("gpk_potrf", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(ws.info), st)
+        # the rest of the chain is enqueued before the pivot check is read back (one host round trip per fit instead of
+        # two; a failed factorisation is rare and only costs the wasted launches)
+        call("gpk_trtri", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(W), npad, ptr(ws.U), npad, ptr(ws.T), ws.T.numel(), st)
+        call("gpk_solve_alpha", ptr(W), npad, ptr(ws.U), npad, ptr(ws.L), npad, npad, ptr(ws.y_pad), ptr(ws.t_work),
+             ptr(alpha), ptr(ws.scal), st)
+        if want_kinv:
+            call("gpk_kinv", ptr(ws.U), npad, npad, ptr(ws.need_kinv()), npad, st)
         info = int(ws.info.item())          # the reference syncs here too (loss value / NotPSD check)
         if info == 0:
             break
         if attempt == max_tries:
             raise NotPSDError(f"K + noise I not positive definite after jitter {jitter:g} (potrf info={info})")
         jitter = 1e-8 if jitter == 0.0 else jitter * 10.0
-    call("gpk_trtri", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(W), npad, ptr(ws.U), npad, ptr(ws.T), ws.T.numel(), st)
-    call("gpk_solve_alpha", ptr(W), npad, ptr(ws.U), npad, ptr(ws.L), npad, npad, ptr(ws.y_pad), ptr(ws.t_work),
-         ptr(alpha), ptr(ws.scal), st)
-    if want_kinv:
-        call("gpk_kinv", ptr(ws.U), npad, npad, ptr(ws.need_kinv()), npad, st)
     wimg = wscale = None
     if want_image and i8_supported(npad, digits):
         wimg, wscale, digits = slice_w(W, npad, digits, wimg_out, wscale_out)
