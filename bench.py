@@ -333,8 +333,8 @@ def measure_roofline(gb, Z, flush, dev, steps):
     return {"kernel": f"oz_var_kernel<{S}> (variance contraction W K_ZX^T, {S}-digit int8 slices on tcgen05, int32 TMEM "
                       "accumulators, fp64 recombination)",
             "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TOP/s (int8)", "frac": achieved / peak,
-            "traffic": ncu_dram_bytes("ncu_oz_var_kernel_S5_r01_v3.csv") if S == 5 else None,
-            "traffic_unit": "bytes per launch (dram read + write, ncu --set full, profiles/ncu_oz_var_kernel_S5_r01_v3.csv)",
+            "traffic": ncu_dram_bytes("ncu_oz_var_kernel_S5_r01_v6.csv") if S == 5 else None,
+            "traffic_unit": "bytes per launch (dram read + write, ncu --set full, profiles/ncu_oz_var_kernel_S5_r01_v6.csv)",
             "algorithmic_bytes_per_launch": float(B) * S * npad * (qp + npad),
             "ms_per_launch": ms, "algorithmic_int8_ops_per_launch": int8_ops,
             "fp64_equivalent_tflops": fp64_flops / (ms * 1e-3) / 1e12, "fp64_dmma_peak_tflops": DMMA_PEAK_TFLOPS,

@@ -342,7 +342,13 @@ def _loss_and_set_grads(gp: GaussianProcess, dev: torch.device, W_buf: torch.Ten
     .grad (replaces output = gp(train_x); loss = -mll(output, y); loss.backward(), gpmpc/gp.py:61-63)."""
     ell, sf2, noise = gp.hyperparameters()
     X = gp.train_inputs[0]
-    fit, ws = E.factorize(X.to(dev), gp.train_targets.to(dev), ell, sf2, noise, want_kinv=True, W_out=W_buf,
+    cache = getattr(gp, "_fit_cache", None)
+    if cache is None or cache[0] is not X or cache[4] is not gp.train_targets:
+        # training data on the compute device and its centre (read back once per fit, not once per iteration)
+        Xd = X.detach().to(dev, torch.float64).contiguous()
+        cache = gp._fit_cache = (X, Xd, gp.train_targets.detach().to(dev, torch.float64).contiguous(), Xd.mean(dim=0).cpu(),
+                                 gp.train_targets)
+    fit, ws = E.factorize(cache[1], cache[2], ell, sf2, noise, center=cache[3], want_kinv=True, W_out=W_buf,
                           want_image=False)
     if grad_reduce is None:
         partials = E.grad_partials(fit, ws)
@@ -392,6 +398,7 @@ def fit_gp(gp: GaussianProcess, n_train=500, lr=0.01, device: str = "cpu", *, co
             break
         last_loss = loss
     del W_buf
+    gp._fit_cache = None
     if compute_covariances:
         gp.K, gp.K_inv = gp.compute_covariances()
 
