@@ -97,19 +97,19 @@ static GemmParams gemm_args(const double* A, long lda, const double* B, long ldb
 }
 
 // ------------------------------------------------------------------------------------------------
-// 128x128 leaf: Cholesky of a diagonal block in shared memory + inverse of its factor
+// 128x128 leaf: Cholesky of a diagonal block (one CTA) + inverse of its factor (16 CTAs)
 // ------------------------------------------------------------------------------------------------
 constexpr int P_N = 128, P_LD = 129, P_B = 8, P_NB = P_N / P_B, P_THREADS = 160;
-// shared memory: L (row-major, P_LD) | inverses of the 16 diagonal 8x8 factors | 1/l_jj | current panel
-// (column-major, permuted) | two published row blocks of X (permuted)
-constexpr int P_SMEM = (P_N * P_LD + P_NB * P_B * P_B + P_N + P_B * P_N + 2 * P_B * P_N) * 8;
+// shared memory of the Cholesky kernel: diagonal blocks of L (row-major, P_LD) | 1/l_jj | current panel (column-major,
+// permuted)
+constexpr int P_SMEM = (P_N * P_LD + P_N + P_B * P_N) * 8;
 // position of element R = 8 t + c inside a 128-vector read as double2 pairs by 16 consecutive block indices t:
 // pair p = c / 2 of block t sits at doubles [32 p + 2 t, 32 p + 2 t + 1]
 __device__ __forceinline__ int p_perm(int R) { return ((R & 7) >> 1) * 32 + (R >> 3) * 2 + (R & 7 & 1); }
 
 // Thread -> 8x8 block of the lower triangle (136 blocks, 160 threads).  Warps 0-3 (one per SM sub-partition) share
 // the blocks that take part in the rank-8 updates, dealt round-robin so that every step keeps the four warps evenly
-// loaded; warp 4 holds the 16 blocks that never take part in them (phase 1: block column 0; phase 2: the diagonal).
+// loaded; warp 4 holds the 16 blocks that never take part in them (block column 0).
 __device__ __forceinline__ void p_map1(int t, int& ty, int& tx) {
     const int w = t >> 5, l = t & 31;
     ty = tx = -1;
@@ -121,34 +121,16 @@ __device__ __forceinline__ void p_map1(int t, int& ty, int& tx) {
     tx = 15 - m;
     ty = tx + (i - m * (m + 1) / 2);
 }
-__device__ __forceinline__ void p_map2(int t, int& ty, int& tx) {
-    const int w = t >> 5, l = t & 31;
-    ty = tx = -1;
-    if (w == 4) { if (l < 16) { ty = l; tx = l; } return; }
-    const int i = l * 4 + w;                  // index into the off-diagonal blocks, ordered by (tx, ty) ascending
-    if (i >= 120) return;
-    int c = 0, before = 0;
-    while (before + (15 - c) <= i) { before += 15 - c; c++; }
-    tx = c;
-    ty = c + 1 + (i - before);
-}
-
-// Each thread keeps one 8 x 8 block of the lower triangle in REGISTERS.  Blocked right-looking algorithms with block
-// size 8, so the 128 sequential pivots cost 16 block steps:
-//   phase 1  Cholesky, step kb: (a) the owner of the diagonal block factors it in registers; (b) the blocks below it
-//            become L_ik = A_ik L_kk^-T by forward substitution and are published as the panel; (c) every lower block
-//            right of the panel does A_ic -= L_ik L_ck^T (512 FMAs)
-//   phase 2  X = L^-1 by blocked forward elimination of [L | I]: the 16 diagonal 8 x 8 factors are inverted at once,
-//            then step j: (a) block row j is finished, X_jk = L_jj^-1 R_jk, and published; (b) rows below do
-//            R_ik -= L_ij X_jk (512 FMAs)
-// Two barriers per block step in phase 1, one in phase 2 (published rows are double-buffered).
+// Cholesky of a 128 x 128 leaf.  Each thread keeps one 8 x 8 block of the lower triangle in REGISTERS; blocked
+// right-looking with block size 8, so the 128 sequential pivots cost 16 block steps:  step kb: (a) the owner of the
+// diagonal block factors it in registers; (b) the blocks below it become L_ik = A_ik L_kk^-T by forward substitution
+// and are published as the panel; (c) every lower block right of the panel does A_ic -= L_ik L_ck^T (512 FMAs).
+// Two barriers per block step.  The inverse of the factor is a separate kernel (leaf_inv_kernel below).
 __global__ void __launch_bounds__(P_THREADS, 1)
-potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, int* __restrict__ info, int row_offset) {
+potf2_kernel(double* __restrict__ A, long lda, int* __restrict__ info, int row_offset) {
     extern __shared__ __align__(16) double S[];
-    double* D8 = S + P_N * P_LD;                         // [16][8][8] inverse of the diagonal factors (lower)
-    double* dinv = D8 + P_NB * P_B * P_B;                // [128] 1 / l_jj
+    double* dinv = S + P_N * P_LD;                       // [128] 1 / l_jj
     double* Pn = dinv + P_N;                             // [8][128] panel, Pn[k][perm(R)] = L[R][8 kb + k]
-    double* Xs = Pn + P_B * P_N;                         // [2][8][128] row block j of X, Xs[j&1][r][perm(C)]
     const int tid = threadIdx.x;
     int ty, tx;
     p_map1(tid, ty, tx);
@@ -229,14 +211,11 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
         }
         __syncthreads();
         if (panel) {
-            // off the critical path: the finished block goes to shared memory (phase 2) and back to global memory
+            // off the critical path: the finished block goes back to global memory
 #pragma unroll
             for (int r = 0; r < 8; r++)
 #pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    S[(r0 + r) * P_LD + c0 + c] = a[r][c];
-                    A[(long)(r0 + r) * lda + c0 + c] = a[r][c];
-                }
+                for (int c = 0; c < 8; c++) A[(long)(r0 + r) * lda + c0 + c] = a[r][c];
         }
         if (tx > kb && ty >= tx) {
             // (c) trailing update of the lower blocks with the published panel
@@ -258,106 +237,102 @@ potf2_inv_kernel(double* __restrict__ A, long lda, double* __restrict__ Dinv, in
         }
         // no barrier here: the panel is rewritten only after the next step's first barrier
     }
+}
+
+// X = L^-1 of a factored 128 x 128 leaf, one CTA per 8-wide block column k: the 16 block columns of the inverse are
+// independent forward substitutions,  X_kk = L_kk^-1,  X_jk = -L_jj^-1 sum_{k <= m < j} L_jm X_mk  for j > k.
+// 256 threads = 4 groups x (8 x 8 entries); group g takes the terms m = k + g, k + g + 4, ... of the sum.
+// This used to be the second half of the leaf kernel (one SM, ~35 us); as 16 CTAs it is ~6 us of the critical path.
+constexpr int PI_THREADS = 256;
+constexpr int PI_SMEM = (P_N * P_LD + 2 * P_NB * 64 + 4 * 64 + P_N) * 8;
+__global__ void __launch_bounds__(PI_THREADS)
+leaf_inv_kernel(const double* __restrict__ L, long ldl, double* __restrict__ Dinv) {
+    extern __shared__ __align__(16) double S[];
+    double* D8 = S + P_N * P_LD;              // [16][8][8] inverses of the diagonal 8 x 8 factors
+    double* Xs = D8 + P_NB * 64;              // [16][8][8] block column k of X
+    double* part = Xs + P_NB * 64;            // [4][64] partial sums of the groups
+    double* dinv = part + 4 * 64;             // [128] 1 / l_ii
+    const int tid = threadIdx.x, k = blockIdx.x;
+    const int g = tid >> 6, e = tid & 63, r = e >> 3, c = e & 7;
+    const int row_lo = k * 8;
+    // rows >= 8k of L (columns 8k .. row) into shared memory
+    for (int idx = tid; idx < (P_N - row_lo) * (P_N / 2); idx += PI_THREADS) {
+        const int row = row_lo + idx / (P_N / 2), cp = (idx % (P_N / 2)) * 2;
+        if (cp + 1 >= row_lo && cp <= row) {
+            const double2 v = *reinterpret_cast<const double2*>(L + (long)row * ldl + cp);
+            S[row * P_LD + cp] = v.x;
+            S[row * P_LD + cp + 1] = v.y;
+        }
+    }
     __syncthreads();
-    // ---- phase 2: X = L^-1 ----
-    p_map2(tid, ty, tx);
-    r0 = ty * 8; c0 = tx * 8;
-    if (ty >= 0 && ty == tx) {
-        // inverse of this diagonal 8 x 8 factor, column by column
-        const double* Lk = S + r0 * P_LD + c0;
+    if (tid < P_N - row_lo) dinv[row_lo + tid] = 1.0 / S[(row_lo + tid) * P_LD + row_lo + tid];
+    __syncthreads();
+    if (tid < P_NB - k) {
+        // inverse of the diagonal 8 x 8 factor j, column by column
+        const int j = k + tid;
+        const double* Lk = S + (j * 8) * P_LD + j * 8;
         double x[8][8];
 #pragma unroll
-        for (int c = 0; c < 8; c++) {
+        for (int cc = 0; cc < 8; cc++) {
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
-                if (r < c) x[r][c] = 0.0;
-                else if (r == c) x[r][c] = dinv[r0 + c];
+            for (int rr = 0; rr < 8; rr++) {
+                if (rr < cc) x[rr][cc] = 0.0;
+                else if (rr == cc) x[rr][cc] = dinv[j * 8 + cc];
                 else {
                     double sacc = 0.0;
 #pragma unroll
-                    for (int m = c; m < r; m++) sacc = fma(Lk[r * P_LD + m], x[m][c], sacc);
-                    x[r][c] = -dinv[r0 + r] * sacc;
+                    for (int m = cc; m < rr; m++) sacc = fma(Lk[rr * P_LD + m], x[m][cc], sacc);
+                    x[rr][cc] = -dinv[j * 8 + rr] * sacc;
                 }
             }
         }
 #pragma unroll
-        for (int r = 0; r < 8; r++)
+        for (int rr = 0; rr < 8; rr++)
 #pragma unroll
-            for (int c = 0; c < 8; c++) D8[(ty * 8 + r) * 8 + c] = x[r][c];
+            for (int cc = 0; cc < 8; cc++) D8[j * 64 + rr * 8 + cc] = x[rr][cc];
     }
-#pragma unroll
-    for (int r = 0; r < 8; r++)
-#pragma unroll
-        for (int c = 0; c < 8; c++) a[r][c] = (ty == tx && r == c) ? 1.0 : 0.0;
     __syncthreads();
-#pragma unroll 1
-    for (int j = 0; j < P_NB; j++) {
-        double* xs = Xs + (j & 1) * P_B * P_N;
-        if (ty == j) {
-            // (a) X_jk = L_jj^-1 R_jk:  x[r][c] = sum_{m <= r} d[r][m] a[m][c]
-            const double* dd = D8 + j * 64;
-            double x[8][8];
+    if (tid < 64) Xs[k * 64 + e] = D8[k * 64 + e];
+    __syncthreads();
+    for (int j = k + 1; j < P_NB; j++) {
+        double acc = 0.0;
+        for (int m = k + g; m < j; m += 4) {
+            const double* lrow = S + (j * 8 + r) * P_LD + m * 8;
+            const double* xm = Xs + m * 64 + c;
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
+            for (int i = 0; i < 8; i++) acc = fma(lrow[i], xm[i * 8], acc);
+        }
+        part[g * 64 + e] = acc;
+        __syncthreads();
+        if (tid < 64) {
+            const double* dd = D8 + j * 64 + r * 8;
+            double x = 0.0;
 #pragma unroll
-                for (int c = 0; c < 8; c++) x[r][c] = 0.0;
-#pragma unroll
-                for (int m = 0; m <= r; m++) {
-                    const double dv = dd[r * 8 + m];
-#pragma unroll
-                    for (int c = 0; c < 8; c++) x[r][c] = fma(dv, a[m][c], x[r][c]);
-                }
+            for (int i = 0; i <= 7; i++) {
+                const double tot = (part[i * 8 + c] + part[64 + i * 8 + c]) + (part[128 + i * 8 + c] + part[192 + i * 8 + c]);
+                x = fma(dd[i], tot, x);          // dd[i] = 0 for i > r
             }
-#pragma unroll
-            for (int r = 0; r < 8; r++)
-#pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    a[r][c] = x[r][c];
-                    xs[r * P_N + p_perm(c0 + c)] = x[r][c];
-                }
+            Xs[j * 64 + e] = -x;
         }
         __syncthreads();
-        if (ty > j && tx >= 0 && tx <= j) {
-            // (b) R_ik -= L_ij X_jk
-#pragma unroll
-            for (int m = 0; m < 8; m++) {
-                double lr[8], xr[8];
-#pragma unroll
-                for (int r = 0; r < 8; r++) lr[r] = S[(r0 + r) * P_LD + j * 8 + m];
-#pragma unroll
-                for (int p2 = 0; p2 < 4; p2++) {
-                    const double2 v = *reinterpret_cast<const double2*>(xs + m * P_N + p2 * 32 + tx * 2);
-                    xr[2 * p2] = v.x; xr[2 * p2 + 1] = v.y;
-                }
-#pragma unroll
-                for (int r = 0; r < 8; r++)
-#pragma unroll
-                    for (int c = 0; c < 8; c++) a[r][c] = fma(-lr[r], xr[c], a[r][c]);
-            }
-        }
     }
-    if (ty >= 0) {
-#pragma unroll
-        for (int r = 0; r < 8; r++)
-#pragma unroll
-            for (int c = 0; c < 8; c += 2)
-                *reinterpret_cast<double2*>(Dinv + (r0 + r) * P_N + c0 + c) = make_double2(a[r][c], a[r][c + 1]);
-    }
-    // the strict upper blocks of X are zero
-    for (int e = tid; e < P_NB * P_NB * 32; e += P_THREADS) {
-        const int blk = e >> 5, by = blk >> 4, bx = blk & 15, w = e & 31;
-        if (bx > by)
-            *reinterpret_cast<double2*>(Dinv + (by * 8 + (w >> 2)) * P_N + bx * 8 + (w & 3) * 2) = make_double2(0.0, 0.0);
+    // block column k of X: zero above the diagonal block
+    for (int idx = tid; idx < P_N * 8; idx += PI_THREADS) {
+        const int row = idx >> 3, cc = idx & 7, jb = row >> 3;
+        Dinv[row * P_N + k * 8 + cc] = jb < k ? 0.0 : Xs[jb * 64 + (row & 7) * 8 + cc];
     }
 }
 
 static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_offset, cudaStream_t st) {
     static bool attr_done = false;
     if (!attr_done) {
-        GPK_CUDA(cudaFuncSetAttribute(potf2_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+        GPK_CUDA(cudaFuncSetAttribute(potf2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
+        GPK_CUDA(cudaFuncSetAttribute(leaf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PI_SMEM));
         attr_done = true;
     }
-    potf2_inv_kernel<<<1, P_THREADS, P_SMEM, st>>>(A, lda, Dinv, info, row_offset);
+    potf2_kernel<<<1, P_THREADS, P_SMEM, st>>>(A, lda, info, row_offset);
+    GPK_LAUNCHED();
+    leaf_inv_kernel<<<P_NB, PI_THREADS, PI_SMEM, st>>>(A, lda, Dinv);
     GPK_LAUNCHED();
     return 0;
 }
