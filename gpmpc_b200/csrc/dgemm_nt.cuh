@@ -82,8 +82,10 @@ __device__ __forceinline__ void tile_coords(const GemmParams& p, int id, int& tm
 }
 
 // Tile configurations: BM x BN CTA tile, WM x WN warps, warp tile (BM/WM) x (BN/WN) = FM x FN DMMA fragments.
-//   128 x 128 (2 x 4 warps, 64 x 32 warp tiles): the throughput configuration
-//    32 x  32 (2 x 2 warps, 16 x 16): every GEMM with fewer than ~100 128-tiles, i.e. the many small GEMMs of the
+//   128 x 128 (2 x 4 warps, 64 x 32 warp tiles): the throughput configuration (variance GEMM, the largest fit GEMMs)
+//    64 x  64 (2 x 2 warps, 32 x 32): mid-size fit GEMMs (up to ~9000 128-tiles): their triangular k-ranges leave a
+//              128-tile grid waiting for its longest tile; 4x the CTAs balance better
+//    32 x  32 (2 x 2 warps, 16 x 16): every GEMM with fewer than ~200 128-tiles, i.e. the many small GEMMs of the
 //              recursive factorisations -- one SM only sustains ~0.25 TFLOP/s of DMMA, so a GEMM with a handful of
 //              tiles is bound by that and wants as many CTAs as possible (measured at N=2048: MLL iteration
 //              3.65 ms with 64 x 64 tiles, 3.17 ms with 32 x 32)
@@ -232,6 +234,7 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
 
 // EPI 0: C = beta C + alpha A B^T (potrf / trtri / K^-1 building block)
 __global__ void __launch_bounds__(G_THREADS, 1) dgemm_nt_kernel(const GemmParams p) { dgemm_nt_body<0, 128, 128, 2, 4>(p); }
+__global__ void __launch_bounds__(128, 2) dgemm_nt64_kernel(const GemmParams p) { dgemm_nt_body<0, 64, 64, 2, 2>(p); }
 __global__ void __launch_bounds__(128, 4) dgemm_nt32_kernel(const GemmParams p) { dgemm_nt_body<0, 32, 32, 2, 2>(p); }
 __global__ void __launch_bounds__(128, 2) dgemm_nt16x128_kernel(const GemmParams p) { dgemm_nt_body<0, 16, 128, 1, 4>(p); }
 // EPI 1: posterior-variance contraction, column sums of squares of W K_ZX^T (DMMA variance path)
