@@ -217,6 +217,10 @@ def run_b200(args):
     t0 = time.perf_counter()
     gb = E.fit_batch(X, Y, problem["ell"], problem["sf2"], problem["noise"])   # replicated fitted state
     torch.cuda.synchronize(dev)
+    fit_first_s = time.perf_counter() - t0       # includes one-time module loading and scratch allocation
+    t0 = time.perf_counter()
+    gb = E.fit_batch(X, Y, problem["ell"], problem["sf2"], problem["noise"])
+    torch.cuda.synchronize(dev)
     fit_s = time.perf_counter() - t0
     flush = l2_flusher(dev)
     preds_per_step = N_GP * N_QUERY
@@ -269,7 +273,7 @@ def run_b200(args):
         "config": {"workload": WORKLOAD, "per_gpu_queries": N_QUERY, "parallelism": f"query-sharded x{world}, state replicated",
                    "l2": "flushed (256 MB write) before every timed step"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": launches, "clocks": clocks, "fit_state_s": fit_s,
+        "gpu_launches": launches, "clocks": clocks, "fit_state_s": fit_s, "fit_state_first_call_s": fit_first_s,
     }
     if rank == 0:
         line["roofline"] = measure_roofline(gb, Z, flush, dev, args.steps)
