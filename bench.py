@@ -336,7 +336,8 @@ def measure_roofline(gb, Z, flush, dev, steps):
     peak = 2.0 * bf16 if bf16 else 2.0 * 1590.0
     return {"kernel": f"oz_var_kernel<{S}> (variance contraction W K_ZX^T, {S}-digit int8 slices on tcgen05, int32 TMEM "
                       "accumulators, fp64 recombination)",
-            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TOP/s (int8)", "frac": achieved / peak,
+            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+            "unit_note": "int8 tensor operations (multiply + add = 2 ops), i.e. TOP/s on the scale of the bf16 TFLOP/s peak x 2",
             "traffic": ncu_dram_bytes("ncu_oz_var_kernel_S5_r01_v6.csv") if S == 5 else None,
             "traffic_unit": "bytes per launch (dram read + write, ncu --set full, profiles/ncu_oz_var_kernel_S5_r01_v6.csv)",
             "algorithmic_bytes_per_launch": float(B) * S * npad * (qp + npad),
