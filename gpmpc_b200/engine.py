@@ -395,7 +395,8 @@ VAR_WORK_BYTES = 4 << 30   # default scratch budget for the K_ZX chunks of the v
 
 
 def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_work_bytes: int | None = None,
-            var_path: str = "i8", mj_event: torch.cuda.Event | None = None, mj_path: str = "auto"):
+            var_path: str = "i8", mj_event: torch.cuda.Event | None = None, mj_path: str = "auto",
+            want_mean_jac: bool = True):
     """Posterior mean (B,Q), latent variance var_f (B,Q) and input-Jacobian (B,Q,d) at queries Z.
 
     Z: (Q,d) shared by all GPs or (B,Q,d); float64 or float32 selects the prediction path.  The batched
@@ -418,13 +419,18 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
         q, strideZ = Z.shape[1], Z.stride(0)
     assert Z.shape[-1] == d
     st = _lib.stream_ptr(dev)
-    mean = torch.empty(B, q, dtype=dt, device=dev)
-    jac = torch.empty(B, q, d, dtype=dt, device=dev)
+    assert want_var or want_mean_jac, "nothing to compute"
+    mean = torch.empty(B, q, dtype=dt, device=dev) if want_mean_jac else None
+    jac = torch.empty(B, q, d, dtype=dt, device=dev) if want_mean_jac else None
     var = torch.empty(B, q, dtype=dt, device=dev) if want_var else None
     if q == 0:
         return mean, var, jac
     if var_path == "i8" and gp.wimg is None and not i8_supported(npad, gp.digits or None):
         var_path = "f64"                     # training set too large for exact int32 accumulation
+    if not want_mean_jac and var_path != "i8":
+        # variance alone exists on the int8 path only; the DMMA path computes mean and Jacobian on the way
+        mean = torch.empty(B, q, dtype=dt, device=dev)
+        jac = torch.empty(B, q, d, dtype=dt, device=dev)
     if want_var and var_path == "i8":
         # fused front end (kernel evaluated once for mean, Jacobian and the digit image) + variance contraction
         # on the tcgen05 int8 pipe (exact digit products, fp64 recombination)

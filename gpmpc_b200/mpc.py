@@ -83,7 +83,7 @@ class ConstraintTightening:
         """Latent posterior variances (3, len(z)) of the three GPs at the stage inputs z (.., nx+nu) [gpmpc.py:441-445]."""
         Zg = z[:, self._cols] * self._mask          # (Q, 3, dpad)
         Zg = Zg.permute(1, 0, 2).contiguous()
-        return E.predict(self.batch, Zg)[1]
+        return E.predict(self.batch, Zg, want_mean_jac=False)[1]      # variance only: no Jacobian GEMM in the front kernel
 
     @torch.no_grad()
     def propagate_constraint_limits(self, x_prev, u_prev):

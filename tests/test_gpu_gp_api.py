@@ -249,6 +249,9 @@ def test_variance_paths_agree(n, d, q, monkeypatch):
     v_i8 = E.predict(fit, Z)[1][0].cpu()
     v_f64 = E.predict(fit, Z, var_path="f64")[1][0].cpu()
     assert o.rel_err(v_i8, vr) < 1e-7 and o.rel_err(v_f64, vr) < 1e-9
+    m0, v0, j0 = E.predict(fit, Z, want_mean_jac=False)          # variance alone: the front kernel skips the Jacobian GEMM
+    assert m0 is None and j0 is None and torch.equal(v0[0].cpu(), v_i8)
+    assert torch.equal(E.predict(fit, Z, want_mean_jac=False, var_path="f64")[1][0].cpu(), v_f64)
     for S in (4, 6):
         fs, _ = E.factorize(X, y, p["ell"], p["sf2"], p["noise"], digits=S)
         assert o.rel_err(E.predict(fs, Z)[1][0].cpu(), vr) < {4: 1e-5, 6: 1e-9}[S]
