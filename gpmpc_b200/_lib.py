@@ -42,6 +42,10 @@ SIGNATURES = {
     "gpk_var_colsq": (_i, [_p, _l, _l, _p, _l, _l, _l, _l, _p, _l, _l, _i, _p]),
     "gpk_var_finalize": (_i, [_i, _p, _l, _l, _i, _l, _p, _p, _l, _i, _p]),
     "gpk_dgemm_nt": (_i, [_p, _l, _p, _l, _p, _l, _l, _l, _l, _d, _d, _i, _i, _p]),
+    "gpk_oz_dgemm_nt_work_bytes": (_l, [_l, _l, _l, _i, _i]),
+    "gpk_oz_dgemm_nt": (_i, [_p, _l, _p, _l, _p, _l, _l, _l, _l, _d, _d, _i, _i, _i, _p, _l, _p]),
+    "gpk_oz_gemm_work_bytes": (_l, [_l, _i]),
+    "gpk_oz_gemm_set_workspace": (_i, [_p, _l, _i, _l]),
     "gpk_oz_default_digits": (_i, []),
     "gpk_oz_w_image_bytes": (_l, [_l, _i]),
     "gpk_oz_e_image_bytes": (_l, [_l, _l, _i]),

@@ -17,6 +17,7 @@
 // per-tile column sums of squares  colsq[tile_m][j] = sum_{i in tile} C[i,j]^2.
 #pragma once
 #include "common.cuh"
+#include "gemm_params.cuh"
 
 namespace gpk {
 
@@ -24,24 +25,6 @@ constexpr int G_BM = 128, G_BN = 128, G_BK = 16, G_STAGES = 4, G_THREADS = 256;
 constexpr int G_ROW = G_BK + 4;                         // padded smem row, doubles (160 B)
 constexpr int G_STAGE_ELEMS = (G_BM + G_BN) * G_ROW;    // doubles per stage
 constexpr int G_SMEM_BYTES = G_STAGES * G_STAGE_ELEMS * 8;
-
-struct GemmParams {
-    const double* A;
-    const double* B;
-    double* C;
-    long lda, ldb, ldc;
-    long strideA, strideB, strideC;   // batch strides (elements); grid.z = batch
-    int M, N, K;
-    double alpha, beta;
-    int a_tri;       // 0 full, 1 lower, 2 upper
-    int c_lower;     // 1: skip tiles entirely above the diagonal
-    int c_inplace;   // 1: C aliases A (one CTA owns all columns of its rows)
-    int tiles_m, tiles_n;
-    int group_m, group_n;   // super-tile for L2 reuse across the ~148 concurrently resident CTAs
-    int order, nbatch;      // tile enumeration (see tile_coords)
-    double* colsq;          // epilogue 1 output: [tiles_m][ld_colsq]
-    long ld_colsq, stride_colsq;
-};
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"

@@ -41,6 +41,11 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
     if (epilogue == 1) GPK_ARG(p.colsq != nullptr, "colsq output missing");
     p.nbatch = batch;
     p.c_inplace = (epilogue == 0 && p.C == p.A) ? 1 : 0;
+    if (epilogue == 0 && !p.c_inplace) {
+        // large GEMMs go to the tcgen05 int8 digit path when the caller registered its scratch (ozgemm.cu)
+        const int r = ozg_try(p, batch, st);
+        if (r != 0) return r < 0 ? r : 0;
+    }
     // tile configuration: the 128 x 128 tiles need ~one wave of CTAs to pay off (see dgemm_nt.cuh)
     const long tiles128 = (long)(p.M / G_BM) * (p.N / G_BN) * batch / (p.c_lower ? 2 : 1);
     int bm = G_BM, bn = G_BN;

@@ -179,4 +179,53 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, int32_t (&v)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
 
+// ------------------------------------------------------------------------------------------------
+// balanced base-256 digits of a signed fixed-point integer (most significant digit first)
+//   I = sum_s dig[s] * 256^(S-1-s),  dig[s] in [-128, 127]  (leading digit in [-64, 64] by the scaling)
+// ------------------------------------------------------------------------------------------------
+template <int S>
+__device__ __forceinline__ void signed_digits(long long I, int8_t (&dig)[S]) {
+#pragma unroll
+    for (int s = S - 1; s > 0; s--) {
+        const int low = (int)(I & 255);
+        const int dgt = low >= 128 ? low - 256 : low;    // in [-128, 127]
+        dig[s] = (int8_t)dgt;
+        I = (I - dgt) >> 8;
+    }
+    dig[0] = (int8_t)I;                                  // |I| <= 64 by construction of the scaling
+}
+
+// x in [-1, 1] -> nearest integer of x * 2^(6 + 8 (S-1))  (S <= 6: 46 bits)
+template <int S>
+__device__ __forceinline__ long long to_fixed(double x) {
+    constexpr double SCALE = (double)(1ull << (6 + 8 * (S - 1)));
+    return __double2ll_rn(x * SCALE);
+}
+
+
+__device__ __forceinline__ double oz_ll2d(long long v) {
+    // exact int64 -> double for |v| < 2^51 without the conversion pipe: bit pattern of 1.5 * 2^52 + v, minus the bias
+    return __longlong_as_double(0x4338000000000000LL + v) - 6755399441055744.0;
+}
+// R = sum_g 256^-g D_g: digit groups are combined three at a time in exact int64 arithmetic (integer pipe),
+// so the FP64 pipe only sees one conversion add per triple and the Horner steps between triples
+template <int S>
+__device__ __forceinline__ double oz_recombine(const int32_t (&v)[S][8], int j) {
+    constexpr int NT = (S + 2) / 3;
+    double acc = 0.0;
+#pragma unroll
+    for (int tr = NT - 1; tr >= 0; tr--) {
+        const int g0 = 3 * tr;
+        const int cnt = (S - g0) < 3 ? (S - g0) : 3;
+        long long t = v[g0][j];
+#pragma unroll
+        for (int u = 1; u < cnt; u++) t = t * 256 + v[g0 + u][j];
+        // t = sum_u D_{g0+u} 256^(cnt-1-u); its weight relative to the triple's leading digit is 256^-(cnt-1)
+        const double dv = oz_ll2d(t) * (cnt == 3 ? 1.0 / 65536.0 : cnt == 2 ? 1.0 / 256.0 : 1.0);
+        acc = (tr == NT - 1) ? dv : fma(acc, 1.0 / 16777216.0, dv);
+    }
+    return acc;
+}
+
+
 }  // namespace gpk

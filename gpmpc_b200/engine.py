@@ -53,6 +53,22 @@ def make_hyp(center, ell, sf2: float, noise: float, d: int, device) -> torch.Ten
     return h.to(device, non_blocking=True)
 
 
+# Large fit GEMMs (potrf / trtri / K^-1 at npad >= FIT_GEMM_MIN_NPAD) run on the tcgen05 int8 pipe with this many
+# balanced base-256 digits per operand (csrc/ozgemm.cu): 7 digits reproduce the DMMA result to ~2e-15 of max|C|,
+# 6 to ~5e-13, 5 to ~1e-10; 0 keeps every GEMM on the FP64 DMMA pipe.
+FIT_GEMM_DIGITS = 6
+FIT_GEMM_MIN_NPAD = 4096
+FIT_GEMM_MIN_WORK_G = 0     # tuning hook: smallest GEMM (1e9 multiply-adds) sent to the int8 path; 0 = library default
+
+
+def _register_fit_gemm_workspace(buf: torch.Tensor | None, digits: int = 0):
+    """(Un)register the per-device scratch of the int8 fit GEMMs with the library (it only borrows the pointer)."""
+    if buf is None:
+        call("gpk_oz_gemm_set_workspace", None, 0, 0, 0)
+    else:
+        call("gpk_oz_gemm_set_workspace", ptr(buf), buf.numel(), digits, -int(FIT_GEMM_MIN_WORK_G))
+
+
 @dataclass
 class FitScratch:
     """Scratch for fitting one GP of padded size npad; reused across GPs and MLL iterations."""
@@ -70,6 +86,8 @@ class FitScratch:
     grad_work: torch.Tensor = None
     grad_out: torch.Tensor = None
     y_pad: torch.Tensor = None
+    gemm_work: torch.Tensor = None     # digit images of the int8 fit GEMMs (None: DMMA only)
+    gemm_digits: int = 0
 
     def __post_init__(self):
         lib = _lib.load()
@@ -83,6 +101,14 @@ class FitScratch:
         self.info = torch.zeros(1, dtype=torch.int32, device=dev)
         self.grad_out = torch.zeros(34, dtype=F64, device=dev)
         self.y_pad = torch.zeros(n, dtype=F64, device=dev)
+        if FIT_GEMM_DIGITS and n >= FIT_GEMM_MIN_NPAD:
+            self.gemm_digits = int(FIT_GEMM_DIGITS)
+            self.gemm_work = torch.empty(lib.gpk_oz_gemm_work_bytes(n, self.gemm_digits), dtype=torch.uint8, device=dev)
+
+    def activate(self):
+        """Point the library's GEMM dispatcher at this scratch (or at nothing) on this device."""
+        with torch.cuda.device(self.device):
+            _register_fit_gemm_workspace(self.gemm_work, self.gemm_digits)
 
     def need_kinv(self):
         if self.Kinv is None:
@@ -94,16 +120,23 @@ _scratch_cache: dict = {}
 
 
 def get_fit_scratch(npad: int, device: torch.device) -> FitScratch:
-    key = (npad, device.index)
+    key = (npad, device.index, int(FIT_GEMM_DIGITS), int(FIT_GEMM_MIN_NPAD))
     if key not in _scratch_cache:
         # keep at most one size per device alive: the big configs need the memory back
         for k in [k for k in _scratch_cache if k[1] == device.index]:
+            with torch.cuda.device(device):
+                _register_fit_gemm_workspace(None)
             del _scratch_cache[k]
         _scratch_cache[key] = FitScratch(npad, device)
+        _scratch_cache[key].activate()
     return _scratch_cache[key]
 
 
 def release_scratch():
+    if torch.cuda.is_available():
+        for k in _scratch_cache:
+            with torch.cuda.device(k[1]):
+                _register_fit_gemm_workspace(None)
     _scratch_cache.clear()
     _work_cache.clear()
 

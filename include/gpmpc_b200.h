@@ -199,6 +199,23 @@ int gpk_stage_rk4(const double* x, long ldx, const double* u, long ldu, long q, 
 int gpk_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C, long ldc,
                  long M, long N, long K, double alpha, double beta, int a_tri, int c_lower, void* stream);
 
+/* ---- fit GEMMs on the tcgen05 int8 tensor pipe ---------------------------------------------------
+ * The O(N^3) steps behind gpmpc/gp.py:62 (Cholesky, solves) and gpmpc/gp.py:46 (inverse) are GEMMs of the contract
+ * above.  gpk_oz_dgemm_nt runs one of them error-free on int8 digit slices (`digits` = 5/6/7 balanced base-256
+ * digits per operand, power-of-two scales per row and chunk of 2048 k; exact int32 accumulation in TMEM, fp64
+ * recombination): M, N multiples of 128, K of 64, a_tri != 0 needs M == K, C must not alias A or B.
+ * Scratch: gpk_oz_dgemm_nt_work_bytes(M, N, K, same = (A == B), digits).
+ * gpk_oz_gemm_set_workspace registers per-device scratch (gpk_oz_gemm_work_bytes(npad, digits)) that makes
+ * gpk_potrf / gpk_trtri / gpk_kinv / gpk_dgemm_nt route every GEMM with M, N >= min_dim (0 = keep the default of
+ * 2048) and K >= 1024 through this path; ptr == NULL or digits == 0 restores the DMMA path.  The caller owns the
+ * memory and must keep it alive while registered. */
+long gpk_oz_dgemm_nt_work_bytes(long M, long N, long K, int same, int digits);
+int gpk_oz_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C, long ldc, long M, long N,
+                    long K, double alpha, double beta, int a_tri, int c_lower, int digits, void* work,
+                    long work_bytes, void* stream);
+long gpk_oz_gemm_work_bytes(long npad, int digits);
+int gpk_oz_gemm_set_workspace(void* ptr, long bytes, int digits, long min_dim);
+
 #ifdef __cplusplus
 }
 #endif

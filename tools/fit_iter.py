@@ -16,7 +16,7 @@ for _ in range(2): it()
 torch.cuda.synchronize()
 torch.cuda.profiler.start()
 t0 = time.perf_counter()
-n = 5
+n = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 for _ in range(n): r = it()
 torch.cuda.synchronize()
 torch.cuda.profiler.stop()
