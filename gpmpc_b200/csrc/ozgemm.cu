@@ -343,7 +343,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * 8, 1) ozg_
 struct OzgWorkspace { void* ptr = nullptr; long bytes = 0; int digits = 0; };
 static OzgWorkspace g_ozg_ws[64];
 static long g_ozg_min_dim = 1024;          // smallest M, N for which the int8 path is used
-static double g_ozg_min_work = 6e9;
+static double g_ozg_min_work = 2e9;
 
 static int ozg_device() {
     int dev = 0;
