@@ -409,6 +409,38 @@ def measure_extras(gb, problem, Z, flush, dev):
         mll_iter()
     torch.cuda.synchronize(dev)
     out["mll_grad_iters_per_s_n2048"] = 5 / (time.perf_counter() - t0)
+    # the same iteration at N = 16384 (half of config 4's N, to keep the default run short): the large GEMMs of the
+    # Cholesky / triangular inverse / K^-1 run on the tcgen05 int8 pipe (csrc/ozgemm.cu, E.FIT_GEMM_DIGITS digits),
+    # compared with the FP64 DMMA pipe alone
+    gb16 = torch.Generator().manual_seed(1337)
+    Xb = (torch.rand(16384, DIM, generator=gb16, dtype=torch.float64) * 2.0 - 1.0).to(dev)
+    yb = (torch.sin(Xb @ torch.randn(DIM, generator=gb16, dtype=torch.float64).to(dev))
+          + 0.05 * torch.randn(16384, generator=gb16, dtype=torch.float64).to(dev))
+    big = problem
+    saved = E.FIT_GEMM_DIGITS
+    losses = {}
+    for tag, digits in (("dmma", 0), ("int8", saved or 6)):
+        E.FIT_GEMM_DIGITS = digits
+        E.release_scratch()
+
+        def big_iter():
+            fit, ws = E.factorize(Xb, yb, big["ell"], big["sf2"], big["noise"], want_kinv=True, want_image=False)
+            return E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))[0]
+
+        big_iter()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            losses[tag] = big_iter()
+        torch.cuda.synchronize(dev)
+        dt = (time.perf_counter() - t0) / 3
+        out[f"mll_grad_iters_per_s_n16384_{tag}"] = 1.0 / dt
+        out[f"mll_grad_n16384_{tag}_tflops_of_n3"] = 16384.0 ** 3 / dt * 1e-12
+    out["mll_grad_n16384_int8_digits"] = int(saved or 6)
+    out["mll_n16384_rel_dev_int8_vs_dmma"] = abs(losses["int8"] - losses["dmma"]) / abs(losses["dmma"])
+    E.FIT_GEMM_DIGITS = saved
+    E.release_scratch()
+    del Xb, yb
     out.update(measure_mpc_rows(gb, problem, flush, dev))
     return out
 

@@ -169,6 +169,12 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, int32_t (&v)[8]) {
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
                  : "r"(taddr));
 }
+// 32 lanes x 4 consecutive 32-bit columns
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, int32_t (&v)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];\n"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+                 : "r"(taddr));
+}
 // 32 lanes x 16 consecutive 32-bit columns
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, int32_t (&v)[16]) {
     asm volatile(
@@ -209,8 +215,8 @@ __device__ __forceinline__ double oz_ll2d(long long v) {
 }
 // R = sum_g 256^-g D_g: digit groups are combined three at a time in exact int64 arithmetic (integer pipe),
 // so the FP64 pipe only sees one conversion add per triple and the Horner steps between triples
-template <int S>
-__device__ __forceinline__ double oz_recombine(const int32_t (&v)[S][8], int j) {
+template <int S, int W>
+__device__ __forceinline__ double oz_recombine(const int32_t (&v)[S][W], int j) {
     constexpr int NT = (S + 2) / 3;
     double acc = 0.0;
 #pragma unroll

@@ -5,7 +5,7 @@
 // gpytorch -> torch LAPACK in the reference), where the DMMA pipe (37 TFLOP/s) is the bound.
 //
 //   operand (fp64, rows x K) -> digit image  [row block of 64][k block of 64][digit s][64 x 64 B tile]   (int8)
-//                               + power-of-two scales per (row, k-CHUNK of KC k-blocks)
+//                               + power-of-two scales per (row, k-CHUNK of KC = 64 k-blocks = 4096 k)
 //     x[i][k] = 2^e(i,chunk) * sum_s dig_s[i][k] 2^(-6-8s)
 //   Per-chunk scales keep the fixed-point grid relative to the row's magnitude INSIDE the chunk (rows of a Cholesky
 //   factor decay along k), and bound the int32 accumulation length (KC * 64 * S * 2^14 < 2^31).
@@ -16,13 +16,16 @@
 // CTA pairs with the A tile multicast into both shared memories) with a storing epilogue.
 #include "ozaki.cuh"
 #include "gemm_params.cuh"
+#include <cstdlib>
 #include <map>
 #include <tuple>
 #include <vector>
 
 namespace gpk {
 
-constexpr int OZG_KC = 32;          // k-blocks (of 64) per scale chunk: 2048 k
+// k-blocks (of 64) per scale chunk (runtime tunable for experiments: GPK_OZG_KC); int32 accumulation stays exact while
+// kc * 64 * S * 2^14 < 2^31 (kc <= 256 at S = 7)
+static int g_ozg_kc = 64;
 
 // ------------------------------------------------------------------------------------------------
 // operand slicing, two HBM-bound passes:
@@ -37,7 +40,7 @@ __device__ __forceinline__ void ozg_valid_kb(int row, int kb_total, int tri, int
 }
 
 __global__ void __launch_bounds__(256)
-ozg_scale_kernel(const double* __restrict__ src, long ld, int rows, int kb_total, int tri, double* __restrict__ scale) {
+ozg_scale_kernel(const double* __restrict__ src, long ld, int rows, int kb_total, int tri, int OZG_KC, double* __restrict__ scale) {
     const int chunk = blockIdx.x;
     const int row = blockIdx.y * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     int v0, v1;
@@ -63,8 +66,8 @@ ozg_scale_kernel(const double* __restrict__ src, long ld, int rows, int kb_total
 
 template <int S>
 __global__ void __launch_bounds__(256)
-ozg_digit_kernel(const double* __restrict__ src, long ld, int rows, int kb_total, int tri, const double* __restrict__ scale,
-                 int8_t* __restrict__ img) {
+ozg_digit_kernel(const double* __restrict__ src, long ld, int rows, int kb_total, int tri, int OZG_KC,
+                 const double* __restrict__ scale, int8_t* __restrict__ img) {
     const int kb = blockIdx.x, ib = blockIdx.y;
     int v0, v1;
     ozg_valid_kb(ib * OZ_WB, kb_total, tri, v0, v1);
@@ -95,10 +98,11 @@ ozg_digit_kernel(const double* __restrict__ src, long ld, int rows, int kb_total
 
 template <int S>
 static int ozg_slice(const double* src, long ld, int rows, int kb_total, int tri, double* scale, int8_t* img, cudaStream_t st) {
+    const int OZG_KC = g_ozg_kc;
     const int nchunks = (kb_total + OZG_KC - 1) / OZG_KC;
-    ozg_scale_kernel<<<dim3((unsigned)nchunks, (unsigned)(rows / 8)), 256, 0, st>>>(src, ld, rows, kb_total, tri, scale);
+    ozg_scale_kernel<<<dim3((unsigned)nchunks, (unsigned)(rows / 8)), 256, 0, st>>>(src, ld, rows, kb_total, tri, OZG_KC, scale);
     GPK_LAUNCHED();
-    ozg_digit_kernel<S><<<dim3((unsigned)kb_total, (unsigned)(rows / OZ_WB)), 256, 0, st>>>(src, ld, rows, kb_total, tri, scale, img);
+    ozg_digit_kernel<S><<<dim3((unsigned)kb_total, (unsigned)(rows / OZ_WB)), 256, 0, st>>>(src, ld, rows, kb_total, tri, OZG_KC, scale, img);
     GPK_LAUNCHED();
     return 0;
 }
@@ -112,7 +116,7 @@ struct OzGemmArgs {
     int rowsA, rowsB;
     double* C; long ldc;
     double alpha, beta;
-    int kb_total, a_tri;
+    int kb_total, a_tri, kc;
     const int2* items; int total_items;           // (A tile of 128 rows, B row-block pair = C tile column)
 };
 
@@ -123,6 +127,7 @@ __device__ __forceinline__ void ozg_krange(const OzGemmArgs& a, int qt, int& kb0
 
 template <int S>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * 8, 1) ozg_gemm_kernel(const OzGemmArgs a) {
+    const int OZG_KC = a.kc;
     constexpr int EPI_WARPS = 8, PRODUCER_WARP = 8, MMA_WARP = 9;
     constexpr int NST = oz_stages(S);
     constexpr uint32_t STAGE_BYTES = oz_stage_bytes(S);
@@ -345,6 +350,17 @@ static OzgWorkspace g_ozg_ws[64];
 static long g_ozg_min_dim = 1024;          // smallest M, N for which the int8 path is used
 static double g_ozg_min_work = 2e9;
 
+static int g_ozg_gm = 8, g_ozg_gn = 9, g_ozg_pairs = 0;
+static void ozg_env() {
+    static bool done = false;
+    if (done) return;
+    done = true;
+    if (getenv("GPK_OZG_KC")) g_ozg_kc = atoi(getenv("GPK_OZG_KC"));
+    if (getenv("GPK_OZG_GM")) g_ozg_gm = atoi(getenv("GPK_OZG_GM"));
+    if (getenv("GPK_OZG_GN")) g_ozg_gn = atoi(getenv("GPK_OZG_GN"));
+    if (getenv("GPK_OZG_PAIRS")) g_ozg_pairs = atoi(getenv("GPK_OZG_PAIRS"));
+}
+
 static int ozg_device() {
     int dev = 0;
     cudaGetDevice(&dev);
@@ -371,7 +387,7 @@ static const int2* ozg_items(int tiles_m, int tiles_n, int a_tri, int c_lower, i
     const Key key{ozg_device(), tiles_m, tiles_n, a_tri, c_lower};
     auto f = cache.find(key);
     if (f != cache.end()) { *total = f->second.second; return f->second.first; }
-    constexpr int GM = 8, GN = 9;
+    const int GM = g_ozg_gm, GN = g_ozg_gn;
     std::vector<int2> items;
     items.reserve((size_t)tiles_m * tiles_n);
     const int srows = (tiles_m + GM - 1) / GM;
@@ -396,10 +412,11 @@ static const int2* ozg_items(int tiles_m, int tiles_n, int a_tri, int c_lower, i
 }
 
 static long ozg_img_bytes(long rows, long K, int S) { return rows * K * S; }
-static long ozg_scale_bytes(long rows, long K) { return ((K / OZ_BK + OZG_KC - 1) / OZG_KC) * rows * 8; }
+static long ozg_scale_bytes(long rows, long K) { return ((K / OZ_BK + g_ozg_kc - 1) / g_ozg_kc) * rows * 8; }
 
 template <int S>
 static int ozg_run(const GemmParams& p, uint8_t* work, cudaStream_t st) {
+    ozg_env();
     const int kb_total = p.K / OZ_BK;
     const bool same = p.A == p.B && p.lda == p.ldb && p.M == p.N;
     int8_t* imgA = reinterpret_cast<int8_t*>(work);
@@ -418,7 +435,7 @@ static int ozg_run(const GemmParams& p, uint8_t* work, cudaStream_t st) {
     a.imgA = imgA; a.imgB = imgB; a.scaleA = scaleA; a.scaleB = scaleB;
     a.rowsA = p.M; a.rowsB = p.N;
     a.C = p.C; a.ldc = p.ldc; a.alpha = p.alpha; a.beta = p.beta;
-    a.kb_total = kb_total; a.a_tri = p.a_tri;
+    a.kb_total = kb_total; a.a_tri = p.a_tri; a.kc = g_ozg_kc;
     a.items = ozg_items(p.M / OZ_QT, p.N / (2 * OZ_WB), p.a_tri, p.c_lower, &a.total_items, st);
     GPK_ARG(a.items != nullptr, "could not build the item list");
     constexpr int smem = oz_stages(S) * oz_stage_bytes(S);
@@ -427,7 +444,8 @@ static int ozg_run(const GemmParams& p, uint8_t* work, cudaStream_t st) {
         GPK_CUDA(cudaFuncSetAttribute(ozg_gemm_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_done = true;
     }
-    const int hw_pairs = ozg_sm_count() / 2;
+    int hw_pairs = ozg_sm_count() / 2;
+    if (g_ozg_pairs > 0 && g_ozg_pairs < hw_pairs) hw_pairs = g_ozg_pairs;
     const int grid = 2 * (a.total_items < hw_pairs ? a.total_items : hw_pairs);
     ozg_gemm_kernel<S><<<grid, 64 + 32 * 8, smem, st>>>(a);
     GPK_LAUNCHED();

@@ -202,7 +202,7 @@ int gpk_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C
 /* ---- fit GEMMs on the tcgen05 int8 tensor pipe ---------------------------------------------------
  * The O(N^3) steps behind gpmpc/gp.py:62 (Cholesky, solves) and gpmpc/gp.py:46 (inverse) are GEMMs of the contract
  * above.  gpk_oz_dgemm_nt runs one of them error-free on int8 digit slices (`digits` = 5/6/7 balanced base-256
- * digits per operand, power-of-two scales per row and chunk of 2048 k; exact int32 accumulation in TMEM, fp64
+ * digits per operand, power-of-two scales per row and chunk of 4096 k; exact int32 accumulation in TMEM, fp64
  * recombination): M, N multiples of 128, K of 64, a_tri != 0 needs M == K, C must not alias A or B.
  * Scratch: gpk_oz_dgemm_nt_work_bytes(M, N, K, same = (A == B), digits).
  * gpk_oz_gemm_set_workspace registers per-device scratch (gpk_oz_gemm_work_bytes(npad, digits)) that makes

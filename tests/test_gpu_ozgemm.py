@@ -29,9 +29,9 @@ def _lib():
     (256, 384, 1024, 0, 0, False, -1.0, 1.0),
     (384, 128, 384, 1, 0, False, -1.0, 0.0),        # lower-triangular A: k-range grows with the tile row
     (512, 256, 512, 2, 0, False, 1.0, 0.0),         # upper-triangular A
-    (640, 640, 2112, 0, 1, True, -1.0, 1.0),        # SYRK-like: shared image, two scale chunks (K > 2048)
-    (2560, 2560, 2560, 2, 1, True, 1.0, 0.0),       # K^-1 = U U^T shape, > one super-tile, chunk boundary inside a tile row
-    (1280, 1152, 4160, 0, 0, False, 0.5, -2.0),     # three chunks, general alpha / beta
+    (640, 640, 4160, 0, 1, True, -1.0, 1.0),        # SYRK-like: shared image, two scale chunks (K > 4096)
+    (4352, 4352, 4352, 2, 1, True, 1.0, 0.0),       # K^-1 = U U^T shape, > one super-tile, chunk boundary inside a tile row
+    (1280, 1152, 8256, 0, 0, False, 0.5, -2.0),     # three chunks, general alpha / beta
 ])
 def test_oz_dgemm_nt(digits, M, N, K, a_tri, c_lower, same, alpha, beta):
     L = _lib()

@@ -55,6 +55,10 @@ def run(M, N, K, a_tri, c_lower, same, digits, alpha=-1.0, beta=1.0, decay=False
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "one":      # one shape, e.g. for ncu: one M N K tri low same S
+        M, N, K, tri, low, same, S = [int(a) for a in sys.argv[2:9]]
+        run(M, N, K, tri, low, bool(same), S, reps=2)
+        sys.exit(0)
     big = len(sys.argv) > 1 and sys.argv[1] == "big"
     for S in (5, 6, 7):
         run(256, 256, 1024, 0, 0, False, S)
