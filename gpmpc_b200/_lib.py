@@ -30,6 +30,7 @@ SIGNATURES = {
     "gpk_trtri_scratch_elems": (_l, [_l]),
     "gpk_trtri": (_i, [_p, _l, _l, _p, _p, _l, _p, _l, _p, _l, _p]),
     "gpk_kinv": (_i, [_p, _l, _l, _p, _l, _p]),
+    "gpk_kinv_rows": (_i, [_p, _l, _l, _l, _l, _p, _l, _p]),
     "gpk_solve_alpha": (_i, [_p, _l, _p, _l, _p, _l, _l, _p, _p, _p, _p, _p]),
     "gpk_grad_trace_work_elems": (_l, [_l, _i, _l, _l]),
     "gpk_mll_grad_reduce": (_i, [_p, _l, _l, _i, _p, _p, _l, _p, _l, _l, _p, _l, _p, _p]),

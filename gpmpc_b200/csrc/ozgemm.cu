@@ -412,28 +412,50 @@ static const int2* ozg_items(int tiles_m, int tiles_n, int a_tri, int c_lower, i
 }
 
 static long ozg_img_bytes(long rows, long K, int S) { return rows * K * S; }
+
+// A may be B itself (SYRK, K^-1 = U U^T) or a window of B's rows (row-split K^-1): one image then serves both operands.
+// Returns the first row of A inside B, or -1 when the operands are unrelated.
+static long ozg_a_row_in_b(const GemmParams& p) {
+    if (p.lda != p.ldb) return -1;
+    const uintptr_t a = (uintptr_t)p.A, b = (uintptr_t)p.B;
+    if (a < b || (a - b) % ((uintptr_t)p.ldb * 8)) return -1;
+    const long r = (long)((a - b) / ((uintptr_t)p.ldb * 8));
+    if (r % OZ_QT || r + p.M > p.N) return -1;
+    return r;
+}
 static long ozg_scale_bytes(long rows, long K) { return ((K / OZ_BK + g_ozg_kc - 1) / g_ozg_kc) * rows * 8; }
 
 template <int S>
 static int ozg_run(const GemmParams& p, uint8_t* work, cudaStream_t st) {
     ozg_env();
     const int kb_total = p.K / OZ_BK;
-    const bool same = p.A == p.B && p.lda == p.ldb && p.M == p.N;
-    int8_t* imgA = reinterpret_cast<int8_t*>(work);
-    long off = ozg_img_bytes(p.M, p.K, S);
-    int8_t* imgB = imgA;
-    if (!same) { imgB = reinterpret_cast<int8_t*>(work + off); off += ozg_img_bytes(p.N, p.K, S); }
-    off = (off + 255) / 256 * 256;
-    double* scaleA = reinterpret_cast<double*>(work + off);
-    off += ozg_scale_bytes(p.M, p.K);
-    double* scaleB = scaleA;
-    if (!same) { scaleB = reinterpret_cast<double*>(work + off); off += ozg_scale_bytes(p.N, p.K); }
-
-    GPK_TRY(ozg_slice<S>(p.A, p.lda, p.M, kb_total, p.a_tri, scaleA, imgA, st));
-    if (!same) GPK_TRY(ozg_slice<S>(p.B, p.ldb, p.N, kb_total, 0, scaleB, imgB, st));
+    const long arow = ozg_a_row_in_b(p);
+    int8_t *imgA, *imgB;
+    double *scaleA, *scaleB;
+    int rowsA = p.M;
+    if (arow >= 0) {
+        // shared image; the triangular k-range may only be skipped while slicing when no tile reads outside it
+        const int tri = (arow == 0 && p.M == p.N && p.a_tri == 2 && p.c_lower) ? 2 : 0;
+        imgB = reinterpret_cast<int8_t*>(work);
+        const long off = (ozg_img_bytes(p.N, p.K, S) + 255) / 256 * 256;
+        scaleB = reinterpret_cast<double*>(work + off);
+        GPK_TRY(ozg_slice<S>(p.B, p.ldb, p.N, kb_total, tri, scaleB, imgB, st));
+        imgA = imgB + (arow / OZ_WB) * (long)kb_total * S * OZ_B_SLICE;
+        scaleA = scaleB + arow;
+        rowsA = p.N;
+    } else {
+        imgA = reinterpret_cast<int8_t*>(work);
+        long off = ozg_img_bytes(p.M, p.K, S);
+        imgB = reinterpret_cast<int8_t*>(work + off);
+        off = (off + ozg_img_bytes(p.N, p.K, S) + 255) / 256 * 256;
+        scaleA = reinterpret_cast<double*>(work + off);
+        scaleB = reinterpret_cast<double*>(work + off + ozg_scale_bytes(p.M, p.K));
+        GPK_TRY(ozg_slice<S>(p.A, p.lda, p.M, kb_total, p.a_tri, scaleA, imgA, st));
+        GPK_TRY(ozg_slice<S>(p.B, p.ldb, p.N, kb_total, 0, scaleB, imgB, st));
+    }
     OzGemmArgs a{};
     a.imgA = imgA; a.imgB = imgB; a.scaleA = scaleA; a.scaleB = scaleB;
-    a.rowsA = p.M; a.rowsB = p.N;
+    a.rowsA = rowsA; a.rowsB = p.N;
     a.C = p.C; a.ldc = p.ldc; a.alpha = p.alpha; a.beta = p.beta;
     a.kb_total = kb_total; a.a_tri = p.a_tri; a.kc = g_ozg_kc;
     a.items = ozg_items(p.M / OZ_QT, p.N / (2 * OZ_WB), p.a_tri, p.c_lower, &a.total_items, st);
@@ -453,15 +475,14 @@ static int ozg_run(const GemmParams& p, uint8_t* work, cudaStream_t st) {
 }
 
 static long ozg_need_bytes(const GemmParams& p, int S) {
-    const bool same = p.A == p.B && p.lda == p.ldb && p.M == p.N;
-    long b = ozg_img_bytes(p.M, p.K, S) + ozg_scale_bytes(p.M, p.K) + 512;
-    if (!same) b += ozg_img_bytes(p.N, p.K, S) + ozg_scale_bytes(p.N, p.K);
+    long b = ozg_img_bytes(p.N, p.K, S) + ozg_scale_bytes(p.N, p.K) + 512;
+    if (ozg_a_row_in_b(p) < 0) b += ozg_img_bytes(p.M, p.K, S) + ozg_scale_bytes(p.M, p.K);
     return b;
 }
 
 static bool ozg_shape_ok(const GemmParams& p) {
     if (p.M % OZ_QT || p.N % (2 * OZ_WB) || p.K % OZ_BK) return false;
-    if (p.a_tri != 0 && p.M != p.K) return false;
+    if (p.a_tri != 0 && p.M > p.K) return false;
     if (p.C == p.A || p.C == p.B) return false;
     if (p.lda % 2 || p.ldb % 2 || p.ldc % 2) return false;
     if (((uintptr_t)p.A | (uintptr_t)p.B | (uintptr_t)p.C) % 16) return false;
@@ -524,15 +545,15 @@ int gpk_oz_dgemm_nt(const double* A, long lda, const double* B, long ldb, double
     p.M = (int)M; p.N = (int)N; p.K = (int)K; p.alpha = alpha; p.beta = beta; p.a_tri = a_tri; p.c_lower = c_lower;
     GPK_ARG(A && B && C && work, "null pointer");
     GPK_ARG(M > 0 && N > 0 && K > 0, "empty GEMM");
-    GPK_ARG(ozg_shape_ok(p), "M, N multiples of 128, K of 64; a_tri needs M == K; C must not alias A or B; 16-byte alignment");
+    GPK_ARG(ozg_shape_ok(p), "M, N multiples of 128, K of 64; a_tri needs M <= K; C must not alias A or B; 16-byte alignment");
     GPK_ARG(digits >= 5 && digits <= 7, "digits must be 5, 6 or 7");
     GPK_ARG(work_bytes >= ozg_need_bytes(p, digits), "scratch too small");
     return ozg_dispatch(p, digits, static_cast<uint8_t*>(work), (cudaStream_t)stream);
 }
 
 long gpk_oz_dgemm_nt_work_bytes(long M, long N, long K, int same, int digits) {
-    long b = ozg_img_bytes(M, K, digits) + ozg_scale_bytes(M, K) + 512;
-    if (!same) b += ozg_img_bytes(N, K, digits) + ozg_scale_bytes(N, K);
+    long b = ozg_img_bytes(N, K, digits) + ozg_scale_bytes(N, K) + 512;     // same: A is B or a row window of B
+    if (!same) b += ozg_img_bytes(M, K, digits) + ozg_scale_bytes(M, K);
     return b;
 }
 

@@ -221,11 +221,19 @@ def slice_w(W: torch.Tensor, npad: int, digits: int | None = None, wimg_out=None
     return wimg, wscale, digits
 
 
+def kinv_row_hull(r0: int, r1: int, npad: int) -> tuple[int, int]:
+    """128-aligned hull of the row range [r0, r1) inside [0, npad] (the granularity of gpk_kinv_rows)."""
+    if r1 <= r0:
+        return 0, 0
+    return r0 // TILE * TILE, min(npad, round_up(r1, TILE))
+
+
 def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *, center=None,
               want_kinv: bool = False, W_out: torch.Tensor | None = None, max_tries: int = 3,
               digits: int | None = None, wimg_out=None, wscale_out=None,
               want_image: bool = True) -> tuple[GPFit, FitScratch]:
     """Assemble K, Cholesky, W = L^-1, alpha, y^T K^-1 y and log det K on the GPU (float64).
+    want_kinv: True also forms K^-1 (ws.Kinv); a (r0, r1) tuple forms only those rows of it (row-split gradient).
 
     Replaces the gpytorch work behind gpmpc/gp.py:61-62 (train mode) and the prediction-strategy cache
     behind gpmpc/gpmpc.py:444 (eval mode).  On a failed pivot the diagonal jitter policy of gpytorch's
@@ -261,7 +269,14 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
         call("gpk_trtri", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(W), npad, ptr(ws.U), npad, ptr(ws.T), ws.T.numel(), st)
         call("gpk_solve_alpha", ptr(W), npad, ptr(ws.U), npad, ptr(ws.L), npad, npad, ptr(ws.y_pad), ptr(ws.t_work),
              ptr(alpha), ptr(ws.scal), st)
-        if want_kinv:
+        if isinstance(want_kinv, tuple) and kinv_row_hull(want_kinv[0], want_kinv[1], npad) == (0, npad):
+            want_kinv = True            # all rows: the symmetric product (lower tiles + mirror) is 3x cheaper
+        if isinstance(want_kinv, tuple):
+            # row-split gradient: only the (128-aligned hull of the) rows this rank's share of the trace reads
+            k0, k1 = kinv_row_hull(want_kinv[0], want_kinv[1], npad)
+            if k1 > k0:
+                call("gpk_kinv_rows", ptr(ws.U), npad, npad, k0, k1, ptr(ws.need_kinv()), npad, st)
+        elif want_kinv:
             call("gpk_kinv", ptr(ws.U), npad, npad, ptr(ws.need_kinv()), npad, st)
         info = int(ws.info.item())          # the reference syncs here too (loss value / NotPSD check)
         if info == 0:

@@ -348,7 +348,9 @@ def _loss_and_set_grads(gp: GaussianProcess, dev: torch.device, W_buf: torch.Ten
         Xd = X.detach().to(dev, torch.float64).contiguous()
         cache = gp._fit_cache = (X, Xd, gp.train_targets.detach().to(dev, torch.float64).contiguous(), Xd.mean(dim=0).cpu(),
                                  gp.train_targets)
-    fit, ws = E.factorize(cache[1], cache[2], ell, sf2, noise, center=cache[3], want_kinv=True, W_out=W_buf,
+    # a row-split reducer (sharding.RowSplitGradReduce) names the rows of K^-1 this rank needs; everyone else gets all
+    want_kinv = grad_reduce.rows(gp.n_ind_points) if hasattr(grad_reduce, "rows") else True
+    fit, ws = E.factorize(cache[1], cache[2], ell, sf2, noise, center=cache[3], want_kinv=want_kinv, W_out=W_buf,
                           want_image=False)
     if grad_reduce is None:
         partials = E.grad_partials(fit, ws)

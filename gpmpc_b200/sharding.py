@@ -160,12 +160,47 @@ def allreduce_row_partials(partials_fn: Callable[[int, int], torch.Tensor], n_ro
     return part
 
 
+def balanced_row_bounds(n: int, world: int, rank: int, align: int = 128) -> tuple[int, int]:
+    """Row block [r0, r1) of `rank` for the row-split K^-1 + gradient trace of one GP.  Row i of K^-1 = U U^T costs
+    (n - i) n multiply-adds (upper-triangular U), so equal work means equal integrals of (n - i):
+    r_g = n (1 - sqrt(1 - g / world)), rounded to `align` (the tile of gpk_kinv_rows); the last block ends at n."""
+    assert world >= 1 and 0 <= rank < world and n >= 0
+
+    def cut(g: int) -> int:
+        if g >= world:
+            return n
+        r = n * (1.0 - (1.0 - g / world) ** 0.5)
+        return min(n, int(round(r / align)) * align)
+
+    return cut(rank), max(cut(rank), cut(rank + 1))
+
+
+class RowSplitGradReduce:
+    """grad_reduce callback for gp.fit_gp(..., grad_reduce=...): every rank factorises the same GP (the Cholesky is not
+    distributed), forms ONLY its rows of K^-1 (`rows(n)`, picked up by the fit loop) and reduces the
+    gradient trace over them; one all_reduce(sum) of d+2 doubles completes the gradient on every rank."""
+
+    def __init__(self, group=None):
+        self.group = group
+
+    def rows(self, n: int) -> tuple[int, int]:
+        rank, world = world_info(self.group)
+        return balanced_row_bounds(n, world, rank)
+
+    def __call__(self, fit, ws):
+        from . import engine as E
+
+        rank, world = world_info(self.group)
+        r0, r1 = balanced_row_bounds(fit.n, world, rank)
+        if r1 > r0:
+            part = E.grad_partials(fit, ws, r0, r1).clone()
+        else:   # empty block (small n): contributes zeros, and must not touch K^-1 rows it never formed
+            part = torch.zeros(E._lib.load().gpk_pad_dim(fit.d) + 2, dtype=torch.float64, device=fit.device)
+        if world > 1:
+            dist.all_reduce(part, op=dist.ReduceOp.SUM, group=self.group)
+        return part
+
+
 def rowsplit_grad_reduce(group=None) -> Callable:
-    """grad_reduce callback for gp.fit_gp(..., grad_reduce=...): every rank factorises the same GP (the
-    Cholesky is not distributed) and the N x N trace pass is split by rows and all-reduced."""
-    from . import engine as E
-
-    def reduce(fit, ws):
-        return allreduce_row_partials(lambda r0, r1: E.grad_partials(fit, ws, r0, r1), fit.n, group=group)
-
-    return reduce
+    """See RowSplitGradReduce."""
+    return RowSplitGradReduce(group)

@@ -63,6 +63,9 @@ long gpk_trtri_scratch_elems(long npad);
 int gpk_trtri(const double* L, long ldl, long npad, const double* dinv, double* W, long ldw,
               double* U, long ldu, double* tmp, long tmp_elems, void* stream);
 int gpk_kinv(const double* U, long ldu, long npad, double* Kinv, long ldk, void* stream);
+/* Rows [r0, r1) (multiples of 128) of K^-1 with all their columns: what one rank of a row-split MLL gradient needs
+ * (SURVEY.md 8e); the other rows of Kinv are not touched. */
+int gpk_kinv_rows(const double* U, long ldu, long npad, long r0, long r1, double* Kinv, long ldk, void* stream);
 
 /* ---- (3) alpha, y^T K^-1 y, log det K --------------------------------------------------------
  * alpha = K^-1 y = U (W y); scal[0] = y^T K^-1 y, scal[1] = log det K (from diag L).  Replaces the
@@ -203,7 +206,8 @@ int gpk_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C
  * The O(N^3) steps behind gpmpc/gp.py:62 (Cholesky, solves) and gpmpc/gp.py:46 (inverse) are GEMMs of the contract
  * above.  gpk_oz_dgemm_nt runs one of them error-free on int8 digit slices (`digits` = 5/6/7 balanced base-256
  * digits per operand, power-of-two scales per row and chunk of 4096 k; exact int32 accumulation in TMEM, fp64
- * recombination): M, N multiples of 128, K of 64, a_tri != 0 needs M == K, C must not alias A or B.
+ * recombination): M, N multiples of 128, K of 64, a_tri != 0 needs M <= K, C must not alias A or B; when A is B or a
+ * 128-aligned window of B's rows one digit image serves both operands.
  * Scratch: gpk_oz_dgemm_nt_work_bytes(M, N, K, same = (A == B), digits).
  * gpk_oz_gemm_set_workspace registers per-device scratch (gpk_oz_gemm_work_bytes(npad, digits)) that makes
  * gpk_potrf / gpk_trtri / gpk_kinv / gpk_dgemm_nt route every GEMM with M, N >= min_dim (0 = keep the default of

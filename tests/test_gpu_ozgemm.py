@@ -148,3 +148,27 @@ def test_fit_int8_gemms_agree_with_dmma_path(fit_gemm_settings):
     assert o.rel_err(a1.cpu(), a0.cpu()) < 1e-7
     assert o.rel_err(w1.cpu(), w0.cpu()) < 1e-7
     assert o.rel_err(g1.cpu(), g0.cpu()) < 1e-7
+
+
+@pytest.mark.parametrize("digits", [0, 6])
+def test_kinv_rows_match_full_inverse(fit_gemm_settings, digits):
+    """gpk_kinv_rows (row-split gradient) against the rows of the full K^-1, on the DMMA and on the int8 path (where
+    the window of U shares one digit image with U)."""
+    E = fit_gemm_settings
+    n, d = 4096, 16
+    p = o.synthetic_problem(n, d, 1, seed=3)
+    X, y = p["X"].to(_dev()), p["Y"][:, 0].to(_dev())
+    E.FIT_GEMM_DIGITS, E.FIT_GEMM_MIN_NPAD, E.FIT_GEMM_MIN_WORK_G = digits, 1024, 1
+    E.release_scratch()
+    fit, ws = E.factorize(X, y, p["ell"], p["sf2"], p["noise"], want_kinv=True, want_image=False)
+    full = ws.Kinv.clone()
+    gfull = E.grad_partials(fit, ws).clone()
+    acc = torch.zeros_like(gfull)
+    for r0, r1 in ((0, 1000), (1000, 2304), (2304, 4096)):      # unaligned cuts: the 128-hull is formed
+        ws.Kinv.fill_(float("nan"))
+        fit2, ws2 = E.factorize(X, y, p["ell"], p["sf2"], p["noise"], want_kinv=(r0, r1), want_image=False)
+        k0, k1 = E.kinv_row_hull(r0, r1, fit2.npad)
+        assert o.rel_err(ws2.Kinv[k0:k1].cpu(), full[k0:k1].cpu()) < (1e-12 if digits == 0 else 1e-8)
+        assert bool(torch.isnan(ws2.Kinv[:k0]).all()) and bool(torch.isnan(ws2.Kinv[k1:]).all())
+        acc += E.grad_partials(fit2, ws2, r0, r1)
+    assert o.rel_err(acc.cpu(), gfull.cpu()) < 1e-9
