@@ -57,7 +57,7 @@ def make_hyp(center, ell, sf2: float, noise: float, d: int, device) -> torch.Ten
 # balanced base-256 digits per operand (csrc/ozgemm.cu): 7 digits reproduce the DMMA result to ~2e-15 of max|C|,
 # 6 to ~5e-13, 5 to ~1e-10; 0 keeps every GEMM on the FP64 DMMA pipe.
 FIT_GEMM_DIGITS = 6
-FIT_GEMM_MIN_NPAD = 4096
+FIT_GEMM_MIN_NPAD = 2048
 FIT_GEMM_MIN_WORK_G = 0     # tuning hook: smallest GEMM (1e9 multiply-adds) sent to the int8 path; 0 = library default
 
 
