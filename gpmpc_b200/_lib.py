@@ -29,6 +29,7 @@ SIGNATURES = {
     "gpk_potrf": (_i, [_p, _l, _l, _p, _p, _p]),
     "gpk_trtri_scratch_elems": (_l, [_l]),
     "gpk_trtri": (_i, [_p, _l, _l, _p, _p, _l, _p, _l, _p, _l, _p]),
+    "gpk_potrf_trtri": (_i, [_p, _l, _l, _p, _p, _p, _l, _p, _l, _p, _l, _p]),
     "gpk_kinv": (_i, [_p, _l, _l, _p, _l, _p]),
     "gpk_kinv_rows": (_i, [_p, _l, _l, _l, _l, _p, _l, _p]),
     "gpk_solve_alpha": (_i, [_p, _l, _p, _l, _p, _l, _l, _p, _p, _p, _p, _p]),

@@ -24,5 +24,7 @@ struct GemmParams {
 
 // int8 digit path for the large fit GEMMs (ozgemm.cu): 1 = handled, 0 = not eligible, < 0 = error
 int ozg_try(const GemmParams& p, int batch, cudaStream_t st);
+// which half of the registered scratch the following GEMMs of this host thread may use (0 = all, 1 / 2 = a half)
+void ozg_set_partition(int part);
 
 }  // namespace gpk

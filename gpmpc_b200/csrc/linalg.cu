@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include "dgemm_nt.cuh"
 #include <type_traits>
+#include <vector>
 
 namespace gpk {
 
@@ -507,6 +508,69 @@ static int trtri_rec(const RecInv& r, long off, long n) {
     return launch_transpose(W21, r.ldw, r.U + off * r.ldu + off + n1, r.ldu, n2, n1, r.st);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Factorisation with the inverse factor computed BESIDE it (gpk_potrf_trtri).  The Cholesky recursion is a chain of
+// small dependent kernels at its bottom levels (a 128-leaf is ONE CTA on 148 SMs); W = L^-1 of an already factored
+// diagonal block only needs that block, so all of trtri's work goes to a side stream in the recursion's post-order
+// and fills the idle SMs.  Events carry the two dependencies main -> side: "leaf factored + its inverse emitted"
+// and "L21 of this node final"; the side stream's own order gives W11, W22 before a node's combine.
+// ------------------------------------------------------------------------------------------------
+struct FitSide {
+    cudaStream_t side = nullptr;
+    std::vector<cudaEvent_t> pool;
+    size_t next = 0;
+    int get(cudaEvent_t* e) {
+        if (next == pool.size()) {
+            cudaEvent_t ev;
+            GPK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            pool.push_back(ev);
+        }
+        *e = pool[next++];
+        return 0;
+    }
+};
+static FitSide g_fit_side[64];
+
+struct RecBoth {
+    Rec f;             // factorisation, on f.st (the caller's stream)
+    RecInv v;          // inverse factor, on v.st (the side stream)
+    FitSide* fs;
+};
+
+static int potrf_trtri_rec(const RecBoth& r, long off, long n) {
+    cudaEvent_t ev;
+    if (n == TILE) {
+        ozg_set_partition(1);
+        GPK_TRY(launch_potf2(r.f.A + off * r.f.lda + off, r.f.lda, r.f.Dinv + (off / TILE) * TILE * TILE, r.f.info, (int)off, r.f.st));
+        GPK_TRY(r.fs->get(&ev));
+        GPK_CUDA(cudaEventRecord(ev, r.f.st));
+        GPK_CUDA(cudaStreamWaitEvent(r.v.st, ev, 0));
+        ozg_set_partition(2);
+        return trtri_rec(r.v, off, TILE);                       // leaf: copy + transpose of the emitted inverse
+    }
+    const long n1 = split(n), n2 = n - n1;
+    GPK_TRY(potrf_trtri_rec(r, off, n1));
+    ozg_set_partition(1);
+    GPK_TRY(trsm_rec(r.f, off + n1, n2, off, n1));
+    GPK_TRY(r.fs->get(&ev));
+    GPK_CUDA(cudaEventRecord(ev, r.f.st));                       // L21 final
+    double* A21 = r.f.A + (off + n1) * r.f.lda + off;
+    double* A22 = r.f.A + (off + n1) * r.f.lda + off + n1;
+    GPK_TRY(launch_dgemm_nt(gemm_args(A21, r.f.lda, A21, r.f.lda, A22, r.f.lda, n2, n2, n1, -1.0, 1.0, 0, 1), 0, 1, r.f.st));
+    GPK_TRY(potrf_trtri_rec(r, off + n1, n2));
+    // combine on the side stream (W11 / U11 and W22 are already ordered there)
+    ozg_set_partition(2);
+    GPK_CUDA(cudaStreamWaitEvent(r.v.st, ev, 0));
+    const RecInv& v = r.v;
+    const double* U11 = v.U + off * v.ldu + off;
+    const double* L21 = v.L + (off + n1) * v.ldl + off;
+    GPK_TRY(launch_dgemm_nt(gemm_args(U11, v.ldu, L21, v.ldl, v.T, n2, n1, n2, n1, 1.0, 0.0, 2, 0), 0, 1, v.st));
+    const double* W22 = v.W + (off + n1) * v.ldw + off + n1;
+    double* W21 = v.W + (off + n1) * v.ldw + off;
+    GPK_TRY(launch_dgemm_nt(gemm_args(W22, v.ldw, v.T, n2, W21, v.ldw, n2, n1, n2, -1.0, 0.0, 1, 0), 0, 1, v.st));
+    return launch_transpose(W21, v.ldw, v.U + off * v.ldu + off + n1, v.ldu, n2, n1, v.st);
+}
+
 }  // namespace gpk
 
 // ================================================================================================
@@ -550,6 +614,43 @@ int gpk_trtri(const double* L, long ldl, long npad, const double* dinv, double* 
     GPK_CUDA(cudaMemset2DAsync(U, ldu * 8, 0, npad * 8, npad, st));
     RecInv r{st, L, ldl, dinv, W, ldw, U, ldu, tmp};
     return trtri_rec(r, 0, npad);
+}
+
+// gpk_potrf followed by gpk_trtri, with the inverse factor computed on an internal side stream beside the
+// factorisation (fork after the caller's prior work, join before returning control of `stream`): same results,
+// same kernels, shorter critical path.
+int gpk_potrf_trtri(double* A, long lda, long npad, double* dinv, int* info_dev, double* W, long ldw, double* U, long ldu,
+                    double* tmp, long tmp_elems, void* stream) {
+    GPK_ARG(npad > 0 && npad % TILE == 0, "npad must be a positive multiple of 128");
+    GPK_ARG(lda >= npad && lda % 2 == 0, "lda");
+    GPK_ARG(A && dinv && info_dev && W && U, "null pointer");
+    GPK_ARG(ldw >= npad && ldu >= npad && ldw % 2 == 0 && ldu % 2 == 0, "ldw/ldu");
+    if (npad > TILE) {
+        const long n1 = split(npad), n2 = npad - n1;
+        GPK_ARG(tmp && tmp_elems >= n1 * n2, "scratch too small (need split(n) * (n - split(n)) doubles)");
+    }
+    int dev = 0;
+    cudaGetDevice(&dev);
+    GPK_ARG(dev >= 0 && dev < 64, "device index");
+    FitSide& fs = g_fit_side[dev];
+    if (!fs.side) GPK_CUDA(cudaStreamCreateWithFlags(&fs.side, cudaStreamNonBlocking));
+    fs.next = 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaEvent_t ev;
+    GPK_TRY(fs.get(&ev));
+    GPK_CUDA(cudaEventRecord(ev, st));                            // fork: the side stream starts after the caller's prior work
+    GPK_CUDA(cudaStreamWaitEvent(fs.side, ev, 0));
+    GPK_CUDA(cudaMemsetAsync(info_dev, 0, sizeof(int), st));
+    GPK_CUDA(cudaMemset2DAsync(W, ldw * 8, 0, npad * 8, npad, fs.side));
+    GPK_CUDA(cudaMemset2DAsync(U, ldu * 8, 0, npad * 8, npad, fs.side));
+    RecBoth r{Rec{st, A, lda, dinv, info_dev}, RecInv{fs.side, A, lda, dinv, W, ldw, U, ldu, tmp}, &fs};
+    const int rc = potrf_trtri_rec(r, 0, npad);
+    ozg_set_partition(0);
+    GPK_TRY(rc);
+    GPK_TRY(fs.get(&ev));
+    GPK_CUDA(cudaEventRecord(ev, fs.side));                       // join
+    GPK_CUDA(cudaStreamWaitEvent(st, ev, 0));
+    return 0;
 }
 
 long gpk_trtri_scratch_elems(long npad) {

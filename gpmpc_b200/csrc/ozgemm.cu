@@ -499,8 +499,18 @@ static int ozg_dispatch(const GemmParams& p, int S, uint8_t* work, cudaStream_t 
 }
 
 // called by launch_dgemm_nt (linalg.cu): 1 = handled on the int8 pipe, 0 = not eligible (use the DMMA kernel), < 0 error
+// Two enqueuing contexts may be in flight at once (gpk_potrf_trtri: the factorisation on the caller's stream, the
+// inverse factor on a side stream): each gets its own half of the registered scratch.  0 = whole scratch.
+static thread_local int g_ozg_part = 0;
+void ozg_set_partition(int part) { g_ozg_part = part; }
+
 int ozg_try(const GemmParams& p, int batch, cudaStream_t st) {
-    const OzgWorkspace& ws = g_ozg_ws[ozg_device()];
+    OzgWorkspace ws = g_ozg_ws[ozg_device()];
+    if (ws.ptr != nullptr && g_ozg_part != 0) {
+        const long half = ws.bytes / 2 / 256 * 256;
+        ws.ptr = static_cast<uint8_t*>(ws.ptr) + (g_ozg_part == 2 ? half : 0);
+        ws.bytes = half;
+    }
     if (ws.ptr == nullptr || ws.digits == 0 || batch != 1) return 0;
     if (p.M < g_ozg_min_dim || p.N < g_ozg_min_dim || p.K < 1024) return 0;
     // below ~1.2e10 useful multiply-adds the slicing passes and the 74-pair tile quantisation eat the gain

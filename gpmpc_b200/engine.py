@@ -58,6 +58,7 @@ def make_hyp(center, ell, sf2: float, noise: float, d: int, device) -> torch.Ten
 # 6 to ~5e-13, 5 to ~1e-10; 0 keeps every GEMM on the FP64 DMMA pipe.
 FIT_GEMM_DIGITS = 6
 FIT_GEMM_MIN_NPAD = 2048
+FIT_OVERLAP_INVERSE = True  # W = L^-1 on a side stream beside the Cholesky recursion (gpk_potrf_trtri)
 FIT_GEMM_MIN_WORK_G = 0     # tuning hook: smallest GEMM (1e9 multiply-adds) sent to the int8 path; 0 = library default
 
 
@@ -263,10 +264,14 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
         hyp = make_hyp(center_h, ell_t, sf2, noise + jitter, d, dev)
         call("gpk_cross_kernel", 1, ptr(X), X.stride(0), n, 0, ptr(X), X.stride(0), n, 0, d, ptr(hyp), ptr(ws.L),
              npad, 0, npad, npad, 1, 1, st)
-        call("gpk_potrf", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(ws.info), st)
         # the rest of the chain is enqueued before the pivot check is read back (one host round trip per fit instead of
         # two; a failed factorisation is rare and only costs the wasted launches)
-        call("gpk_trtri", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(W), npad, ptr(ws.U), npad, ptr(ws.T), ws.T.numel(), st)
+        if FIT_OVERLAP_INVERSE:
+            call("gpk_potrf_trtri", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(ws.info), ptr(W), npad, ptr(ws.U), npad,
+                 ptr(ws.T), ws.T.numel(), st)
+        else:
+            call("gpk_potrf", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(ws.info), st)
+            call("gpk_trtri", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(W), npad, ptr(ws.U), npad, ptr(ws.T), ws.T.numel(), st)
         call("gpk_solve_alpha", ptr(W), npad, ptr(ws.U), npad, ptr(ws.L), npad, npad, ptr(ws.y_pad), ptr(ws.t_work),
              ptr(alpha), ptr(ws.scal), st)
         if isinstance(want_kinv, tuple) and kinv_row_hull(want_kinv[0], want_kinv[1], npad) == (0, npad):

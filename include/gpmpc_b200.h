@@ -62,6 +62,12 @@ int gpk_potrf(double* A, long lda, long npad, double* dinv, int* info_dev, void*
 long gpk_trtri_scratch_elems(long npad);
 int gpk_trtri(const double* L, long ldl, long npad, const double* dinv, double* W, long ldw,
               double* U, long ldu, double* tmp, long tmp_elems, void* stream);
+/* gpk_potrf followed by gpk_trtri in one call: same kernels and results, but the inverse factor is computed beside
+ * the factorisation on a side stream of the library (forked after the work already enqueued on `stream`, joined
+ * before this call's effects are visible to later work on `stream`), which fills the SMs the small dependent kernels
+ * of the Cholesky recursion leave idle. */
+int gpk_potrf_trtri(double* A, long lda, long npad, double* dinv, int* info_dev, double* W, long ldw,
+                    double* U, long ldu, double* tmp, long tmp_elems, void* stream);
 int gpk_kinv(const double* U, long ldu, long npad, double* Kinv, long ldk, void* stream);
 /* Rows [r0, r1) (multiples of 128) of K^-1 with all their columns: what one rank of a row-split MLL gradient needs
  * (SURVEY.md 8e); the other rows of Kinv are not touched. */
