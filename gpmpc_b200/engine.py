@@ -58,6 +58,9 @@ def make_hyp(center, ell, sf2: float, noise: float, d: int, device) -> torch.Ten
 # 6 to ~5e-13, 5 to ~1e-10; 0 keeps every GEMM on the FP64 DMMA pipe.
 FIT_GEMM_DIGITS = 6
 FIT_GEMM_MIN_NPAD = 2048
+# K^-1 = U U^T only feeds the MLL gradient (and gp.K_inv): one digit less there costs ~1e-9 on the gradient (nothing on
+# the MLL, alpha or the predictions) and removes 6 of its 21 digit products.  0 = same digits as the factorisation.
+FIT_GEMM_DIGITS_KINV = 5
 FIT_OVERLAP_INVERSE = True  # W = L^-1 on a side stream beside the Cholesky recursion (gpk_potrf_trtri)
 FIT_GEMM_MIN_WORK_G = 0     # tuning hook: smallest GEMM (1e9 multiply-adds) sent to the int8 path; 0 = library default
 
@@ -274,6 +277,10 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
             call("gpk_trtri", ptr(ws.L), npad, npad, ptr(ws.dinv), ptr(W), npad, ptr(ws.U), npad, ptr(ws.T), ws.T.numel(), st)
         call("gpk_solve_alpha", ptr(W), npad, ptr(ws.U), npad, ptr(ws.L), npad, npad, ptr(ws.y_pad), ptr(ws.t_work),
              ptr(alpha), ptr(ws.scal), st)
+        kinv_digits = int(FIT_GEMM_DIGITS_KINV) if ws.gemm_work is not None else 0
+        switch_digits = bool(want_kinv) and 5 <= kinv_digits < ws.gemm_digits      # the scratch is sized for gemm_digits
+        if switch_digits:
+            _register_fit_gemm_workspace(ws.gemm_work, kinv_digits)
         if isinstance(want_kinv, tuple) and kinv_row_hull(want_kinv[0], want_kinv[1], npad) == (0, npad):
             want_kinv = True            # all rows: the symmetric product (lower tiles + mirror) is 3x cheaper
         if isinstance(want_kinv, tuple):
@@ -283,6 +290,8 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
                 call("gpk_kinv_rows", ptr(ws.U), npad, npad, k0, k1, ptr(ws.need_kinv()), npad, st)
         elif want_kinv:
             call("gpk_kinv", ptr(ws.U), npad, npad, ptr(ws.need_kinv()), npad, st)
+        if switch_digits:
+            _register_fit_gemm_workspace(ws.gemm_work, ws.gemm_digits)
         info = int(ws.info.item())          # the reference syncs here too (loss value / NotPSD check)
         if info == 0:
             break

@@ -172,3 +172,27 @@ def test_kinv_rows_match_full_inverse(fit_gemm_settings, digits):
         assert bool(torch.isnan(ws2.Kinv[:k0]).all()) and bool(torch.isnan(ws2.Kinv[k1:]).all())
         acc += E.grad_partials(fit2, ws2, r0, r1)
     assert o.rel_err(acc.cpu(), gfull.cpu()) < 1e-9
+
+
+@pytest.mark.parametrize("n", [300, 1000, 2304])
+def test_overlapped_inverse_is_bit_identical(fit_gemm_settings, n):
+    """gpk_potrf_trtri (inverse factor on a side stream beside the factorisation) against gpk_potrf + gpk_trtri on one
+    stream: same kernels on the same data, so L, W = L^-1, U = W^T, alpha and the scalars must agree bit for bit --
+    any difference is a missing dependency between the two streams.  Repeated to give a race a chance to show."""
+    E = fit_gemm_settings
+    p = o.synthetic_problem(n, 16, 1, seed=n)
+    X, y = p["X"].to(_dev()), p["Y"][:, 0].to(_dev())
+    saved = E.FIT_OVERLAP_INVERSE
+    try:
+        E.FIT_OVERLAP_INVERSE = False
+        fit0, ws0 = E.factorize(X, y, p["ell"], p["sf2"], p["noise"], want_kinv=True)
+        ref = [t.clone() for t in (ws0.L, fit0.W, ws0.U, fit0.alpha, ws0.Kinv)] + [fit0.quad, fit0.logdet]
+        E.FIT_OVERLAP_INVERSE = True
+        for _ in range(5):
+            fit1, ws1 = E.factorize(X, y, p["ell"], p["sf2"], p["noise"], want_kinv=True)
+            got = [ws1.L, fit1.W, ws1.U, fit1.alpha, ws1.Kinv]
+            for a, b in zip(got, ref[:5]):
+                assert torch.equal(a, b)
+            assert (fit1.quad, fit1.logdet) == (ref[5], ref[6])
+    finally:
+        E.FIT_OVERLAP_INVERSE = saved

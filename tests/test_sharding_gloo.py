@@ -89,6 +89,27 @@ def _worker(rank, world, port, q_total):
 
         red = S.allreduce_row_partials(partials, n)
         assert torch.allclose(red, partials(0, n), rtol=1e-12, atol=1e-12)
+        # --- the fit loop's reducer: balanced row blocks (rank 0's block is EMPTY at n = 60: cuts are 128-aligned), the
+        #     product callable replaced by the oracle double, padded like engine.grad_partials (pad_dim(d) + 2 entries)
+        from gpmpc_b200 import engine as E
+
+        pad = E._lib.load().gpk_pad_dim(d) + 2
+
+        class _Fit:
+            pass
+
+        fake = _Fit()
+        fake.n, fake.d, fake.device = n, d, torch.device("cpu")
+        rsr = S.rowsplit_grad_reduce()
+        assert rsr.rows(n) == S.balanced_row_bounds(n, world, rank)
+        assert rsr.rows(n) == ((0, 0) if rank == 0 else (0, n))
+        orig = E.grad_partials
+        E.grad_partials = lambda fit, ws, r0, r1: torch.cat([partials(r0, r1), torch.zeros(pad - d - 2, dtype=torch.float64)])
+        try:
+            red2 = rsr(fake, None)
+        finally:
+            E.grad_partials = orig
+        assert red2.shape == (pad,) and torch.allclose(red2[: d + 2], partials(0, n), rtol=1e-12, atol=1e-12)
         # --- output-GP sharding: each rank "fits" its own GPs, everybody gets all results
         calls = []
 

@@ -9,6 +9,7 @@ noise = float(sys.argv[2]) if len(sys.argv) > 2 else 1e-2
 E.FIT_GEMM_MIN_WORK_G = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 DIGITS = [int(a) for a in sys.argv[4].split(',')] if len(sys.argv) > 4 else [0, 5, 6, 7]
 E.FIT_OVERLAP_INVERSE = bool(int(sys.argv[5])) if len(sys.argv) > 5 else E.FIT_OVERLAP_INVERSE
+E.FIT_GEMM_DIGITS_KINV = int(sys.argv[6]) if len(sys.argv) > 6 else E.FIT_GEMM_DIGITS_KINV
 for N in [int(a) for a in sys.argv[1].split(',')]:
     g = torch.Generator().manual_seed(1337)
     X = (torch.rand(N, D, generator=g, dtype=torch.float64) * 2 - 1).to(dev)
