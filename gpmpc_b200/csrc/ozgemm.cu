@@ -203,7 +203,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * 8, 1) ozg_
                         for (int t = 0; t < S; t++) {
                             const uint64_t adesc = umma_smem_desc(a_base + t * OZ_A_SLICE + j * 256, 128, OZ_BK * 8);
                             const uint32_t acc = (kb > c0 || j > 0 || t > 0) ? 1u : 0u;
-                            constexpr int dummy = 0; (void)dummy;
                             const int ntot = OZ_WB * (S - t);
                             const int nparts = ntot > 256 ? 2 : 1;
                             const int npart = ntot / nparts;
