@@ -228,6 +228,17 @@ mean_jac_kernel(const MeanJacArgs a) {
         ez[r] = (T)(-0.5) * s * ESCALE;
         m[r] = 0;
     }
+    constexpr bool PACK = sizeof(T) == 4 && DP % 2 == 0;
+    float2 zl2[RQ][PACK ? DP / 2 : 1], S2[RQ][PACK ? DP / 2 : 1];
+    if constexpr (PACK) {
+#pragma unroll
+        for (int r = 0; r < RQ; r++)
+#pragma unroll
+            for (int jj = 0; jj < DP / 2; jj++) {
+                zl2[r][jj] = make_float2((float)zl[r][2 * jj], (float)zl[r][2 * jj + 1]);
+                S2[r][jj] = make_float2(0.f, 0.f);
+            }
+    }
 
     for (int t = t_begin; t < t_end; t++) {
         const int it = t - t_begin, cur = it & 1;
@@ -244,18 +255,46 @@ mean_jac_kernel(const MeanJacArgs a) {
             T x[DP];
             load_row<T, DP>(xs + i * DP, x);
             const T e = es[i], al = as[i];
+            if constexpr (PACK) {
+                // float32: both GEMM-shaped parts as packed FFMA2 (fma.rn.f32x2) over pairs of input dimensions --
+                // Blackwell's FP32 pipe only reaches its 128 FMA/clk/SM through the packed form
+                float2 x2[DP / 2];
 #pragma unroll
-            for (int r = 0; r < RQ; r++) {
-                T s = e + ez[r];
+                for (int jj = 0; jj < DP / 2; jj++) x2[jj] = make_float2((float)x[2 * jj], (float)x[2 * jj + 1]);
 #pragma unroll
-                for (int j = 0; j < DP; j++) s = fma(zl[r][j], x[j], s);
-                const T w = kexp_sel<TAB>(s, etab) * al;
-                m[r] += w;
+                for (int r = 0; r < RQ; r++) {
+                    float2 s2 = make_float2((float)(e + ez[r]), 0.f);
 #pragma unroll
-                for (int j = 0; j < DP; j++) S[r][j] = fma(w, x[j], S[r][j]);
+                    for (int jj = 0; jj < DP / 2; jj++) s2 = __ffma2_rn(zl2[r][jj], x2[jj], s2);
+                    const float w = kexp(s2.x + s2.y) * (float)al;
+                    m[r] += (T)w;
+                    const float2 w2 = make_float2(w, w);
+#pragma unroll
+                    for (int jj = 0; jj < DP / 2; jj++) S2[r][jj] = __ffma2_rn(w2, x2[jj], S2[r][jj]);
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < RQ; r++) {
+                    T s = e + ez[r];
+#pragma unroll
+                    for (int j = 0; j < DP; j++) s = fma(zl[r][j], x[j], s);
+                    const T w = kexp_sel<TAB>(s, etab) * al;
+                    m[r] += w;
+#pragma unroll
+                    for (int j = 0; j < DP; j++) S[r][j] = fma(w, x[j], S[r][j]);
+                }
             }
         }
         __syncthreads();
+    }
+    if constexpr (PACK) {
+#pragma unroll
+        for (int r = 0; r < RQ; r++)
+#pragma unroll
+            for (int jj = 0; jj < DP / 2; jj++) {
+                S[r][2 * jj] = (T)S2[r][jj].x;
+                S[r][2 * jj + 1] = (T)S2[r][jj].y;
+            }
     }
 
     if (a.n_split == 1) {
