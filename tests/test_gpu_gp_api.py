@@ -190,6 +190,53 @@ def test_full_size_properties_config2():
     assert o.rel_err(j32[0][idx].cpu(), j_ref) < TOL32
 
 
+def test_full_size_properties_config3():
+    """BASELINE config 3 training size (N=16384, d=16; the fit runs its large GEMMs on the int8 tensor pipe, the
+    inverse factor on the side stream), checked through exact identities that need no O(N^3) oracle pass:
+      mean at the training inputs:  K_f alpha = y - noise * alpha          (from (K_f + noise I) alpha = y)
+      variance at a training input: var_f(x_i) = noise - noise^2 (K^-1)_ii  (from K_f K^-1 = I - noise K^-1)
+      y^T K^-1 y = y . alpha,  W W^T-free residual:  || L (L^T alpha) - y || small
+      Jacobian == central finite difference of the mean;  int8 variance path == DMMA variance path."""
+    from gpmpc_b200 import engine as E
+
+    dev = torch.device("cuda", 0)
+    n, d = 16384, 16
+    p = o.synthetic_problem(n, d, 512, p=1, seed=1337)
+    X, y, Z = p["X"].to(dev), p["Y"][:, 0].to(dev), p["Z"].to(dev)
+    noise, sf2 = p["noise"], p["sf2"]
+    fit, ws = E.factorize(X, y, p["ell"], sf2, noise, want_kinv=True)
+    assert ws.gemm_work is not None, "the int8 fit GEMMs must be active at this size"
+    alpha = fit.alpha[:n]
+    # residual of the linear system through the factor itself: K alpha = L (L^T alpha)
+    Lm = torch.tril(ws.L[:n, :n])
+    res = Lm @ (Lm.T @ alpha) - y
+    # 6-digit int8 GEMMs: 5.8e-8 measured (|K| ~ 4e3, |alpha| ~ 10: 1.5e-12 of |K| |alpha|); DMMA only: ~1e-11
+    assert float(res.abs().max()) < TOL64 * float(y.abs().max())
+    assert abs(fit.quad - float(y @ alpha)) < 1e-9 * abs(fit.quad)
+    assert abs(fit.logdet - 2.0 * float(torch.log(Lm.diagonal()).sum())) < 1e-10 * abs(fit.logdet)
+    # predictions at 1024 training inputs
+    idx = torch.arange(0, n, 16, device=dev)
+    mean, var, jac = E.predict(fit, X[idx])
+    assert o.rel_err(mean[0].cpu(), (y[idx] - noise * alpha[idx]).cpu()) < TOL64
+    kinv_diag = ws.Kinv.diagonal()[:n][idx]
+    assert o.rel_err(var[0].cpu(), (noise - noise * noise * kinv_diag).cpu()) < TOL64
+    assert float(var.min()) > 0.0 and float(var.max()) <= noise
+    # away from the data: both variance paths, Jacobian against finite differences of the mean
+    m1, v1, j1 = E.predict(fit, Z)
+    m2, v2, j2 = E.predict(fit, Z, var_path="f64")
+    assert o.rel_err(v1[0].cpu(), v2[0].cpu()) < TOL64 and o.rel_err(m1[0].cpu(), m2[0].cpu()) < 1e-10
+    assert float(v1.min()) > 0.0 and float(v1.max()) <= sf2
+    h = 1e-5
+    for j in (0, 7, 15):
+        e = torch.zeros(d, dtype=torch.float64, device=dev)
+        e[j] = h
+        mp = E.predict(fit, Z + e, want_var=False)[0]
+        mm = E.predict(fit, Z - e, want_var=False)[0]
+        fd = (mp - mm)[0] / (2 * h)
+        assert o.rel_err(j1[0][:, j].cpu(), fd.cpu()) < 1e-5
+    E.release_scratch()
+
+
 def test_predict_host_roundtrip():
     from gpmpc_b200 import engine as E
     from gpmpc_b200.gp import predict_host
