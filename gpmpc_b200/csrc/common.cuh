@@ -38,6 +38,13 @@ constexpr int TILE = 128;                 // every padded matrix dimension is a 
         return gpk::fail(-(1000 + (int)e_), "%s: kernel launch -> %s", __func__, cudaGetErrorString(e_)); } while (0)
 #define GPK_TRY(x) do { int r_ = (x); if (r_ != 0) return r_; } while (0)
 
+// index of the current device, clamped to the size of the per-device static tables
+inline int current_device() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return d < 0 || d >= 64 ? 0 : d;
+}
+
 // ---- small device helpers -----------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

@@ -351,7 +351,8 @@ __global__ void mean_jac_finalize_kernel(const MeanJacArgs a) {
 template <typename T, int DP, int RQ>
 static int launch_mean_jac_t(MeanJacArgs a, int batch, cudaStream_t st) {
     constexpr int smem = 2 * TP * (DP + 2) * (int)sizeof(T);
-    static bool attr_done = false;
+    static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
+    bool& attr_done = attr_dev[current_device()];
     if (!attr_done) {
         GPK_CUDA(cudaFuncSetAttribute(mean_jac_kernel<T, DP, RQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_done = true;

@@ -75,7 +75,8 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
         p.group_m = p.tiles_m <= 18 ? p.tiles_m : 12;
         p.group_n = 148 / p.group_m > 0 ? 148 / p.group_m : 1;
     }
-    static bool attr_done = false;
+    static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
+    bool& attr_done = attr_dev[current_device()];
     if (!attr_done) {
         GPK_CUDA(cudaFuncSetAttribute(dgemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
         GPK_CUDA(cudaFuncSetAttribute(var_colsq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_BYTES));
@@ -338,7 +339,8 @@ leaf_inv_kernel(const double* __restrict__ L, long ldl, double* __restrict__ Din
 }
 
 static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_offset, cudaStream_t st) {
-    static bool attr_done = false;
+    static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
+    bool& attr_done = attr_dev[current_device()];
     if (!attr_done) {
         GPK_CUDA(cudaFuncSetAttribute(potf2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
         GPK_CUDA(cudaFuncSetAttribute(leaf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PI_SMEM));

@@ -642,7 +642,8 @@ static int oz_num_pieces(long qtiles_total, long npairs_w) {
 template <int S>
 static int oz_launch_var(const OzArgs& a, cudaStream_t st) {
     constexpr int smem = oz_stages(S) * oz_stage_bytes(S);
-    static bool attr_done = false;
+    static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
+    bool& attr_done = attr_dev[current_device()];
     if (!attr_done) {
         GPK_CUDA(cudaFuncSetAttribute(oz_var_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_done = true;

@@ -460,7 +460,8 @@ static int ozg_run(const GemmParams& p, uint8_t* work, cudaStream_t st) {
     a.items = ozg_items(p.M / OZ_QT, p.N / (2 * OZ_WB), p.a_tri, p.c_lower, &a.total_items, st);
     GPK_ARG(a.items != nullptr, "could not build the item list");
     constexpr int smem = oz_stages(S) * oz_stage_bytes(S);
-    static bool attr_done = false;
+    static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
+    bool& attr_done = attr_dev[current_device()];
     if (!attr_done) {
         GPK_CUDA(cudaFuncSetAttribute(ozg_gemm_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr_done = true;

@@ -15,6 +15,7 @@ HBM layout (row-major, float64 unless noted; npad = N rounded up to 128, identit
 
 from __future__ import annotations
 
+import functools
 import math
 from dataclasses import dataclass, field
 
@@ -27,6 +28,27 @@ TILE = 128
 LOG_2PI = math.log(2.0 * math.pi)
 F64 = torch.float64
 DTYPE_CODE = {torch.float32: 0, torch.float64: 1}
+
+
+def _on_arg_device(fn):
+    """Run `fn` with the CUDA device of its first device-carrying argument current (kernels launch on the current
+    device; cudaFuncSetAttribute, the side stream and the registered scratch are per device).  A no-op in the usual
+    one-process-per-GPU setting where the caller already selected the device."""
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kw):
+        dev = None
+        for a in args:
+            d = getattr(a, "device", None)
+            if isinstance(d, torch.device) and d.type == "cuda":
+                dev = d
+                break
+        if dev is None or dev.index is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kw)
+        with torch.cuda.device(dev):
+            return fn(*args, **kw)
+
+    return wrapper
 
 
 class NotPSDError(RuntimeError):
@@ -212,6 +234,7 @@ def i8_supported(npad: int, digits: int | None = None) -> bool:
     return digits * npad * 16384 < 2 ** 31
 
 
+@_on_arg_device
 def slice_w(W: torch.Tensor, npad: int, digits: int | None = None, wimg_out=None, wscale_out=None):
     """int8 digit image + power-of-two row scales of W = L^-1 (operand of the tcgen05 variance contraction)."""
     lib = _lib.load()
@@ -232,6 +255,7 @@ def kinv_row_hull(r0: int, r1: int, npad: int) -> tuple[int, int]:
     return r0 // TILE * TILE, min(npad, round_up(r1, TILE))
 
 
+@_on_arg_device
 def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *, center=None,
               want_kinv: bool = False, W_out: torch.Tensor | None = None, max_tries: int = 3,
               digits: int | None = None, wimg_out=None, wscale_out=None,
@@ -308,6 +332,7 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
     return fit, ws
 
 
+@_on_arg_device
 def grad_partials(fit: GPFit, ws: FitScratch, r0: int = 0, r1: int | None = None) -> torch.Tensor:
     """(d+2) partial sums of the MLL gradient trace over rows [r0, r1) (device tensor, float64).
     Needs ws.Kinv from factorize(want_kinv=True)."""
@@ -334,6 +359,7 @@ def loss_and_grad_from_partials(fit: GPFit, partials: torch.Tensor):
     return loss, g_noise, g_sf2, g_ell
 
 
+@_on_arg_device
 def dense_K(fit: GPFit) -> torch.Tensor:
     """K_f(X,X) + noise I as a dense (N,N) tensor (gpmpc/gp.py:45)."""
     n, npad = fit.n, round_up(fit.n, 64)
@@ -343,6 +369,7 @@ def dense_K(fit: GPFit) -> torch.Tensor:
     return out[:n, :n]
 
 
+@_on_arg_device
 def cross_K(fit: GPFit, A: torch.Tensor, B: torch.Tensor | None = None) -> torch.Tensor:
     """Noise-free K_f(A, B) with this GP's hyper-parameters (gp.covar_module(a, b).to_dense(), gpmpc.py:392-393)."""
     dev = fit.device
@@ -428,6 +455,7 @@ class GPBatch:
         return self.packs[dtype]
 
 
+@_on_arg_device
 def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise, digits: int | None = None) -> GPBatch:
     """Fit P independent GPs that share the inputs X (N,d) with targets Y (N,P) at fixed hyper-parameters.
     ell: (P,d) or (d,) ; sf2, noise: (P,) or scalars.  The factors are written straight into one stacked buffer."""
@@ -456,6 +484,7 @@ def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise, digits: int | N
 VAR_WORK_BYTES = 4 << 30   # default scratch budget for the K_ZX chunks of the variance path
 
 
+@_on_arg_device
 def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_work_bytes: int | None = None,
             var_path: str = "i8", mj_event: torch.cuda.Event | None = None, mj_path: str = "auto",
             want_mean_jac: bool = True):
@@ -534,6 +563,7 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
     return mean, var, jac
 
 
+@_on_arg_device
 def posterior_covariance(fit: GPFit, Z: torch.Tensor) -> torch.Tensor:
     """Dense latent posterior covariance K_zz - K_zX K^-1 K_Xz (Q,Q) for modest Q: the matrix
     gp(z).covariance_matrix returns at gpmpc/gpmpc.py:444 (the caller keeps only its diagonal, for which

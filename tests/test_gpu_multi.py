@@ -99,3 +99,25 @@ def _worker(rank, world, port):
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_two_gpu_nccl_sharding():
     mp.spawn(_worker, args=(2, _free_port()), nprocs=2, join=True)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_second_device_in_one_process():
+    """One process, two devices: tensors on cuda:1 while cuda:0 is current.  Launches, function attributes (dynamic
+    shared memory), the fit's side stream and the int8 GEMM scratch are all per device."""
+    from gpmpc_b200 import engine as E
+
+    assert torch.cuda.current_device() == 0
+    p = o.synthetic_problem(2304, 16, 300, p=1, seed=21)
+    outs = []
+    for idx in (0, 1):
+        dev = torch.device("cuda", idx)
+        fit, ws = E.factorize(p["X"].to(dev), p["Y"][:, 0].to(dev), p["ell"], p["sf2"], p["noise"], want_kinv=True)
+        part = E.grad_partials(fit, ws).cpu()
+        mean, var, jac = E.predict(fit, p["Z"].to(dev))
+        outs.append((fit.mll_per_n(), part, mean.cpu(), var.cpu(), jac.cpu()))
+        assert mean.device == dev and torch.cuda.current_device() == 0
+    assert outs[0][0] == outs[1][0]
+    for a, b in zip(outs[0][1:], outs[1][1:]):
+        assert torch.equal(a, b)
+    E.release_scratch()
