@@ -409,9 +409,15 @@ template <int DP>
 __global__ void __launch_bounds__(256)
 grad_trace_kernel(const double* __restrict__ X, long ldx, long n, int d, const double* __restrict__ hyp,
                   const double* __restrict__ Kinv, long ldk, const double* __restrict__ alpha, long r0, long r1,
-                  double* __restrict__ partial) {
+                  double* __restrict__ partial, int sym) {
     __shared__ double As[CK_T * CK_LD], Bs[CK_T * CK_LD], ea[CK_T], eb[CK_T], red[8][DP + 2];
     const long row0 = r0 + (long)blockIdx.y * CK_T, col0 = (long)blockIdx.x * CK_T;
+    // sym: the summand is symmetric in (a, b), so only b <= a is visited (b < a counted twice): half the K^-1
+    // traffic and exponentials, and only the lower triangle of K^-1 is read
+    if (sym && col0 > row0 + CK_T - 1) {
+        if (threadIdx.x < DP + 2) partial[((long)blockIdx.y * gridDim.x + blockIdx.x) * (DP + 2) + threadIdx.x] = 0.0;
+        return;
+    }
     stage_scaled_rows(X, ldx, n, row0, d, DP, hyp, As, ea);
     stage_scaled_rows(X, ldx, n, col0, d, DP, hyp, Bs, eb);
     __syncthreads();
@@ -441,10 +447,10 @@ grad_trace_kernel(const double* __restrict__ X, long ldx, long n, int d, const d
         for (int c = 0; c < 4; c++) {
             const long gr = row0 + ty * 4 + r, gc = col0 + tx + 16 * c;
             double v = 0.0;
-            if (gr < r1 && gr < n && gc < n) {
+            if (gr < r1 && gr < n && gc < n && (!sym || gc <= gr)) {
                 const double g = alpha[gr] * alpha[gc] - Kinv[gr * ldk + gc];
                 const double kf = gr == gc ? sf2 : sf2 * exp(fmin(w[r][c], 0.0));
-                v = g * kf;
+                v = g * kf * ((sym && gc < gr) ? 2.0 : 1.0);
                 if (gr == gc) acc_tr += g;
             }
             w[r][c] = v;
@@ -631,9 +637,9 @@ long gpk_grad_trace_work_elems(long n, int d, long r0, long r1) {
 }
 
 // out[0] = tr G over rows [r0,r1), out[1] = sum G*K_f, out[2+j] = sum G*K_f*(x~_aj - x~_bj)^2, j < d
-int gpk_mll_grad_reduce(const double* X, long ldx, long n, int d, const double* hyp, const double* Kinv, long ldk,
-                        const double* alpha, long r0, long r1, double* work, long work_elems, double* out,
-                        void* stream) {
+static int mll_grad_reduce(const double* X, long ldx, long n, int d, const double* hyp, const double* Kinv, long ldk,
+                           const double* alpha, long r0, long r1, double* work, long work_elems, double* out, int sym,
+                           void* stream) {
     GPK_ARG(X && hyp && Kinv && alpha && work && out, "null pointer");
     GPK_ARG(d >= 1 && d <= HYP_MAXD && n > 0, "n / d");
     GPK_ARG(0 <= r0 && r0 < r1 && r1 <= n, "row range");
@@ -641,7 +647,7 @@ int gpk_mll_grad_reduce(const double* X, long ldx, long n, int d, const double* 
     const int dp = pad_dim(d);
     dim3 grid((unsigned)((n + CK_T - 1) / CK_T), (unsigned)((r1 - r0 + CK_T - 1) / CK_T));
     cudaStream_t st = (cudaStream_t)stream;
-#define GT_CASE(DPV) case DPV: grad_trace_kernel<DPV><<<grid, 256, 0, st>>>(X, ldx, n, d, hyp, Kinv, ldk, alpha, r0, r1, work); break;
+#define GT_CASE(DPV) case DPV: grad_trace_kernel<DPV><<<grid, 256, 0, st>>>(X, ldx, n, d, hyp, Kinv, ldk, alpha, r0, r1, work, sym); break;
     switch (dp) {
         GT_CASE(1) GT_CASE(2) GT_CASE(3) GT_CASE(4) GT_CASE(8) GT_CASE(16) GT_CASE(32)
         default: return fail(-1, "grad_trace: unsupported padded dimension %d", dp);
@@ -651,6 +657,18 @@ int gpk_mll_grad_reduce(const double* X, long ldx, long n, int d, const double* 
     reduce_partials_kernel<<<dp + 2, 256, 0, st>>>(work, (long)grid.x * grid.y, dp + 2, out);
     GPK_LAUNCHED();
     return 0;
+}
+
+int gpk_mll_grad_reduce(const double* X, long ldx, long n, int d, const double* hyp, const double* Kinv, long ldk,
+                        const double* alpha, long r0, long r1, double* work, long work_elems, double* out,
+                        void* stream) {
+    return mll_grad_reduce(X, ldx, n, d, hyp, Kinv, ldk, alpha, r0, r1, work, work_elems, out, 0, stream);
+}
+
+int gpk_mll_grad_reduce_sym(const double* X, long ldx, long n, int d, const double* hyp, const double* Kinv, long ldk,
+                            const double* alpha, long r0, long r1, double* work, long work_elems, double* out,
+                            void* stream) {
+    return mll_grad_reduce(X, ldx, n, d, hyp, Kinv, ldk, alpha, r0, r1, work, work_elems, out, 1, stream);
 }
 
 }  // extern "C"

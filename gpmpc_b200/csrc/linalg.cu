@@ -672,13 +672,14 @@ int gpk_kinv(const double* U, long ldu, long npad, double* Kinv, long ldk, void*
     return 0;
 }
 
-// rows [r0, r1) of K^-1 = U U^T with ALL their columns (row-split MLL gradient: every rank holds U and forms only
-// the rows its share of the trace reads; no mirror step).  Row i only needs k >= i: upper-triangular A window.
-int gpk_kinv_rows(const double* U, long ldu, long npad, long r0, long r1, double* Kinv, long ldk, void* stream) {
+// rows [r0, r1) of K^-1 = U U^T, columns [0, ncols) (row-split MLL gradient: every rank holds U and forms only what its
+// share of the trace reads -- all columns, or with the symmetric trace only ncols = r1; no mirror step).  Row i only needs k >= i: upper-triangular A window.
+int gpk_kinv_rows(const double* U, long ldu, long npad, long r0, long r1, long ncols, double* Kinv, long ldk, void* stream) {
     GPK_ARG(npad > 0 && npad % TILE == 0, "npad must be a positive multiple of 128");
     GPK_ARG(r0 >= 0 && r1 > r0 && r1 <= npad && r0 % TILE == 0 && r1 % TILE == 0, "row range must be 128-aligned inside [0, npad]");
+    GPK_ARG(ncols > 0 && ncols <= npad && ncols % TILE == 0, "ncols must be a multiple of 128 in (0, npad]");
     GPK_ARG(U && Kinv && ldu >= npad && ldk >= npad, "null pointer / leading dimensions");
-    return launch_dgemm_nt(gemm_args(U + r0 * ldu + r0, ldu, U + r0, ldu, Kinv + r0 * ldk, ldk, r1 - r0, npad, npad - r0,
+    return launch_dgemm_nt(gemm_args(U + r0 * ldu + r0, ldu, U + r0, ldu, Kinv + r0 * ldk, ldk, r1 - r0, ncols, npad - r0,
                                      1.0, 0.0, 2, 0), 0, 1, (cudaStream_t)stream);
 }
 

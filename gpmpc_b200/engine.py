@@ -83,6 +83,7 @@ FIT_GEMM_MIN_NPAD = 2048
 # K^-1 = U U^T only feeds the MLL gradient (and gp.K_inv): one digit less there costs ~1e-9 on the gradient (nothing on
 # the MLL, alpha or the predictions) and removes 6 of its 21 digit products.  0 = same digits as the factorisation.
 FIT_GEMM_DIGITS_KINV = 5
+FIT_SYMMETRIC_TRACE = True  # gradient trace from the lower triangle of K^-1 only (gpk_mll_grad_reduce_sym)
 FIT_OVERLAP_INVERSE = True  # W = L^-1 on a side stream beside the Cholesky recursion (gpk_potrf_trtri)
 FIT_GEMM_MIN_WORK_G = 0     # tuning hook: smallest GEMM (1e9 multiply-adds) sent to the int8 path; 0 = library default
 
@@ -310,8 +311,9 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
         if isinstance(want_kinv, tuple):
             # row-split gradient: only the (128-aligned hull of the) rows this rank's share of the trace reads
             k0, k1 = kinv_row_hull(want_kinv[0], want_kinv[1], npad)
-            if k1 > k0:
-                call("gpk_kinv_rows", ptr(ws.U), npad, npad, k0, k1, ptr(ws.need_kinv()), npad, st)
+            if k1 > k0:   # the symmetric trace reads columns <= row only
+                call("gpk_kinv_rows", ptr(ws.U), npad, npad, k0, k1, k1 if FIT_SYMMETRIC_TRACE else npad,
+                     ptr(ws.need_kinv()), npad, st)
         elif want_kinv:
             call("gpk_kinv", ptr(ws.U), npad, npad, ptr(ws.need_kinv()), npad, st)
         if switch_digits:
@@ -335,13 +337,16 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
 @_on_arg_device
 def grad_partials(fit: GPFit, ws: FitScratch, r0: int = 0, r1: int | None = None) -> torch.Tensor:
     """(d+2) partial sums of the MLL gradient trace over rows [r0, r1) (device tensor, float64).
-    Needs ws.Kinv from factorize(want_kinv=True)."""
+    Needs ws.Kinv from factorize(want_kinv=True) (or the rows [r0, r1) of it from want_kinv=(r0, r1)).  With
+    FIT_SYMMETRIC_TRACE the partial of a row block counts its columns b < a twice and skips b > a: partials of a
+    partition of the rows still add up to the full sums, a single block's partial is not the full-row sum."""
     lib = _lib.load()
     r1 = fit.n if r1 is None else r1
     assert ws.Kinv is not None, "factorize(..., want_kinv=True) first"
     elems = lib.gpk_grad_trace_work_elems(fit.n, fit.d, r0, r1)
     work = get_work("grad", elems * 8, fit.device)
-    call("gpk_mll_grad_reduce", ptr(fit.X), fit.X.stride(0), fit.n, fit.d, ptr(fit.hyp), ptr(ws.Kinv), fit.npad,
+    call("gpk_mll_grad_reduce_sym" if FIT_SYMMETRIC_TRACE else "gpk_mll_grad_reduce", ptr(fit.X), fit.X.stride(0), fit.n,
+         fit.d, ptr(fit.hyp), ptr(ws.Kinv), fit.npad,
          ptr(fit.alpha), r0, r1, ptr(work), elems, ptr(ws.grad_out), _lib.stream_ptr(fit.device))
     return ws.grad_out[: lib.gpk_pad_dim(fit.d) + 2]
 

@@ -160,19 +160,47 @@ def allreduce_row_partials(partials_fn: Callable[[int, int], torch.Tensor], n_ro
     return part
 
 
-def balanced_row_bounds(n: int, world: int, rank: int, align: int = 128) -> tuple[int, int]:
+def balanced_row_bounds(n: int, world: int, rank: int, align: int = 128, lower_only: bool = True) -> tuple[int, int]:
     """Row block [r0, r1) of `rank` for the row-split K^-1 + gradient trace of one GP.  Row i of K^-1 = U U^T costs
-    (n - i) n multiply-adds (upper-triangular U), so equal work means equal integrals of (n - i):
-    r_g = n (1 - sqrt(1 - g / world)), rounded to `align` (the tile of gpk_kinv_rows); the last block ends at n."""
+    (n - i) multiply-adds per column (upper-triangular U).  With the symmetric trace (lower_only) a block only forms
+    columns [0, r1): work(r0, r1) = r1 * integral_{r0}^{r1} (n - i) di; with all columns: n * the same integral, i.e.
+    r_g = n (1 - sqrt(1 - g / world)).  Cuts are rounded to `align` (the tile of gpk_kinv_rows); the last block ends
+    at n."""
     assert world >= 1 and 0 <= rank < world and n >= 0
 
-    def cut(g: int) -> int:
-        if g >= world:
-            return n
-        r = n * (1.0 - (1.0 - g / world) ** 0.5)
+    def snap(r: float) -> int:
         return min(n, int(round(r / align)) * align)
 
-    return cut(rank), max(cut(rank), cut(rank + 1))
+    if not lower_only or world == 1 or n == 0:
+        cuts = [snap(n * (1.0 - (1.0 - g / world) ** 0.5)) for g in range(world)] + [n]
+    else:
+        def integral(a: float, b: float) -> float:      # of (n - i) over [a, b]
+            return (b - a) * (n - 0.5 * (a + b))
+
+        def cuts_for(w: float) -> list[float]:           # greedy cuts so that every block has work w (the last: the rest)
+            c = [0.0]
+            for _ in range(world - 1):
+                lo, hi = c[-1], float(n)
+                for _ in range(50):
+                    mid = 0.5 * (lo + hi)
+                    if mid * integral(c[-1], mid) < w:
+                        lo = mid
+                    else:
+                        hi = mid
+                c.append(0.5 * (lo + hi))
+            return c + [float(n)]
+
+        lo_w, hi_w = 0.0, float(n) * integral(0.0, float(n))
+        for _ in range(60):                               # the work per block for which the last block matches too
+            w = 0.5 * (lo_w + hi_w)
+            c = cuts_for(w)
+            if n * integral(c[-2], float(n)) > w:
+                lo_w = w
+            else:
+                hi_w = w
+        cuts = [snap(x) for x in cuts_for(0.5 * (lo_w + hi_w))[:-1]] + [n]
+    cuts = [max(cuts[i], max(cuts[:i], default=0)) for i in range(len(cuts))]      # monotone after rounding
+    return cuts[rank], cuts[rank + 1]
 
 
 class RowSplitGradReduce:
@@ -184,14 +212,16 @@ class RowSplitGradReduce:
         self.group = group
 
     def rows(self, n: int) -> tuple[int, int]:
+        from . import engine as E
+
         rank, world = world_info(self.group)
-        return balanced_row_bounds(n, world, rank)
+        return balanced_row_bounds(n, world, rank, lower_only=bool(E.FIT_SYMMETRIC_TRACE))
 
     def __call__(self, fit, ws):
         from . import engine as E
 
         rank, world = world_info(self.group)
-        r0, r1 = balanced_row_bounds(fit.n, world, rank)
+        r0, r1 = self.rows(fit.n)
         if r1 > r0:
             part = E.grad_partials(fit, ws, r0, r1).clone()
         else:   # empty block (small n): contributes zeros, and must not touch K^-1 rows it never formed

@@ -69,9 +69,11 @@ int gpk_trtri(const double* L, long ldl, long npad, const double* dinv, double* 
 int gpk_potrf_trtri(double* A, long lda, long npad, double* dinv, int* info_dev, double* W, long ldw,
                     double* U, long ldu, double* tmp, long tmp_elems, void* stream);
 int gpk_kinv(const double* U, long ldu, long npad, double* Kinv, long ldk, void* stream);
-/* Rows [r0, r1) (multiples of 128) of K^-1 with all their columns: what one rank of a row-split MLL gradient needs
- * (SURVEY.md 8e); the other rows of Kinv are not touched. */
-int gpk_kinv_rows(const double* U, long ldu, long npad, long r0, long r1, double* Kinv, long ldk, void* stream);
+/* Rows [r0, r1) and columns [0, ncols) (multiples of 128) of K^-1: what one rank of a row-split MLL gradient needs
+ *  -- ncols = npad for gpk_mll_grad_reduce, ncols = r1 for gpk_mll_grad_reduce_sym; the rest of Kinv is
+ * not touched. */
+int gpk_kinv_rows(const double* U, long ldu, long npad, long r0, long r1, long ncols, double* Kinv, long ldk,
+                  void* stream);
 
 /* ---- (3) alpha, y^T K^-1 y, log det K --------------------------------------------------------
  * alpha = K^-1 y = U (W y); scal[0] = y^T K^-1 y, scal[1] = log det K (from diag L).  Replaces the
@@ -88,6 +90,12 @@ int gpk_solve_alpha(const double* W, long ldw, const double* U, long ldu, const 
  * GP's trace be split over GPUs; the (d+2) partials are then all-reduced by the caller. */
 long gpk_grad_trace_work_elems(long n, int d, long r0, long r1);
 int gpk_mll_grad_reduce(const double* X, long ldx, long n, int d, const double* hyp,
+                        const double* Kinv, long ldk, const double* alpha, long r0, long r1,
+                        double* work, long work_elems, double* out, void* stream);
+/* The same sums from the lower triangle of K^-1 only (the summand is symmetric: columns b < a counted twice, b > a
+ * skipped): half the traffic and exponentials.  The partial of a row range differs from gpk_mll_grad_reduce's, the sum
+ * over a partition of the rows is the same. */
+int gpk_mll_grad_reduce_sym(const double* X, long ldx, long n, int d, const double* hyp,
                         const double* Kinv, long ldk, const double* alpha, long r0, long r1,
                         double* work, long work_elems, double* out, void* stream);
 

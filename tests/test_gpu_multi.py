@@ -53,8 +53,10 @@ def _worker(rank, world, port):
         rs = S.rowsplit_grad_reduce()
         rows = rs.rows(fit.n)
         fit2, ws2 = E.factorize(X, Y[:, 0], p["ell"], 1.0, 1e-2, want_kinv=rows)
-        ws2.Kinv[: rows[0]].fill_(float("nan"))            # rows of other ranks must never be read
-        ws2.Kinv[E.kinv_row_hull(rows[0], rows[1], fit2.npad)[1]:].fill_(float("nan"))
+        k0, k1 = E.kinv_row_hull(rows[0], rows[1], fit2.npad)
+        ws2.Kinv[:k0].fill_(float("nan"))                  # rows of other ranks must never be read
+        ws2.Kinv[k1:].fill_(float("nan"))
+        ws2.Kinv[k0:k1, k1:].fill_(float("nan"))           # nor the columns right of the block (symmetric trace)
         assert o.rel_err(rs(fit2, ws2).cpu(), ref.cpu()) < 1e-11
         # fit_gp with the row-split gradient follows the same trajectory as the oracle loop
         Xs, ys = p["X"][:45, :3].contiguous(), p["Y"][:45, 0].contiguous()

@@ -168,8 +168,10 @@ def test_kinv_rows_match_full_inverse(fit_gemm_settings, digits):
         ws.Kinv.fill_(float("nan"))
         fit2, ws2 = E.factorize(X, y, p["ell"], p["sf2"], p["noise"], want_kinv=(r0, r1), want_image=False)
         k0, k1 = E.kinv_row_hull(r0, r1, fit2.npad)
-        assert o.rel_err(ws2.Kinv[k0:k1].cpu(), full[k0:k1].cpu()) < (1e-12 if digits == 0 else 1e-8)
+        assert E.FIT_SYMMETRIC_TRACE            # default: only columns [0, k1) of the rows are formed and read
+        assert o.rel_err(ws2.Kinv[k0:k1, :k1].cpu(), full[k0:k1, :k1].cpu()) < (1e-12 if digits == 0 else 1e-8)
         assert bool(torch.isnan(ws2.Kinv[:k0]).all()) and bool(torch.isnan(ws2.Kinv[k1:]).all())
+        assert bool(torch.isnan(ws2.Kinv[k0:k1, k1:]).all())
         acc += E.grad_partials(fit2, ws2, r0, r1)
     assert o.rel_err(acc.cpu(), gfull.cpu()) < 1e-9
 
@@ -196,3 +198,27 @@ def test_overlapped_inverse_is_bit_identical(fit_gemm_settings, n):
             assert (fit1.quad, fit1.logdet) == (ref[5], ref[6])
     finally:
         E.FIT_OVERLAP_INVERSE = saved
+
+
+def test_symmetric_trace_equals_full_trace(fit_gemm_settings):
+    """gpk_mll_grad_reduce_sym (lower triangle of K^-1, off-diagonal entries counted twice) against gpk_mll_grad_reduce
+    (all entries): same d+2 sums, also when the rows are cut at unaligned places; the upper triangle is never read."""
+    E = fit_gemm_settings
+    n, d = 1000, 5
+    p = o.synthetic_problem(n, d, 1, seed=9)
+    ell = p["ell"] * torch.linspace(0.7, 1.4, d, dtype=torch.float64)
+    fit, ws = E.factorize(p["X"].to(_dev()), p["Y"][:, 0].to(_dev()), ell, 1.3, 0.02, want_kinv=True)
+    saved = E.FIT_SYMMETRIC_TRACE
+    try:
+        E.FIT_SYMMETRIC_TRACE = False
+        full = E.grad_partials(fit, ws).clone()
+        E.FIT_SYMMETRIC_TRACE = True
+        ws.Kinv.copy_(torch.tril(ws.Kinv) + torch.triu(torch.full_like(ws.Kinv, float("nan")), diagonal=1))
+        sym = E.grad_partials(fit, ws).clone()
+        assert o.rel_err(sym.cpu(), full.cpu()) < 1e-12
+        acc = torch.zeros_like(full)
+        for r0, r1 in ((0, 1), (1, 333), (333, 334), (334, 1000)):
+            acc += E.grad_partials(fit, ws, r0, r1)
+        assert o.rel_err(acc.cpu(), full.cpu()) < 1e-12
+    finally:
+        E.FIT_SYMMETRIC_TRACE = saved

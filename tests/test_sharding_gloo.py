@@ -156,19 +156,21 @@ def test_world_size_2_gloo(q_total):
 
 
 def test_balanced_row_bounds_partition():
-    """Row blocks of the row-split K^-1: disjoint, cover [0, n), 128-aligned inner cuts, later blocks longer (their
-    rows of the upper-triangular product are cheaper)."""
+    """Row blocks of the row-split K^-1: disjoint, cover [0, n), 128-aligned inner cuts, equal work under the cost
+    model of each mode (all columns: n * integral of (n - i); lower triangle only: r1 * that integral)."""
     from gpmpc_b200 import sharding as S
 
-    for n in (0, 45, 128, 500, 2048, 32768):
-        for world in (1, 2, 3, 8):
-            blocks = [S.balanced_row_bounds(n, world, r) for r in range(world)]
-            assert blocks[0][0] == 0 and blocks[-1][1] == n
-            for (a0, a1), (b0, b1) in zip(blocks, blocks[1:]):
-                assert a1 == b0 and a0 <= a1
-            assert all(lo % 128 == 0 for lo, _ in blocks)
-            if n >= 128 * 8 * world:
-                sizes = [hi - lo for lo, hi in blocks]
-                assert sizes == sorted(sizes)
-                work = [sum(n - i for i in range(lo, hi, 64)) for lo, hi in blocks]      # ~ integral of (n - i)
-                assert max(work) < 1.35 * (sum(work) / world)
+    for lower_only in (False, True):
+        for n in (0, 45, 128, 500, 2048, 32768):
+            for world in (1, 2, 3, 8):
+                blocks = [S.balanced_row_bounds(n, world, r, lower_only=lower_only) for r in range(world)]
+                assert blocks[0][0] == 0 and blocks[-1][1] == n
+                for (a0, a1), (b0, b1) in zip(blocks, blocks[1:]):
+                    assert a1 == b0 and a0 <= a1
+                assert all(lo % 128 == 0 for lo, _ in blocks)
+                if n >= 128 * 8 * world:
+                    work = [(hi if lower_only else n) * (hi - lo) * (n - 0.5 * (lo + hi)) for lo, hi in blocks]
+                    assert max(work) < 1.35 * (sum(work) / world)
+                    if not lower_only:          # later rows are cheaper: later blocks are longer
+                        sizes = [hi - lo for lo, hi in blocks]
+                        assert sizes == sorted(sizes)
