@@ -234,4 +234,32 @@ __device__ __forceinline__ double oz_recombine(const int32_t (&v)[S][W], int j) 
 }
 
 
+// Balanced base-256 digits of four values in (-1, 1) (S <= 6) without integer division or carries: ONE fused multiply-add
+// x * 2^(8S-2) + 1.5 * 2^52 leaves the rounded fixed-point integer in the mantissa; a bias of 128 per digit turns the
+// balanced digits into the plain BYTES of that integer (two's complement digit = byte ^ 0x80); byte permutes gather
+// digit s of the four values into one 32-bit word (most significant digit first).  Same digits as signed_digits(to_fixed(x)).
+template <int S>
+__device__ __forceinline__ void oz_pack_digits4(const double (&e)[4], uint32_t (&out)[S]) {
+    constexpr double SC = (double)(1ull << (6 + 8 * (S - 1)));
+    long long bias = 0;
+#pragma unroll
+    for (int i = 0; i < S; i++) bias += 128ll << (8 * i);
+    bias -= 0x4338000000000000LL;
+    uint32_t lo[4], hi[4];
+#pragma unroll
+    for (int v = 0; v < 4; v++) {
+        const long long b = __double_as_longlong(fma(e[v], SC, 6755399441055744.0)) + bias;   // sum_i (d_i + 128) 256^i
+        lo[v] = (uint32_t)b;
+        hi[v] = (uint32_t)(b >> 32);
+    }
+#pragma unroll
+    for (int i = 0; i < S; i++) {                       // i = 0: least significant digit = byte i of the integer
+        const uint32_t sel = (uint32_t)((i & 3) | (((i & 3) + 4) << 4));
+        const uint32_t p01 = __byte_perm(i < 4 ? lo[0] : hi[0], i < 4 ? lo[1] : hi[1], sel);
+        const uint32_t p23 = __byte_perm(i < 4 ? lo[2] : hi[2], i < 4 ? lo[3] : hi[3], sel);
+        out[S - 1 - i] = __byte_perm(p01, p23, 0x5410) ^ 0x80808080u;
+    }
+}
+
+
 }  // namespace gpk
