@@ -1,13 +1,26 @@
 """bench.py -- GP posterior predictions/s (mean + variance + Jacobian) of the gp-mpc GP hot path on B200.
 
-Workload (BASELINE.json configs[1], SURVEY.md 8d "config 2"): P=3 independent exact GPs sharing N=2048
-training points in d=16 (12 states + 4 inputs), Q=8192 horizon queries per step, float64 (the reference's
-arithmetic type: float64 data promotes gpytorch's kernel matrix).  One step = one pass of the hot path
-over one batch: mean, variance and d-vector Jacobian for Q queries of each of the P GPs = P*Q predictions.
-With --gpus N every rank holds the replicated fitted state and its own Q-query shard (weak scaling, no
-data-path collective); value = all ranks' predictions / max-over-ranks device time.
+Headline workload (BASELINE.json configs[2], SURVEY.md 8d "config 3"): P=3 independent exact GPs sharing N=16384
+training points in d=16 (12 states + 4 inputs), ONE fixed global batch of Q rollout queries per step, float64 (the
+reference's arithmetic type).  One step = mean, variance and d-vector Jacobian for all Q queries of each of the P
+GPs = P*Q predictions, issued through `gpmpc_b200.sharding.predict_sharded`: the global batch is cut into one
+contiguous block per rank (strong scaling), the fitted state is computed ONCE on rank 0 and replicated with
+`sharding.replicate_batch` (timed, `state_broadcast_s`), and there is no collective in the prediction itself.
+Before the timed region every rank checks that the sharded + gathered result equals its own unsharded prediction.
+Q defaults to 1,048,576 = a quarter of config 3's 4,194,304 queries (--queries to change): the full batch costs
+~20 s per step on one GPU, and the driver's 25 timed + warm-up steps plus the equally long end-to-end leg would not
+fit its per-N time budget; per-query cost does not depend on Q at this size (8192 query tiles per GP).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+Other configs in the same JSON line (`extras`), so that they land in the driver-run records:
+  config2   (N=1 only) BASELINE.json configs[1]: P=3, N=2048, Q=8192 -- round 1's headline, for comparability
+  config4a  P = world GPs of N=32768, one per rank: MLL + gradient iterations/s        (output-GP sharding)
+  config4b  one GP of N=32768, K^-1 rows + gradient trace split over the ranks, NCCL all-reduce timed  (N>1)
+  config5   65,536 rollouts x horizon 50 over the ranks: 50 sequential stage batches (stage dynamics feed the next
+            stage's GP queries) + chance-constraint tightening
+  config1   (N=1 only) the reference's own shapes: 3 GPs, N=45, Adam loop of fit_gp, beside the CPU oracle loop
+and a first-class `mll` block (MLL + gradient iterations/s, half of BASELINE.json's metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload config3|config2]
 
 Prints ONE JSON line (rank 0).  Synthetic data: seed 1337, X~U(-1,1), y=sin(Xw)+0.05eps, ell=0.5 sqrt(d),
 sf2=1, noise=1e-2, Z~U(-1.2,1.2).
@@ -17,6 +30,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import statistics
 import subprocess
@@ -30,22 +44,34 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-N_TRAIN, DIM, N_QUERY, N_GP = 2048, 16, 8192, 3
+DIM, N_GP = 16, 3
+WORKLOADS = {
+    # name: (N train, default global queries per step, what the name means)
+    "config3": (16384, 1 << 20, "BASELINE.json configs[2]"),
+    "config2": (2048, 8192, "BASELINE.json configs[1]"),
+}
 METRIC = "gp_posterior_preds_per_s"
 UNIT = "preds/s"
-WORKLOAD = f"config2: P={N_GP} GPs, N={N_TRAIN} train pts, d={DIM}, Q={N_QUERY} queries/step, mean+var+Jacobian"
-DMMA_PEAK_TFLOPS = 37.1   # measured on this pool's B200 by tools/peaks (profiles/peaks_micro_r01.json); nominal 40
+NOMINAL_INT8_TOPS = 4500.0   # B200 dense int8, NVIDIA's figure
+FALLBACK_BF16_TFLOPS = 1590.0
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
+    ap.add_argument("--queries", type=int, default=0, help="global queries per step (default: the workload's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-extras", action="store_true", help="skip the fp32 / MLL side measurements")
+    ap.add_argument("--no-extras", action="store_true", help="skip the other configs / side measurements")
     return ap.parse_args()
+
+
+def workload_string(name, n, q):
+    return (f"{name} ({WORKLOADS[name][2]}): P={N_GP} GPs, N={n} train pts, d={DIM}, Q={q} queries per step (global, "
+            f"split over the ranks), mean+var+Jacobian")
 
 
 # --------------------------------------------------------------------------------------------------
@@ -68,6 +94,7 @@ class ClockSampler:
             self.thread.start()
         except OSError:
             self.proc = None
+        return self
 
     def _read(self):
         for line in self.proc.stdout:
@@ -81,18 +108,19 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, smax, reasons = [], None, set()
+        sm, smax, power, reasons = [], None, [], set()
         for r in self.rows:
             try:
                 sm.append(float(r[0]))
                 smax = float(r[1])
+                power.append(float(r[2]))
             except (ValueError, IndexError):
                 continue
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
                 if v.lower().startswith("active"):
                     reasons.add(name)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "sm_mhz_min": min(sm) if sm else None, "power_w_max": max(power) if power else None}
 
 
 def l2_flusher(device):
@@ -104,74 +132,134 @@ def l2_flusher(device):
     return flush
 
 
-def make_problem(rank: int):
-    """Synthetic recipe of SURVEY.md 8d (same numbers as oracle.synthetic_problem, restated here so the
-    product arm does not import the oracle)."""
-    import math
-
+def make_problem(n_train: int, n_query: int):
+    """Synthetic recipe of SURVEY.md 8d (same numbers as oracle.synthetic_problem, restated here so the product arm
+    does not import the oracle).  Identical on every rank: Z is the GLOBAL query batch."""
     g = torch.Generator().manual_seed(1337)
-    X = torch.rand(N_TRAIN, DIM, generator=g, dtype=torch.float64) * 2.0 - 1.0
+    X = torch.rand(n_train, DIM, generator=g, dtype=torch.float64) * 2.0 - 1.0
     Wm = torch.randn(DIM, N_GP, generator=g, dtype=torch.float64)
-    eps = torch.randn(N_TRAIN, N_GP, generator=g, dtype=torch.float64)
+    eps = torch.randn(n_train, N_GP, generator=g, dtype=torch.float64)
     Y = torch.sin(X @ Wm) + 0.05 * eps
-    Z = (torch.rand(N_QUERY, DIM, generator=g, dtype=torch.float64) * 2.0 - 1.0) * 1.2
-    if rank > 0:   # every rank predicts its own shard of the global query batch
-        g2 = torch.Generator().manual_seed(1337 + rank)
-        Z = (torch.rand(N_QUERY, DIM, generator=g2, dtype=torch.float64) * 2.0 - 1.0) * 1.2
+    Z = (torch.rand(n_query, DIM, generator=g, dtype=torch.float64) * 2.0 - 1.0) * 1.2
     ell = torch.full((DIM,), 0.5 * math.sqrt(DIM), dtype=torch.float64)
     return {"X": X, "Y": Y, "Z": Z, "ell": ell, "sf2": 1.0, "noise": 1e-2}
 
 
+def load_peaks():
+    peaks = {}
+    for fn in ("MEASURED_PEAKS.json", os.path.join("profiles", "peaks_micro_r02.json")):
+        try:
+            with open(os.path.join(ROOT, fn)) as f:
+                peaks.update(json.load(f))
+        except (OSError, ValueError):
+            pass
+    return peaks
+
+
 # --------------------------------------------------------------------------------------------------
 # CPU arm: the oracle (torch float64 restatement of the gpytorch math) on the host cores.
-# gpytorch itself is not installable here (SURVEY.md section 0), so kind = "port".
 # --------------------------------------------------------------------------------------------------
-def cpu_predict_rate(problem, n_queries: int, steps: int = 1, warmup: int = 0):
-    """Times oracle.predict (mean + variance + Jacobian) for the P GPs on `n_queries` of the workload's
-    queries with all host threads.  Fit states (Cholesky, alpha) are prepared outside the timed region,
-    like the GPU arm's resident state.  Returns (preds/s, seconds per step)."""
-    from oracle import gp_oracle as o
+def try_gpytorch():
+    """the reference's own GP stack if the box has it (it does not in this image)."""
+    try:
+        import gpytorch  # noqa: F401
+        return "importable (version %s) but the reference arm still times the oracle port" % gpytorch.__version__
+    except Exception as e:  # noqa: BLE001
+        return f"not importable here ({type(e).__name__}): oracle port timed instead"
 
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    X, Y, Z = problem["X"], problem["Y"], problem["Z"][:n_queries]
-    states = [o.fit_state(X, Y[:, p], problem["ell"], problem["sf2"], problem["noise"]) for p in range(N_GP)]
 
-    def step():
-        for st in states:
-            o.predict(Z, X, problem["ell"], problem["sf2"], st["L"], st["alpha"])
+class CpuArm:
+    """oracle.predict (mean + variance + Jacobian) for the P GPs with all host threads; fit states (Cholesky, alpha)
+    are prepared outside the timed region like the GPU arm's resident state.  Two formulations of the kernel matrix
+    are timed -- the direct-difference loop the oracle is written in (gpmpc/gp.py:12-14) and the GEMM form gpytorch's
+    RBFKernel really uses (oracle.se_kernel_gpytorch) -- and the faster is reported."""
 
-    for _ in range(warmup):
-        step()
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        step()
-    dt = (time.perf_counter() - t0) / steps
-    return N_GP * n_queries / dt, dt, cores
+    def __init__(self, problem):
+        from oracle import gp_oracle as o
+
+        self.o, self.p = o, problem
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        # untimed preparation: at large N the kernel matrix is assembled in the GEMM form (16 passes over a 2 GB matrix
+        # otherwise), and only L and alpha are kept
+        saved = o.se_kernel
+        if problem["X"].shape[0] >= 8192:
+            o.se_kernel = o.se_kernel_gpytorch
+        try:
+            self.states = []
+            for k in range(N_GP):
+                st = o.fit_state(problem["X"], problem["Y"][:, k], problem["ell"], problem["sf2"], problem["noise"])
+                self.states.append({"L": st["L"], "alpha": st["alpha"]})
+                del st
+        finally:
+            o.se_kernel = saved
+        self.kernel = "direct"
+
+    def _step(self, Z, kernel):
+        o, p = self.o, self.p
+        saved = o.se_kernel
+        if kernel == "gemm":
+            o.se_kernel = o.se_kernel_gpytorch
+        try:
+            for st in self.states:
+                o.predict(Z, p["X"], p["ell"], p["sf2"], st["L"], st["alpha"])
+        finally:
+            o.se_kernel = saved
+
+    def calibrate(self, q=256):
+        """Pick the faster kernel formulation; returns preds/s of it on q queries."""
+        Z = self.p["Z"][:q]
+        rates = {}
+        for kern in ("direct", "gemm"):
+            self._step(Z[:32], kern)
+            t0 = time.perf_counter()
+            self._step(Z, kern)
+            rates[kern] = N_GP * q / (time.perf_counter() - t0)
+        self.kernel = max(rates, key=rates.get)
+        self.rates = rates
+        return rates[self.kernel]
+
+    def rate(self, n_queries, steps=1, warmup=0):
+        Z = self.p["Z"][:n_queries]
+        for _ in range(warmup):
+            self._step(Z, self.kernel)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            self._step(Z, self.kernel)
+        dt = (time.perf_counter() - t0) / steps
+        return N_GP * n_queries / dt, dt
+
+    def describe(self, sample, q_total):
+        return (f"{sample} of {q_total} queries x {N_GP} GPs per step, fit state prepared untimed; oracle/gp_oracle.py "
+                f"(torch float64, {self.cores} host threads), kernel matrix by {self.kernel} form "
+                f"(direct {self.rates['direct']:.0f} / gemm {self.rates['gemm']:.0f} preds/s in calibration); gpytorch "
+                f"1.12.0 {try_gpytorch()}")
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path.  gpytorch 1.12.0 cannot be installed
-    here (no wheel, no network), so this is the oracle port on all host cores; each step is a bounded sample
-    of the workload's queries sized so the whole run stays within a few minutes."""
+    """--impl reference: the reference's CPU implementation of the path.  gpytorch 1.12.0 cannot be installed here (no
+    wheel, no network), so this is the oracle port on all host cores; each step is a bounded sample of the workload's
+    queries sized so the whole run stays within a few minutes."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    problem = make_problem(0)
-    # calibrate on 512 queries, then size the per-step sample for ~2.5 s per step
-    rate0, _, cores = cpu_predict_rate(problem, 512, steps=1, warmup=1)
+    n_train, q_default, _ = WORKLOADS[args.workload]
+    q_total = args.queries or q_default
+    problem = make_problem(n_train, min(q_total, 16384))
+    arm = CpuArm(problem)
+    rate0 = arm.calibrate(min(256, problem["Z"].shape[0]))
     total_steps = max(1, args.steps + args.warmup)
     budget_s = min(2.5, 150.0 / total_steps)
-    sample = int(min(N_QUERY, max(256, rate0 * budget_s / N_GP)))
-    rate, dt, cores = cpu_predict_rate(problem, sample, steps=args.steps, warmup=args.warmup)
+    sample = int(min(problem["Z"].shape[0], max(64, rate0 * budget_s / N_GP)))
+    rate, dt = arm.rate(sample, steps=args.steps, warmup=args.warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": f"{sample} of {N_QUERY} queries per step x {N_GP} GPs"},
-        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{sample} of {N_QUERY} queries x {N_GP} GPs per step, fit state prepared untimed; "
-                                   "gpytorch 1.12.0 not installable, oracle/gp_oracle.py (torch float64) timed instead"},
+        "config": {"workload": workload_string(args.workload, n_train, q_total),
+                   "sample": f"{sample} of {q_total} queries per step x {N_GP} GPs"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": arm.cores, "kind": "port",
+                         "sample": arm.describe(sample, q_total)},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -181,6 +269,45 @@ def run_reference(args):
 # --------------------------------------------------------------------------------------------------
 # B200 arm
 # --------------------------------------------------------------------------------------------------
+class Ctx:
+    """Per-process distributed context."""
+
+    def __init__(self):
+        import torch.distributed as dist
+
+        from gpmpc_b200 import _lib
+
+        self.dist = dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dev = _lib.require_cuda(f"cuda:{self.local_rank}")
+        torch.cuda.set_device(self.dev)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=self.dev)
+        self.lib = _lib.load()
+        self.flush = l2_flusher(self.dev)
+
+    def barrier(self):
+        torch.cuda.synchronize(self.dev)
+        if self.world > 1:
+            self.dist.barrier()
+
+    def max_over_ranks(self, v: float) -> float:
+        if self.world == 1:
+            return float(v)
+        t = torch.tensor([v], dtype=torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def gather_objects(self, obj):
+        if self.world == 1:
+            return [obj]
+        out = [None] * self.world
+        self.dist.all_gather_object(out, obj)
+        return out
+
+
 def timed_steps(fn, steps, flush, device):
     """Sum of per-step CUDA-event durations (ms) on the current stream, L2 flushed before every step."""
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
@@ -193,125 +320,185 @@ def timed_steps(fn, steps, flush, device):
     return sum(e0.elapsed_time(e1) for e0, e1 in evs)
 
 
+def rel_dev(a, b):
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-300))
+
+
+def elementwise_var_err(v, v_ref, sf2):
+    """max |dv| / max(v_ref, 1e-3 sf2): element-wise relative error of the variance with a floor at 1e-3 of the prior
+    variance (the variance cancels near training data, so a normwise figure hides the small entries)."""
+    return float(((v - v_ref).abs() / v_ref.clamp_min(1e-3 * sf2)).max())
+
+
 def run_b200(args):
-    import torch.distributed as dist
-
-    from gpmpc_b200 import _lib, engine as E
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    dev = _lib.require_cuda(f"cuda:{local_rank}")
-    torch.cuda.set_device(dev)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    lib = _lib.load()
-
-    def barrier():
-        torch.cuda.synchronize(dev)
-        if world > 1:
-            dist.barrier()
-
-    problem = make_problem(rank)
-    X, Y, Z = problem["X"].to(dev), problem["Y"].to(dev), problem["Z"].to(dev)
-    t0 = time.perf_counter()
-    gb = E.fit_batch(X, Y, problem["ell"], problem["sf2"], problem["noise"])   # replicated fitted state
-    torch.cuda.synchronize(dev)
-    fit_first_s = time.perf_counter() - t0       # includes one-time module loading and scratch allocation
-    t0 = time.perf_counter()
-    gb = E.fit_batch(X, Y, problem["ell"], problem["sf2"], problem["noise"])
-    torch.cuda.synchronize(dev)
-    fit_s = time.perf_counter() - t0
-    flush = l2_flusher(dev)
-    preds_per_step = N_GP * N_QUERY
-
-    def step():
-        return E.predict(gb, Z)
-
-    # ---- value: inputs resident in HBM ----------------------------------------------------------
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier()
-    sampler = ClockSampler(dev.index)
-    sampler.start()
-    lib.gpk_reset_launch_count()
-    torch.cuda.profiler.start()          # ncu --profile-from-start off captures exactly the timed steps
-    total_ms = timed_steps(step, args.steps, flush, dev)
-    torch.cuda.profiler.stop()
-    launches = lib.gpk_launch_count()
-    barrier()
-    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
-    value = world * preds_per_step * args.steps / (total_ms * 1e-3)
-
-    # ---- e2e: host buffers through the public API, H2D + D2H inside the timed region ------------------
+    from gpmpc_b200 import engine as E, sharding as S
     from gpmpc_b200.gp import predict_host
 
+    ctx = Ctx()
+    dev, world, rank, dist = ctx.dev, ctx.world, ctx.rank, ctx.dist
+    n_train, q_default, _ = WORKLOADS[args.workload]
+    q_total = args.queries or q_default
+    problem = make_problem(n_train, q_total)
+    warmup = max(args.warmup, 3)
+
+    # ---- fitted state: once on rank 0, replicated to every rank ------------------------------------
+    fit_first_s = fit_s = None
+    gb = None
+    if rank == 0:
+        X, Y = problem["X"].to(dev), problem["Y"].to(dev)
+        t0 = time.perf_counter()
+        gb = E.fit_batch(X, Y, problem["ell"], problem["sf2"], problem["noise"])
+        torch.cuda.synchronize(dev)
+        fit_first_s = time.perf_counter() - t0       # includes one-time module loading and scratch allocation
+        del gb
+        t0 = time.perf_counter()
+        gb = E.fit_batch(X, Y, problem["ell"], problem["sf2"], problem["noise"])
+        torch.cuda.synchronize(dev)
+        fit_s = time.perf_counter() - t0
+        E.release_scratch()                           # the fit scratch (L, U, GEMM images) is not prediction state
+    ctx.barrier()
+    t0 = time.perf_counter()
+    gb, bcast_bytes = S.replicate_batch(gb, src=0, device=dev)
+    ctx.barrier()
+    bcast_s = time.perf_counter() - t0
+
+    Zd = problem["Z"].to(dev)                         # the global batch, resident in HBM on every rank
+    lo, hi = S.shard_bounds(q_total, world, rank)
+    preds_per_step = N_GP * q_total
+
+    # ---- self-check: sharded (+ gathered) == unsharded, on every rank ---------------------------------------
+    qc = min(q_total, 8192)
+    full = E.predict(gb, Zd[:qc])
+    _, _, gathered = S.predict_sharded(lambda z: E.predict(gb, z), Zd[:qc], gather=True)
+    check = max(rel_dev(a, b) for a, b in zip(gathered, full))
+    check = ctx.max_over_ranks(check)
+    assert check < 1e-11, f"sharded prediction deviates from the unsharded one: {check:.3e}"
+    del full, gathered
+
+    def step():
+        return S.predict_sharded(lambda z: E.predict(gb, z), Zd)
+
+    # ---- value: inputs resident in HBM ----------------------------------------------------------
+    for _ in range(warmup):
+        step()
+    ctx.barrier()
+    sampler = ClockSampler(dev.index).start()
+    ctx.lib.gpk_reset_launch_count()
+    torch.cuda.profiler.start()          # ncu --profile-from-start off captures exactly the timed steps
+    total_ms = timed_steps(step, args.steps, ctx.flush, dev)
+    torch.cuda.profiler.stop()
+    launches = ctx.lib.gpk_launch_count()
+    clocks = sampler.stop()
+    ctx.barrier()
+    total_ms = ctx.max_over_ranks(total_ms)
+    value = preds_per_step * args.steps / (total_ms * 1e-3)
+
+    # ---- e2e: host buffers through the public API, H2D + D2H inside the timed region ------------------
     Zh = problem["Z"].pin_memory()
-    out_h = None
-    for _ in range(3):
-        out_h = predict_host(gb, Zh, out_h)
-    barrier()
+    out_h = [None]
+
+    def e2e_step():
+        def fn(z_host):
+            out_h[0] = predict_host(gb, z_host, out_h[0])      # returns after the results are on the host
+            return out_h[0]
+        return S.predict_sharded(fn, Zh)
+
+    for _ in range(2):
+        e2e_step()
+    ctx.barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        out_h = predict_host(gb, Zh, out_h)      # returns after the results are on the host
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * preds_per_step * args.steps / float(t.item())
-    clocks = sampler.stop()
-    h2d = Zh.numel() * 8
-    d2h = sum(o_.numel() * o_.element_size() for o_ in out_h)
+        e2e_step()
+    e2e_s = ctx.max_over_ranks(time.perf_counter() - t0)
+    e2e_value = preds_per_step * args.steps / e2e_s
+    h2d = (hi - lo) * DIM * 8
+    d2h = sum(o_.numel() * o_.element_size() for o_ in out_h[0])
+    h2d_all = sum(ctx.gather_objects(h2d))
+    d2h_all = sum(ctx.gather_objects(d2h))
+    out_h[0] = None
+    del Zh
 
+    all_clocks = ctx.gather_objects(clocks)
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "per_gpu_queries": N_QUERY, "parallelism": f"query-sharded x{world}, state replicated",
-                   "l2": "flushed (256 MB write) before every timed step"},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": launches, "clocks": clocks, "fit_state_s": fit_s, "fit_state_first_call_s": fit_first_s,
+        "config": {"workload": workload_string(args.workload, n_train, q_total), "global_queries": q_total,
+                   "queries_per_rank": hi - lo,
+                   "parallelism": f"sharding.predict_sharded: contiguous query blocks over {world} rank(s), fitted state "
+                                  "fitted on rank 0 and replicated (sharding.replicate_batch), no collective in the step",
+                   "l2": "flushed (256 MB write) before every timed step; the step's operands (W image "
+                         f"{gb.wimg.numel() / 1e9:.2f} GB + E image chunks) exceed the 126 MB L2 anyway"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all},
+        "gpu_launches": launches, "clocks": clocks,
+        "clocks_all_ranks": {"sm_mhz": [c.get("sm_mhz") for c in all_clocks], "sm_mhz_min": [c.get("sm_mhz_min") for c in all_clocks],
+                             "reasons": sorted({r for c in all_clocks for r in c.get("reasons", [])})},
+        "fit_state_s": fit_s, "fit_state_first_call_s": fit_first_s,
+        "state_broadcast_s": bcast_s if world > 1 else 0.0, "state_broadcast_bytes": bcast_bytes,
+        "sharded_vs_unsharded_max_rel_dev": check,
+        "comm_nranks_seen": dist.get_world_size() if world > 1 else 1,
     }
+    roof = measure_roofline(gb, Zd[lo:hi], ctx, max(3, min(args.steps, 10)))
+    # step-level fraction: the whole step's algorithmic int8 operations against the same peak
+    S_ = gb.digits
+    step_ops = float(gb.n) ** 2 * S_ * (S_ + 1) / 2 * preds_per_step / world       # per GPU
+    roof["step_frac"] = step_ops / (total_ms / args.steps * 1e-3) / 1e12 / roof["peak"]
+    roof["step_frac_note"] = ("whole prediction step (front end + variance contraction + finalize), algorithmic int8 "
+                              "operations of the step / ms_per_step / peak, per GPU")
+    line["roofline"] = roof
+
+    extras = {}
+    if not args.no_extras:
+        del Zd
+        gb_keep = gb if args.workload == "config2" else None
+        del gb
+        E.release_scratch()
+        torch.cuda.empty_cache()
+        extras.update(measure_fit_configs(ctx))
+        extras.update(measure_config5(ctx))
+        if world == 1:
+            extras.update(measure_single_gpu_extras(ctx, gb_keep, args.workload))
     if rank == 0:
-        line["roofline"] = measure_roofline(gb, Z, flush, dev, args.steps)
-        if not args.no_extras:
-            line["extras"] = measure_extras(gb, problem, Z, flush, dev)
+        if extras:
+            line["mll"] = extras.pop("mll", None)
+            line["extras"] = extras
         if world == 1 and not args.no_cpu_baseline:
-            rate0, _, cores = cpu_predict_rate(problem, 512, steps=1, warmup=1)
-            sample = int(min(N_QUERY, max(512, rate0 * 12.0 / N_GP)))   # ~12 s of CPU work
-            rate, dt, cores = cpu_predict_rate(problem, sample, steps=1, warmup=0)
-            line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                                    "sample": f"{sample} of {N_QUERY} queries x {N_GP} GPs, one pass, fit state prepared "
-                                              "untimed; oracle/gp_oracle.py (torch float64, all host threads)"}
+            arm = CpuArm(make_problem(n_train, min(q_total, 16384)))
+            rate0 = arm.calibrate(256)
+            sample = int(min(arm.p["Z"].shape[0], max(256, rate0 * 12.0 / N_GP)))   # ~12 s of CPU work
+            rate, dt = arm.rate(sample, steps=1, warmup=0)
+            line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": arm.cores, "kind": "port",
+                                    "sample": arm.describe(sample, q_total)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
-def measure_roofline(gb, Z, flush, dev, steps):
-    """Dominant kernel = oz_var_kernel: the variance contraction V = W K_ZX^T on the tcgen05 int8 pipe (exact
-    digit products in TMEM, fp64 recombination).  Timed alone with CUDA events on its launch stream, digit
-    image of E prepared beforehand, L2 flushed before every launch.
+def measure_roofline(gb, Z, ctx, steps):
+    """Dominant kernel = oz_var_kernel: the variance contraction V = W K_ZX^T on the tcgen05 int8 pipe (exact digit
+    products in TMEM, fp64 recombination).  Timed alone with CUDA events on its launch stream, digit image of E
+    prepared beforehand, L2 flushed before every launch, on (a chunk of) this rank's query block.
 
-    achieved = int8 tensor-pipe operations the algorithm needs per launch / launch time, where the algorithmic
-    count is SURVEY.md 8d's N^2 flops per prediction (triangular contraction) x the S(S+1)/2 digit products an
-    S-digit error-free fp64 product consists of x P*Q predictions.  peak = 2 x the measured dense bf16 burst of
-    MEASURED_PEAKS.json (the int8 tcgen05 rate is exactly twice the bf16 rate: 8192 vs 4096 MAC/clk/SM,
-    tools/peaks/umma_bench); the file holds no int8 figure of its own."""
+    achieved = int8 tensor-pipe operations the algorithm needs per launch / launch time: SURVEY.md 8d's N^2 flops per
+    prediction (triangular contraction) x the S(S+1)/2 digit products of an S-digit error-free fp64 product x the
+    predictions of the launch.  peak = 2 x the measured dense bf16 burst of MEASURED_PEAKS.json (tcgen05 int8 issues at
+    twice the bf16 rate: 8192 vs 4096 MAC/clk/SM); the int8 rate measured directly by tools/peaks/umma_bench and the
+    nominal 4500 TOP/s are reported beside it."""
     from gpmpc_b200 import _lib, engine as E
     from gpmpc_b200._lib import call, ptr
 
-    lib = _lib.load()
+    lib, dev = ctx.lib, ctx.dev
     B, n, d, npad, S = len(gb.fits), gb.n, gb.d, gb.npad, gb.digits
-    q = Z.shape[0]
-    qp = E.round_up(q, lib.gpk_oz_query_tile())
+    qt = lib.gpk_oz_query_tile()
+    # one work chunk of the prediction step (the step walks the query block in chunks that fit its scratch)
+    per_q = S * npad * B
+    q = int(min(Z.shape[0], max(qt, (E.VAR_WORK_BYTES // per_q) // qt * qt)))
+    Z = Z[:q].contiguous()
+    qp = E.round_up(q, qt)
     st = _lib.stream_ptr(dev)
     eimg = torch.empty(B, S * qp * npad, dtype=torch.int8, device=dev)
-    pieces = lib.gpk_oz_pieces(qp // lib.gpk_oz_query_tile() * B, npad)
+    pieces = lib.gpk_oz_pieces(qp // qt * B, npad)
     part = torch.empty(B, 16, qp, dtype=torch.float64, device=dev)
     call("gpk_oz_cross", 1, ptr(Z), Z.stride(0), q, 0, ptr(gb.X), gb.X.stride(1), n, gb.X.stride(0), d, ptr(gb.hyp),
          ptr(eimg), eimg.stride(0), npad, qp, S, B, st)
@@ -320,31 +507,34 @@ def measure_roofline(gb, Z, flush, dev, steps):
         call("gpk_oz_var_partials", ptr(eimg), eimg.stride(0), ptr(gb.wimg), gb.wimg.stride(0), ptr(gb.wscale),
              gb.wscale.stride(0), ptr(gb.hyp), npad, qp, S, ptr(part), qp, 16 * qp, pieces, B, None, st)
 
-    for _ in range(3):
+    for _ in range(2):
         gemm()
-    ms = timed_steps(gemm, steps, flush, dev) / steps
+    ms = timed_steps(gemm, steps, ctx.flush, dev) / steps
     fp64_flops = float(n) * n * B * q                       # N^2 flops per prediction
     int8_ops = fp64_flops * S * (S + 1) / 2
     achieved = int8_ops / (ms * 1e-3) / 1e12
-    peaks = {}
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks = json.load(f)
-    except OSError:
-        pass
+    peaks = load_peaks()
     bf16 = peaks.get("bf16_tflops")
-    peak = 2.0 * bf16 if bf16 else 2.0 * 1590.0
-    return {"kernel": f"oz_var_kernel<{S}> (variance contraction W K_ZX^T, {S}-digit int8 slices on tcgen05, int32 TMEM "
-                      "accumulators, fp64 recombination)",
-            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-            "unit_note": "int8 tensor operations (multiply + add = 2 ops), i.e. TOP/s on the scale of the bf16 TFLOP/s peak x 2",
-            "traffic": ncu_dram_bytes("ncu_oz_var_kernel_S5_r01_v6.csv") if S == 5 else None,
-            "traffic_unit": "bytes per launch (dram read + write, ncu --set full, profiles/ncu_oz_var_kernel_S5_r01_v6.csv)",
-            "algorithmic_bytes_per_launch": float(B) * S * npad * (qp + npad),
-            "ms_per_launch": ms, "algorithmic_int8_ops_per_launch": int8_ops,
-            "fp64_equivalent_tflops": fp64_flops / (ms * 1e-3) / 1e12, "fp64_dmma_peak_tflops": DMMA_PEAK_TFLOPS,
-            "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops (burst, of measured)" if bf16 else
-                            "2 x 1590 TFLOP/s bf16 (of fallback)") + "; nominal int8 dense 4500 TOP/s"}
+    peak = 2.0 * (bf16 or FALLBACK_BF16_TFLOPS)
+    dmma_peak = peaks.get("dmma_tflops_bps8", 37.1)
+    prof = f"ncu_oz_var_kernel_S{S}_r02_n{n}.csv"
+    out = {"kernel": f"oz_var_kernel<{S}> (variance contraction W K_ZX^T, {S}-digit int8 slices on tcgen05, int32 TMEM "
+                     "accumulators, fp64 recombination)",
+           "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+           "unit_note": "int8 tensor operations (multiply + add = 2 ops), i.e. TOP/s on the scale of the bf16 TFLOP/s peak x 2",
+           "frac_of_nominal": achieved / NOMINAL_INT8_TOPS, "nominal_peak": NOMINAL_INT8_TOPS,
+           "traffic": ncu_dram_bytes(prof),
+           "traffic_unit": f"bytes per launch (dram read + write, ncu --set full, profiles/{prof})",
+           "algorithmic_bytes_per_launch": float(B) * S * npad * (qp + npad / 2),
+           "queries_per_launch": q, "ms_per_launch": ms, "algorithmic_int8_ops_per_launch": int8_ops,
+           "fp64_equivalent_tflops": fp64_flops / (ms * 1e-3) / 1e12, "fp64_dmma_peak_tflops": dmma_peak,
+           "peak_source": ("2 x MEASURED_PEAKS.json bf16_tflops (burst, of measured)" if bf16 else
+                           f"2 x {FALLBACK_BF16_TFLOPS} TFLOP/s bf16 (of fallback)")}
+    if peaks.get("int8_tops_burst"):
+        out["frac_of_measured_int8"] = achieved / peaks["int8_tops_burst"]
+        out["measured_int8_tops"] = {"burst": peaks["int8_tops_burst"], "sustained": peaks.get("int8_tops_sustained"),
+                                     "source": "profiles/peaks_micro_r02.json (tools/peaks/umma_bench --json)"}
+    return out
 
 
 def ncu_dram_bytes(name):
@@ -361,88 +551,339 @@ def ncu_dram_bytes(name):
         return None
 
 
-def measure_extras(gb, problem, Z, flush, dev):
-    """Side measurements (not the headline): float32 prediction path, mean+Jacobian kernel alone, MLL+grad."""
-    from gpmpc_b200 import engine as E
+# --------------------------------------------------------------------------------------------------
+# config 4 (hyper-parameter fit at N = 32768) and the MLL block -- every rank participates
+# --------------------------------------------------------------------------------------------------
+def fit_data(n, seed, dev):
+    g = torch.Generator().manual_seed(seed)
+    X = (torch.rand(n, DIM, generator=g, dtype=torch.float64) * 2.0 - 1.0).to(dev)
+    y = (torch.sin(X @ torch.randn(DIM, generator=g, dtype=torch.float64).to(dev))
+         + 0.05 * torch.randn(n, generator=g, dtype=torch.float64).to(dev))
+    return X, y
 
+
+def timed_iters(fn, iters, ctx):
+    """ms per call of fn (one warm-up, then `iters` calls between two CUDA events), max over ranks."""
+    fn()
+    ctx.barrier()
+    sampler = ClockSampler(ctx.dev.index).start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    out = None
+    for _ in range(iters):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize(ctx.dev)
+    clocks = sampler.stop()
+    ms = ctx.max_over_ranks(e0.elapsed_time(e1) / iters)
+    return ms, out, clocks
+
+
+def measure_fit_configs(ctx, n_big: int = 32768):
+    from gpmpc_b200 import engine as E, sharding as S
+
+    dev, world, rank = ctx.dev, ctx.world, ctx.rank
+    ell = torch.full((DIM,), 0.5 * math.sqrt(DIM), dtype=torch.float64)
+    peaks = load_peaks()
+    dmma_peak = peaks.get("dmma_tflops_bps8", 37.1)
     out = {}
+
+    # (a) one GP per rank (different targets per rank): no collective
+    X, y = fit_data(n_big, 1337 + rank, dev)
+
+    def own_iter():
+        fit, ws = E.factorize(X, y, ell, 1.0, 1e-2, want_kinv=True, want_image=False)
+        return E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
+
+    ms_a, res_a, clk_a = timed_iters(own_iter, 2, ctx)
+    clk_all = ctx.gather_objects({"sm_mhz": clk_a.get("sm_mhz"), "reasons": clk_a.get("reasons")})
+    out["config4a"] = {"what": f"MLL + gradient iteration, N={n_big}, d={DIM}, one GP per rank x {world} rank(s), no collective",
+                       "ms_per_iter_max_over_ranks": ms_a, "iters_per_s_aggregate": world / ms_a * 1e3,
+                       "tflops_of_n3_per_gpu": float(n_big) ** 3 / ms_a * 1e-9, "fit_gemm_digits": int(E.FIT_GEMM_DIGITS),
+                       "kinv_digits": int(E.FIT_GEMM_DIGITS_KINV), "loss_rank0": res_a[0], "clocks_per_rank": clk_all}
+
+    # (b) one GP (rank 0's data everywhere), K^-1 rows + trace split over the ranks, all-reduce of d+2 doubles
+    if world > 1:
+        X0, y0 = fit_data(n_big, 1337, dev)
+        rs = S.rowsplit_grad_reduce(time_allreduce=True)
+
+        def split_iter():
+            fit, ws = E.factorize(X0, y0, ell, 1.0, 1e-2, want_kinv=rs.rows(n_big), want_image=False)
+            return E.loss_and_grad_from_partials(fit, rs(fit, ws))
+
+        ms_b, res_b, clk_b = timed_iters(split_iter, 2, ctx)
+        ar = rs.allreduce_ms()[1:]                                 # drop the warm-up call
+        ar_ms = ctx.max_over_ranks(sum(ar) / max(1, len(ar)))
+        # the collective alone, ranks aligned by a barrier: latency of an all_reduce of d+2 doubles
+        buf = torch.zeros(DIM + 2, dtype=torch.float64, device=dev)
+        for _ in range(5):
+            ctx.dist.all_reduce(buf)
+        ctx.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(50):
+            ctx.dist.all_reduce(buf)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ar_us = ctx.max_over_ranks(e0.elapsed_time(e1) / 50 * 1e3)
+        # unsplit gradient of the same GP on this rank, for the parity figure
+        X, y = X0, y0
+        ref = own_iter()
+        gs = torch.tensor([res_b[1], res_b[2]] + list(res_b[3]))
+        gr = torch.tensor([ref[1], ref[2]] + list(ref[3]))
+        dev_grad = ctx.max_over_ranks(float((gs - gr).abs().max() / gr.abs().max()))
+        out["config4b"] = {"what": f"one GP, N={n_big}: every rank factorises (replicated), K^-1 rows + gradient trace split over "
+                                   f"{world} ranks (sharding.RowSplitGradReduce), NCCL all_reduce of {DIM + 2} doubles",
+                           "ms_per_iter_max_over_ranks": ms_b, "iters_per_s": 1e3 / ms_b,
+                           "speedup_vs_unsplit": ms_a / ms_b,
+                           "ceiling_note": "potrf + trtri (2/3 of the N^3 work) are replicated on every rank: <= 1.5x at any rank count",
+                           "allreduce_ms_in_iter_max_over_ranks": ar_ms,
+                           "allreduce_ms_note": "CUDA events around dist.all_reduce on the compute stream: wait for the slowest rank's "
+                                                "trace + the collective",
+                           "allreduce_us_isolated": ar_us, "rows_rank0": list(rs.rows(n_big)),
+                           "grad_rel_dev_vs_unsplit": dev_grad, "clocks_rank0": {"sm_mhz": clk_b.get("sm_mhz"), "reasons": clk_b.get("reasons")}}
+        del X0, y0
+    del X, y
+    E.release_scratch()
+    torch.cuda.empty_cache()
+
+    # MLL block: iterations/s at the reference-reachable size, at half of config 4 and at config 4 (from (a))
+    mll = {"unit": "MLL+gradient iterations/s (one GP, one GPU)", "points": []}
+    for n in (2048, 16384):
+        Xn, yn = fit_data(n, 1337, dev)
+
+        def it():
+            fit, ws = E.factorize(Xn, yn, ell, 1.0, 1e-2, want_kinv=True, want_image=False)
+            return E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
+
+        ms, res, clk = timed_iters(it, 10 if n <= 4096 else 3, ctx)
+        mll["points"].append({"n": n, "value": 1e3 / ms, "ms_per_iter": ms, "tflops_of_n3": float(n) ** 3 / ms * 1e-9,
+                              "frac_of_fp64_dmma_peak": float(n) ** 3 / ms * 1e-9 / dmma_peak, "loss": res[0],
+                              "sm_mhz": clk.get("sm_mhz")})
+        del Xn, yn
+        E.release_scratch()
+    mll["points"].append({"n": n_big, "value": 1e3 / ms_a, "ms_per_iter": ms_a, "tflops_of_n3": float(n_big) ** 3 / ms_a * 1e-9,
+                          "frac_of_fp64_dmma_peak": float(n_big) ** 3 / ms_a * 1e-9 / dmma_peak, "loss": res_a[0]})
+    mll["value"] = mll["points"][-1]["value"]
+    mll["n"] = n_big
+    mll["roofline"] = {"bound": "tensor", "unit": "TFLOP/s", "peak": dmma_peak, "achieved": mll["points"][-1]["tflops_of_n3"],
+                       "frac": mll["points"][-1]["frac_of_fp64_dmma_peak"],
+                       "note": "N^3 flops per iteration (SURVEY.md 8d) against the FP64 DMMA pipe the iteration was specified on; "
+                               "above 1 because the large GEMMs run as exact int8 digit products on tcgen05 "
+                               f"({int(E.FIT_GEMM_DIGITS)} digits, K^-1 {int(E.FIT_GEMM_DIGITS_KINV)})",
+                       "peak_source": "profiles/peaks_micro_r02.json dmma_tflops_bps8" if "dmma_tflops_bps8" in peaks
+                                      else "37.1 TFLOP/s (round-1 measurement, profiles/peaks_micro_r01.json)"}
+    if rank == 0 and world == 1:
+        # CPU oracle beside it (closed-form loss + gradient, all host threads) at the size the reference can reach
+        from oracle import gp_oracle as o
+
+        torch.set_num_threads(os.cpu_count() or 1)
+        g = torch.Generator().manual_seed(1337)
+        Xc = torch.rand(2048, DIM, generator=g, dtype=torch.float64) * 2.0 - 1.0
+        yc = torch.sin(Xc @ torch.randn(DIM, generator=g, dtype=torch.float64)) + 0.05 * torch.randn(2048, generator=g, dtype=torch.float64)
+        rn, rs_, rl = o.inv_softplus(torch.tensor([1e-2 - 1e-6])), o.inv_softplus(torch.tensor(1.0)), o.inv_softplus(ell.reshape(1, -1))
+        o.loss_and_grad(Xc[:256], yc[:256], rn, rs_, rl)
+        t0 = time.perf_counter()
+        o.loss_and_grad(Xc, yc, rn, rs_, rl)
+        mll["cpu_oracle"] = {"n": 2048, "value": 1.0 / (time.perf_counter() - t0), "cores": os.cpu_count(), "kind": "port",
+                             "what": "oracle.loss_and_grad (torch float64: Cholesky, cholesky_inverse, d trace passes), one call"}
+    out["mll"] = mll
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# config 5: 65,536 rollouts x horizon 50 over the ranks
+# --------------------------------------------------------------------------------------------------
+def measure_config5(ctx, rollouts: int = 65536, horizon: int = 50, n_train: int = 2048):
+    """Large-batch linearised-MPC sweep (BASELINE.json configs[4]).  Every rank owns rollouts/world initial states
+    (sharding.rollouts_sharded) and walks the horizon: per stage t the three d=16 GPs are evaluated at z_t = (x_t, u_t)
+    (mean, variance, Jacobian: what the linearisation and the tightening consume), and the RK4 stage dynamics with
+    sensitivities on the reference's 12-state model (GPs with d = 1, 3, 3) produce x_{t+1}: stage t+1 depends on
+    stage t, so the sweep is 50 sequential batches of rollouts/world queries.  The chance-constraint tightening
+    recursion over the visited states closes the sweep."""
+    from gpmpc_b200 import engine as E, sharding as S
+    from gpmpc_b200.mpc import ConstraintTightening, StageDynamics
+
+    dev, world = ctx.dev, ctx.world
+    p = make_problem(n_train, 8)
+    gb = E.fit_batch(p["X"].to(dev), p["Y"].to(dev), p["ell"], p["sf2"], p["noise"])
+    g = torch.Generator().manual_seed(5)
+    gps = []
+    for k, d in enumerate((1, 3, 3)):
+        Xk = torch.rand(n_train, d, generator=g, dtype=torch.float64) - 0.5
+        yk = 0.3 * torch.sin(4.0 * Xk.sum(dim=1)) + 0.01 * torch.randn(n_train, generator=g, dtype=torch.float64)
+        gps.append((Xk, yk, torch.full((d,), 0.3 + 0.1 * k, dtype=torch.float64), 0.5, 1e-2))
+    sd = StageDynamics(gps, [12.1432, 1.8118, -72.08, -7.5755, 39.8653, -72.08, -7.5755, 39.8653], 0.02)
+    A = torch.eye(12, dtype=torch.float64) + 0.02 * torch.randn(12, 12, generator=g, dtype=torch.float64)
+    B = 0.1 * torch.randn(12, 4, generator=g, dtype=torch.float64)
+    K = -0.3 * torch.randn(4, 12, generator=g, dtype=torch.float64)
+    Bd = torch.eye(12, dtype=torch.float64)[:, [1, 3, 5, 9, 10]]
+    ct = ConstraintTightening(gps, [[0], [1, 2, 3], [4, 5, 6]], A, B, K, Bd, 0.02, 2.0)
+    x0_all = ((torch.rand(rollouts, 12, generator=g, dtype=torch.float64) - 0.5) * 0.8).to(dev)
+    u_all = ((torch.rand(rollouts, 4, horizon, generator=g, dtype=torch.float64) - 0.3) * 0.6).to(dev)
+    ev = {k: [] for k in ("gp", "dyn", "tighten")}
+
+    def sweep_local(x0, u):
+        """x0 (R,12), u (R,4,T) -> per-rollout summaries (R, 2): trace of the final A and the last stage's GP-0 variance."""
+        R = x0.shape[0]
+        xs = torch.empty(R, 12, horizon + 1, dtype=torch.float64, device=dev)
+        xs[:, :, 0] = x0
+        x = x0
+        last_var = None
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(2 * horizon + 2)]
+        for t in range(horizon):
+            ut = u[:, :, t].contiguous()
+            marks[2 * t].record()
+            z = torch.cat([x, ut], dim=1)
+            mean, var, jac = E.predict(gb, z)                      # 3 GPs x R queries: mean, variance, Jacobian
+            marks[2 * t + 1].record()
+            x, Ax, Bu = sd.disc_dyn(x, ut, work_bytes=2 << 30)     # RK4 + sensitivities (4 x 3-GP mean+Jacobian inside)
+            xs[:, :, t + 1] = x
+            last_var = var[0]
+        marks[2 * horizon].record()
+        sc, ic = ct.propagate_constraint_limits(xs, u)
+        marks[2 * horizon + 1].record()
+        ev["marks"] = marks
+        return (torch.stack([Ax.diagonal(dim1=1, dim2=2).sum(1), last_var, sc[:, 0, -1]], dim=1),)
+
+    def sweep():
+        return S.rollouts_sharded(sweep_local, [x0_all, u_all])
+
+    ms, res, clk = timed_iters(sweep, 2, ctx)
+    lo, hi, (summary,) = res
+    marks = ev["marks"]
+    gp_ms = sum(marks[2 * t].elapsed_time(marks[2 * t + 1]) for t in range(horizon))
+    dyn_ms = sum(marks[2 * t + 1].elapsed_time(marks[2 * t + 2]) for t in range(horizon))
+    tight_ms = marks[2 * horizon].elapsed_time(marks[2 * horizon + 1])
+    finite = bool(torch.isfinite(summary).all())
+    finite = ctx.max_over_ranks(0.0 if finite else 1.0) == 0.0
+    clk_all = ctx.gather_objects({"sm_mhz": clk.get("sm_mhz"), "reasons": clk.get("reasons")})
+    out = {"config5": {
+        "what": f"{rollouts} rollouts x horizon {horizon} over {world} rank(s) ({hi - lo} rollouts per rank): {horizon} sequential "
+                f"stage batches [3-GP mean+var+Jacobian (N={n_train}, d=16) + RK4 stage dynamics with sensitivities "
+                f"(GPs d=1,3,3, N={n_train})] + constraint tightening; sharding.rollouts_sharded, no collective",
+        "ms_per_sweep_max_over_ranks": ms, "stage_evals_per_s_aggregate": rollouts * horizon / (ms * 1e-3),
+        "gp_preds_per_s_aggregate": N_GP * rollouts * horizon / (ms * 1e-3),
+        "rank0_breakdown_ms": {"gp_predictions": gp_ms, "stage_dynamics": dyn_ms, "tightening": tight_ms},
+        "all_finite": finite, "clocks_per_rank": clk_all}}
+    del gb, sd, ct
+    E.release_scratch()
+    torch.cuda.empty_cache()
+    return out
+
+
+# --------------------------------------------------------------------------------------------------
+# N = 1 only: config 2 (round 1's headline), the mean+Jacobian kernel alone, float32 path, config 1, MPC rows
+# --------------------------------------------------------------------------------------------------
+def measure_single_gpu_extras(ctx, gb, workload):
+    from gpmpc_b200 import engine as E
+    from gpmpc_b200.gp import predict_host
+
+    dev, flush = ctx.dev, ctx.flush
+    out = {}
+    n_train, n_query, _ = WORKLOADS["config2"]
+    problem = make_problem(n_train, n_query)
+    if gb is None:
+        gb = E.fit_batch(problem["X"].to(dev), problem["Y"].to(dev), problem["ell"], problem["sf2"], problem["noise"])
+    Z = problem["Z"].to(dev)
+    npreds = N_GP * n_query
+    c2 = {"what": workload_string("config2", n_train, n_query)}
+    for _ in range(3):
+        E.predict(gb, Z)
+    steps = 20
+    ms = timed_steps(lambda: E.predict(gb, Z), steps, flush, dev) / steps
+    c2["value"], c2["ms_per_step"] = npreds / (ms * 1e-3), ms
+    Zh = problem["Z"].pin_memory()
+    oh = None
+    for _ in range(3):
+        oh = predict_host(gb, Zh, oh)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oh = predict_host(gb, Zh, oh)
+    c2["e2e_value"] = npreds * steps / (time.perf_counter() - t0)
+    roof = measure_roofline(gb, Z, ctx, 10)
+    S_ = gb.digits
+    roof["step_frac"] = float(n_train) ** 2 * S_ * (S_ + 1) / 2 * npreds / (ms * 1e-3) / 1e12 / roof["peak"]
+    c2["roofline"] = {k: roof[k] for k in ("kernel", "achieved", "peak", "frac", "frac_of_nominal", "step_frac", "ms_per_launch",
+                                           "fp64_equivalent_tflops")}
+    # accuracy of the int8 variance path against the FP64 DMMA path, normwise and element-wise, per digit count
+    v_ref = E.predict(gb, Z, var_path="f64")[1]
+    sf2 = problem["sf2"]
+    v5 = E.predict(gb, Z)[1]
+    c2["var_rel_err_vs_dmma_path"] = {"digits": S_, "normwise": rel_dev(v5, v_ref), "elementwise_floor_1e-3_sf2": elementwise_var_err(v5, v_ref, sf2)}
     Z32 = Z.float()
     for _ in range(3):
         E.predict(gb, Z32)
-    ms = timed_steps(lambda: E.predict(gb, Z32), 10, flush, dev) / 10
-    out["f32_path_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
-    # the same step with the variance contraction on the FP64 DMMA pipe (round-1 first path, kept as var_path="f64")
+    ms32 = timed_steps(lambda: E.predict(gb, Z32), 10, flush, dev) / 10
+    c2["f32_path_preds_per_s"] = npreds / (ms32 * 1e-3)
     for _ in range(3):
         E.predict(gb, Z, var_path="f64")
-    ms = timed_steps(lambda: E.predict(gb, Z, var_path="f64"), 10, flush, dev) / 10
-    out["dmma_var_path_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
-    v_ref = E.predict(gb, Z, var_path="f64")[1]
-    out["var_rel_err_vs_dmma_path_digits5"] = float((E.predict(gb, Z)[1] - v_ref).abs().max() / v_ref.abs().max())
-    # the same step with 4 (30-bit) or 6 (46-bit) digits: 10 / 21 digit products instead of 15
+    msd = timed_steps(lambda: E.predict(gb, Z, var_path="f64"), 10, flush, dev) / 10
+    c2["dmma_var_path_preds_per_s"] = npreds / (msd * 1e-3)
     for S in (4, 6):
-        gbs = E.fit_batch(problem["X"].to(dev), problem["Y"].to(dev), problem["ell"], problem["sf2"], problem["noise"],
-                          digits=S)
+        gbs = E.fit_batch(problem["X"].to(dev), problem["Y"].to(dev), problem["ell"], problem["sf2"], problem["noise"], digits=S)
         for _ in range(3):
             E.predict(gbs, Z)
-        ms = timed_steps(lambda: E.predict(gbs, Z), 10, flush, dev) / 10
-        out[f"digits{S}_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
-        out[f"var_rel_err_vs_dmma_path_digits{S}"] = float((E.predict(gbs, Z)[1] - v_ref).abs().max() / v_ref.abs().max())
+        msS = timed_steps(lambda: E.predict(gbs, Z), 10, flush, dev) / 10
+        vS = E.predict(gbs, Z)[1]
+        c2[f"digits{S}"] = {"preds_per_s": npreds / (msS * 1e-3), "var_normwise": rel_dev(vS, v_ref),
+                            "var_elementwise_floor_1e-3_sf2": elementwise_var_err(vS, v_ref, sf2)}
         del gbs
-    for name, zz in (("f64", Z), ("f32", Z32)):
+    out["config2"] = c2
+    # north-star kernel (a): mean + Jacobian alone, against the FP32 / FP64 FMA pipes (68 flops per pair at d=16)
+    peaks = load_peaks()
+    mj = {}
+    for name, zz, pk in (("f64", Z, peaks.get("dmma_tflops_bps8", 37.1)), ("f32", Z32, peaks.get("ffma_tflops_bps8", 72.5))):
         for _ in range(3):
             E.predict(gb, zz, want_var=False)
-        ms = timed_steps(lambda: E.predict(gb, zz, want_var=False), 10, flush, dev) / 10
-        out[f"mean_jac_only_{name}_preds_per_s"] = N_GP * N_QUERY / (ms * 1e-3)
-        out[f"mean_jac_only_{name}_pairs_per_s"] = N_GP * N_QUERY * N_TRAIN / (ms * 1e-3)
-    # MLL value + full gradient for one GP (fit_gp's inner iteration), N = 2048
-    X, y = problem["X"].to(dev), problem["Y"][:, 0].to(dev)
-
-    def mll_iter():
-        fit, ws = E.factorize(X, y, problem["ell"], problem["sf2"], problem["noise"], want_kinv=True, want_image=False)
-        E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
-
-    for _ in range(2):
-        mll_iter()
-    torch.cuda.synchronize(dev)
-    t0 = time.perf_counter()
-    for _ in range(5):
-        mll_iter()
-    torch.cuda.synchronize(dev)
-    out["mll_grad_iters_per_s_n2048"] = 5 / (time.perf_counter() - t0)
-    # the same iteration at N = 16384 (half of config 4's N, to keep the default run short): the large GEMMs of the
-    # Cholesky / triangular inverse / K^-1 run on the tcgen05 int8 pipe (csrc/ozgemm.cu, E.FIT_GEMM_DIGITS digits),
-    # compared with the FP64 DMMA pipe alone
-    gb16 = torch.Generator().manual_seed(1337)
-    Xb = (torch.rand(16384, DIM, generator=gb16, dtype=torch.float64) * 2.0 - 1.0).to(dev)
-    yb = (torch.sin(Xb @ torch.randn(DIM, generator=gb16, dtype=torch.float64).to(dev))
-          + 0.05 * torch.randn(16384, generator=gb16, dtype=torch.float64).to(dev))
-    big = problem
-    saved = E.FIT_GEMM_DIGITS
-    losses = {}
-    for tag, digits in (("dmma", 0), ("int8", saved or 6)):
-        E.FIT_GEMM_DIGITS = digits
-        E.release_scratch()
-
-        def big_iter():
-            fit, ws = E.factorize(Xb, yb, big["ell"], big["sf2"], big["noise"], want_kinv=True, want_image=False)
-            return E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))[0]
-
-        big_iter()
-        torch.cuda.synchronize(dev)
-        t0 = time.perf_counter()
-        for _ in range(3):
-            losses[tag] = big_iter()
-        torch.cuda.synchronize(dev)
-        dt = (time.perf_counter() - t0) / 3
-        out[f"mll_grad_iters_per_s_n16384_{tag}"] = 1.0 / dt
-        out[f"mll_grad_n16384_{tag}_tflops_of_n3"] = 16384.0 ** 3 / dt * 1e-12
-    out["mll_grad_n16384_int8_digits"] = int(saved or 6)
-    out["mll_n16384_rel_dev_int8_vs_dmma"] = abs(losses["int8"] - losses["dmma"]) / abs(losses["dmma"])
-    E.FIT_GEMM_DIGITS = saved
-    E.release_scratch()
-    del Xb, yb
+        msj = timed_steps(lambda: E.predict(gb, zz, want_var=False), 10, flush, dev) / 10
+        pairs = npreds * n_train / (msj * 1e-3)
+        mj[name] = {"preds_per_s": npreds / (msj * 1e-3), "pairs_per_s": pairs, "tflops_at_68_per_pair": pairs * 68e-12,
+                    "pipe_peak_tflops": pk, "frac": pairs * 68e-12 / pk}
+    out["mean_jac_only"] = mj
     out.update(measure_mpc_rows(gb, problem, flush, dev))
+    out.update(measure_config1(ctx))
     return out
+
+
+def measure_config1(ctx):
+    """BASELINE.json configs[0] restated as shapes: P=3 GPs, d=(1,3,3), N=45, Adam lr 1e-3 <= 500 iterations
+    from raw = 0 through the drop-in fit_gp, then the Q=25 eval-mode covariance diagonal; the CPU oracle loop beside it."""
+    from gpmpc_b200.gp import GaussianProcess, fit_gp
+    from oracle import gp_oracle as o
+
+    g = torch.Generator().manual_seed(1)
+    N = 45
+    X = torch.rand(N, 7, generator=g, dtype=torch.float64) - 0.5
+    Y = 0.3 * torch.sin(3 * X[:, :3]) + 0.01 * torch.randn(N, 3, generator=g, dtype=torch.float64)
+    idx = ([0], [1, 2, 3], [4, 5, 6])
+    torch.set_num_threads(os.cpu_count() or 1)
+    t0 = time.perf_counter()
+    iters_cpu = sum(len(o.fit_hyperparameters(X[:, idx[p]].contiguous(), Y[:, p].contiguous(), n_train=500, lr=1e-3)["losses"])
+                    for p in range(3))
+    t_cpu = time.perf_counter() - t0
+    t_gpu = iters = None
+    for _ in range(2):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        iters = 0
+        for p in range(3):
+            gp = GaussianProcess(X[:, idx[p]].contiguous(), Y[:, p].contiguous())
+            fit_gp(gp, n_train=500, lr=1e-3, device=str(ctx.dev))
+            iters += len(gp.fit_losses)
+        torch.cuda.synchronize()
+        t_gpu = time.perf_counter() - t0
+    z = (torch.rand(25, 3, generator=g, dtype=torch.float64) - 0.5).to(ctx.dev)
+    gp.eval()
+    t0 = time.perf_counter()
+    for _ in range(20):
+        torch.diag(gp.likelihood(gp(z)).covariance_matrix).cpu()
+    t_eval = (time.perf_counter() - t0) / 20
+    return {"config1": {"what": "reference shapes: 3 GPs d=(1,3,3), N=45, fit_gp Adam lr=1e-3 <= 500 iterations (early stop), then "
+                                "eval-mode covariance diagonal at Q=25 (gpmpc/gpmpc.py:441-445)",
+                        "gpu_fit_ms_per_iter": t_gpu / iters * 1e3, "gpu_iters": iters, "gpu_fit_total_s": t_gpu,
+                        "cpu_oracle_fit_ms_per_iter": t_cpu / iters_cpu * 1e3, "cpu_iters": iters_cpu,
+                        "gpu_eval_cov_diag_ms": t_eval * 1e3}}
 
 
 def measure_mpc_rows(gb, problem, flush, dev):

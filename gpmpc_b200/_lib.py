@@ -50,6 +50,7 @@ SIGNATURES = {
     "gpk_oz_gemm_work_bytes": (_l, [_l, _i]),
     "gpk_oz_gemm_set_workspace": (_i, [_p, _l, _i, _l]),
     "gpk_oz_default_digits": (_i, []),
+    "gpk_oz_max_npad": (_l, [_i]),
     "gpk_oz_w_image_bytes": (_l, [_l, _i]),
     "gpk_oz_e_image_bytes": (_l, [_l, _l, _i]),
     "gpk_oz_slice_w": (_i, [_p, _l, _l, _i, _p, _p, _p]),

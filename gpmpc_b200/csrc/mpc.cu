@@ -231,7 +231,8 @@ __global__ void __launch_bounds__(TC_WARPS * 32) tighten_kernel(TightenArgs a) {
 template <int BS>
 static int launch_tighten(const TightenArgs& a, cudaStream_t st) {
     const int smem = (int)sizeof(TightenSmem<BS>);
-    static bool configured = false;
+    static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
+    bool& configured = attr_dev[current_device()];
     if (!configured) {
         GPK_CUDA(cudaFuncSetAttribute(tighten_kernel<BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;

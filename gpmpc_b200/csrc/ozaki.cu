@@ -685,6 +685,17 @@ constexpr int OZ_MAX_SPLITS = 16;
 extern "C" {
 
 int gpk_oz_default_digits(void) { return 5; }
+
+// Largest training-set size whose int32 digit-group accumulators provably cannot overflow.  The last group (g = S-1)
+// sums S digit products per k: (a_0, b_g) and (a_g, b_0) with a leading digit (|a_0| <= 64, 0 <= b_0 <= 64 because
+// E = exp(.) lies in (0, 1]) and S-2 products of trailing digits in [-128, 127].  Most negative sum per k:
+// -(64*128 + 128*64 + (S-2)*128*127) = -(16384 + (S-2)*16256) >= -2^31 / N; the positive side is smaller because
+// a_g * b_0 > 0 needs a_g > 0 (<= 127).  S = 5: N <= 32961 (config 4's N = 32768 fits), S = 6: 26379, S = 4: 43919.
+long gpk_oz_max_npad(int S) {
+    if (S < OZ_MIN_S || S > OZ_MAX_S) return -1;
+    const long per_k = 16384 + (long)(S - 2) * 16256;
+    return ((1L << 31) / per_k) / TILE * TILE;
+}
 int gpk_oz_query_tile(void) { return OZ_QT; }
 
 long gpk_oz_w_image_bytes(long npad, int S) { return (npad % TILE || S < OZ_MIN_S || S > OZ_MAX_S) ? -1 : (long)S * npad * npad; }
@@ -787,7 +798,7 @@ static int oz_var_partials(const void* Eimg, long strideE, const void* Wimg, lon
     GPK_ARG(npad > 0 && npad % TILE == 0 && qpad > 0 && qpad % OZ_QT == 0 && ld_part >= qpad && batch >= 1, "sizes");
     GPK_ARG(S >= OZ_MIN_S && S <= OZ_MAX_S, "digits must be 4, 5 or 6");
     GPK_ARG(((uintptr_t)Wimg % 16) == 0 && ((uintptr_t)Eimg % 16) == 0 && strideW % 16 == 0 && strideE % 16 == 0, "alignment");
-    GPK_ARG((long)S * npad * 16384 < (1L << 31), "npad too large for exact int32 accumulation with this many digits");
+    GPK_ARG(npad <= gpk_oz_max_npad(S), "npad too large for exact int32 accumulation with this many digits");
     const long nib = npad / (2 * OZ_WB);     // W row-block pairs
     GPK_ARG(n_pieces >= 1 && n_pieces <= OZ_MAX_PIECES && n_pieces <= nib, "n_pieces");
     OzArgs a{};

@@ -10,7 +10,8 @@
 //
 // truncated at g < S (S = 4/5/6 digits = 30/38/46 bits: |error| ~ 2^(-8S+2) relative to max|W_i| -- S = 5
 // reproduces the fp64 variance to ~2e-9 relative at N = 2048, see tests).  Everything but the final
-// recombination is exact; the int32 accumulators cannot overflow while S * N * 2^14 < 2^31.
+// recombination is exact; the int32 accumulators cannot overflow while N (16384 + (S-2) 16256) <= 2^31
+// (gpk_oz_max_npad: N <= 32961 at S = 5; the leading digits are <= 64 and E > 0).
 //
 // Shared-memory / HBM operand layout ("tile images"): operands are stored in HBM exactly as the tensor core
 // wants them in shared memory (K-major, no swizzle: 8-row x 16-byte core matrices), so a pipeline stage is

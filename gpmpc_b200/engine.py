@@ -229,10 +229,12 @@ def _as_device_f64(t: torch.Tensor, device) -> torch.Tensor:
 
 
 def i8_supported(npad: int, digits: int | None = None) -> bool:
-    """The int32 accumulators of the tcgen05 variance path are exact while digits * npad * 2^14 < 2^31
-    (npad <= 26214 at the default 5 digits); larger training sets use the DMMA path (var_path="f64")."""
-    digits = _lib.load().gpk_oz_default_digits() if digits is None else digits
-    return digits * npad * 16384 < 2 ** 31
+    """The int32 accumulators of the tcgen05 variance path provably cannot overflow up to gpk_oz_max_npad(digits)
+    training points (32768 at the default 5 digits: the leading digits are <= 64 and E > 0, see csrc/ozaki.cu); larger
+    training sets use the DMMA path (var_path="f64")."""
+    lib = _lib.load()
+    digits = lib.gpk_oz_default_digits() if digits is None else digits
+    return npad <= lib.gpk_oz_max_npad(digits)
 
 
 @_on_arg_device

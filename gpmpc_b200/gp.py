@@ -43,16 +43,16 @@ def _need_casadi():
 def covSE_single(x, z, ell, sf2):
     """sf2 * exp(-1/2 sum_j (x_j - z_j)^2 / ell_j^2), CasADi symbolic; x (d,), z (d,N)."""
     _need_casadi()
-    sq = cs.sum1(((x - z) / ell) ** 2)
-    return sf2 * cs.exp(-sq / 2)
+    r2 = cs.sum1((x - z) ** 2 / ell**2)      # same operation order as the reference: bit-equal outputs
+    return sf2 * cs.exp(-0.5 * r2)
 
 
 def covSE_vectorized(x, Z, ell, sf2):
     """Same kernel with the second argument given row-major, Z (M,d)."""
     _need_casadi()
     m = Z.shape[0]
-    sq = cs.sum1(((cs.repmat(x, 1, m) - Z.T) / ell) ** 2)
-    return sf2 * cs.exp(-sq / 2)
+    r2 = cs.sum1((cs.repmat(x, 1, m) - Z.T) ** 2 / ell**2)
+    return sf2 * cs.exp(-0.5 * r2)
 
 
 # --------------------------------------------------------------------------------------------------

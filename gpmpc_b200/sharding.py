@@ -117,6 +117,66 @@ def broadcast_tensors(tensors: Sequence[torch.Tensor], src: int = 0, group=None)
         dist.broadcast(t, src=src, group=group)
 
 
+def replicate_batch(batch, src: int = 0, *, device=None, with_W: bool = False, group=None):
+    """Fitted prediction state of `src` (an engine.GPBatch; None on the other ranks) -> an equivalent GPBatch on
+    every rank: the one-time state replication after a fit that query sharding needs.  One small
+    object broadcast (sizes, hyper-parameter scalars) and one broadcast per tensor: X, y, hyp, alpha and -- when the
+    fit carries them -- the int8 digit image of W = L^-1 with its row scales (what the tcgen05 variance path reads;
+    S N^2 bytes per GP) ; the float64 W itself (8 N^2 bytes per GP, only the DMMA variance path reads it) travels
+    only with with_W=True.  Returns (batch, bytes received per rank)."""
+    from . import engine as E
+
+    rank, world = world_info(group)
+    if world == 1:
+        return batch, 0
+    meta = [None]
+    if rank == src:
+        f0 = batch.fits[0]
+        has_img = batch.wimg is not None
+        meta[0] = {"B": len(batch.fits), "n": f0.n, "d": f0.d, "npad": f0.npad, "digits": batch.digits if has_img else 0,
+                   "img_bytes": int(batch.wimg.shape[1]) if has_img else 0,
+                   "with_W": bool(with_W and batch.W is not None),
+                   "fits": [{"center": f.center, "ell": f.ell, "sf2": f.sf2, "noise": f.noise, "quad": f.quad,
+                             "logdet": f.logdet, "jitter": f.jitter} for f in batch.fits]}
+        device = batch.device
+    dist.broadcast_object_list(meta, src=src, group=group, device=device if device is not None and
+                               torch.device(device).type == "cuda" else None)
+    m = meta[0]
+    B, n, d, npad = m["B"], m["n"], m["d"], m["npad"]
+    F64 = torch.float64
+    if rank == src:
+        X, hyp, alpha = batch.X.contiguous(), batch.hyp.contiguous(), batch.alpha.contiguous()
+        y = torch.stack([f.y for f in batch.fits])
+        wimg, wscale = batch.wimg, batch.wscale
+        W = batch.W if m["with_W"] else None
+    else:
+        X = torch.empty(B, n, d, dtype=F64, device=device)
+        y = torch.empty(B, n, dtype=F64, device=device)
+        hyp = torch.empty(B, batch_hyp_stride(), dtype=F64, device=device)
+        alpha = torch.empty(B, npad, dtype=F64, device=device)
+        wimg = torch.empty(B, m["img_bytes"], dtype=torch.int8, device=device) if m["digits"] else None
+        wscale = torch.empty(B, npad, dtype=F64, device=device) if m["digits"] else None
+        W = torch.empty(B, npad, npad, dtype=F64, device=device) if m["with_W"] else None
+    tensors = [t for t in (X, y, hyp, alpha, wimg, wscale, W) if t is not None]
+    broadcast_tensors(tensors, src=src, group=group)
+    nbytes = sum(t.numel() * t.element_size() for t in tensors)
+    if rank == src:
+        return batch, nbytes
+    fits = [E.GPFit(X=X[p], y=y[p], n=n, d=d, npad=npad, center=fm["center"], ell=fm["ell"], sf2=fm["sf2"],
+                    noise=fm["noise"], hyp=hyp[p], W=W[p] if W is not None else None, alpha=alpha[p],
+                    wimg=wimg[p] if wimg is not None else None, wscale=wscale[p] if wscale is not None else None,
+                    digits=m["digits"], quad=fm["quad"], logdet=fm["logdet"], jitter=fm["jitter"])
+            for p, fm in enumerate(m["fits"])]
+    out = E.GPBatch(fits, X, W, hyp, wimg, wscale, m["digits"])
+    out._alpha = alpha
+    return out, nbytes
+
+
+def batch_hyp_stride() -> int:
+    """Doubles per GP in the hyper-parameter block (include/gpmpc_b200.h: centre[32] | 1/ell[32] | sf2 | noise | pad)."""
+    return 72
+
+
 # --------------------------------------------------------------------------------------------------
 # output-GP sharding
 # --------------------------------------------------------------------------------------------------
@@ -208,8 +268,12 @@ class RowSplitGradReduce:
     distributed), forms ONLY its rows of K^-1 (`rows(n)`, picked up by the fit loop) and reduces the
     gradient trace over them; one all_reduce(sum) of d+2 doubles completes the gradient on every rank."""
 
-    def __init__(self, group=None):
+    def __init__(self, group=None, time_allreduce: bool = False):
         self.group = group
+        # with time_allreduce the all_reduce of every call is bracketed by CUDA events on the caller's stream
+        # (`allreduce_events`, consumed by `allreduce_ms()`): wait for the slowest rank + the collective itself
+        self.time_allreduce = time_allreduce
+        self.allreduce_events: list = []
 
     def rows(self, n: int) -> tuple[int, int]:
         from . import engine as E
@@ -227,10 +291,26 @@ class RowSplitGradReduce:
         else:   # empty block (small n): contributes zeros, and must not touch K^-1 rows it never formed
             part = torch.zeros(E._lib.load().gpk_pad_dim(fit.d) + 2, dtype=torch.float64, device=fit.device)
         if world > 1:
+            timed = self.time_allreduce and part.is_cuda
+            if timed:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
             dist.all_reduce(part, op=dist.ReduceOp.SUM, group=self.group)
+            if timed:
+                e1.record()
+                self.allreduce_events.append((e0, e1))
         return part
 
+    def allreduce_ms(self) -> list:
+        """Durations (ms) of the timed all_reduces since the last call; synchronises the recorded events."""
+        out = []
+        for e0, e1 in self.allreduce_events:
+            e1.synchronize()
+            out.append(e0.elapsed_time(e1))
+        self.allreduce_events = []
+        return out
 
-def rowsplit_grad_reduce(group=None) -> Callable:
+
+def rowsplit_grad_reduce(group=None, time_allreduce: bool = False) -> Callable:
     """See RowSplitGradReduce."""
-    return RowSplitGradReduce(group)
+    return RowSplitGradReduce(group, time_allreduce)

@@ -145,6 +145,8 @@ int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq,
  * processed in chunks that fit the scratch given.  mj_done_event (cudaEvent_t as void*, may be NULL) is
  * recorded on `stream` as soon as mean and jac are final, before the variance contraction of the last chunk. */
 int gpk_oz_default_digits(void);
+long gpk_oz_max_npad(int digits);                          /* largest npad with overflow-free int32 accumulation: 32768 at
+                                                              5 digits, 26368 at 6, 43904 at 4; -1 if unsupported digits */
 int gpk_oz_query_tile(void);                               /* queries per tile of the E image (128) */
 long gpk_oz_w_image_bytes(long npad, int digits);          /* -1 if unsupported */
 long gpk_oz_e_image_bytes(long qpad, long npad, int digits);

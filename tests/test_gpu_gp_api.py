@@ -237,6 +237,51 @@ def test_full_size_properties_config3():
     E.release_scratch()
 
 
+def test_full_size_properties_config4():
+    """BASELINE config 4 training size (N=32768, d=16): the fit (6-digit int8 potrf / trtri, 5-digit K^-1, inverse factor
+    on the side stream) and BOTH variance paths -- the tcgen05 int8 path is exact up to gpk_oz_max_npad(5) = 32768+ --
+    through the same exact identities as config 3 (no O(N^3) oracle pass)."""
+    from gpmpc_b200 import engine as E
+
+    dev = torch.device("cuda", 0)
+    n, d = 32768, 16
+    assert E.i8_supported(n, 5) and not E.i8_supported(n + 256, 5) and not E.i8_supported(n, 6)
+    p = o.synthetic_problem(n, d, 256, p=1, seed=1337)
+    X, y, Z = p["X"].to(dev), p["Y"][:, 0].to(dev), p["Z"].to(dev)
+    noise, sf2 = p["noise"], p["sf2"]
+    fit, ws = E.factorize(X, y, p["ell"], sf2, noise, want_kinv=True, digits=5)
+    assert ws.gemm_work is not None and fit.wimg is not None and fit.digits == 5
+    alpha = fit.alpha[:n]
+    # residual of the linear system through the factor itself, in row blocks (no second N x N temporary)
+    Lm = ws.L[:n, :n]
+    t = torch.zeros(n, dtype=torch.float64, device=dev)
+    res = torch.empty(n, dtype=torch.float64, device=dev)
+    blk = 4096
+    for r0 in range(0, n, blk):          # t = L^T alpha
+        t[: r0 + blk] += torch.tril(Lm[r0 : r0 + blk, : r0 + blk], diagonal=r0).T @ alpha[r0 : r0 + blk]
+    for r0 in range(0, n, blk):          # res = L t - y
+        res[r0 : r0 + blk] = torch.tril(Lm[r0 : r0 + blk, : r0 + blk], diagonal=r0) @ t[: r0 + blk] - y[r0 : r0 + blk]
+    assert float(res.abs().max()) < TOL64 * float(y.abs().max())
+    assert abs(fit.quad - float(y @ alpha)) < 1e-9 * abs(fit.quad)
+    assert abs(fit.logdet - 2.0 * float(torch.log(Lm.diagonal()).sum())) < 1e-10 * abs(fit.logdet)
+    # predictions at 512 training inputs: mean and variance identities, int8 variance path
+    idx = torch.arange(0, n, 64, device=dev)
+    mean, var, jac = E.predict(fit, X[idx])
+    assert o.rel_err(mean[0].cpu(), (y[idx] - noise * alpha[idx]).cpu()) < TOL64
+    kinv_diag = ws.Kinv.diagonal()[:n][idx]
+    assert o.rel_err(var[0].cpu(), (noise - noise * noise * kinv_diag).cpu()) < TOL64
+    assert float(var.min()) > 0.0 and float(var.max()) <= noise
+    # away from the data: tcgen05 int8 path == DMMA path
+    m1, v1, j1 = E.predict(fit, Z)
+    m2, v2, j2 = E.predict(fit, Z, var_path="f64")
+    assert o.rel_err(v1[0].cpu(), v2[0].cpu()) < TOL64 and o.rel_err(m1[0].cpu(), m2[0].cpu()) < 1e-10
+    assert o.rel_err(j1[0].cpu(), j2[0].cpu()) < 1e-10
+    assert float(v1.min()) > 0.0 and float(v1.max()) <= sf2
+    del fit, ws, Lm
+    E.release_scratch()
+    torch.cuda.empty_cache()
+
+
 def test_predict_host_roundtrip():
     from gpmpc_b200 import engine as E
     from gpmpc_b200.gp import predict_host

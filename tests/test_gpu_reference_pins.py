@@ -1,0 +1,77 @@
+"""GPU parity against outputs of the REFERENCE'S OWN CODE (tests/golden/make_golden_covse.py ran the unmodified
+gpmpc/gp.py:12-21 covSE_single / covSE_vectorized and gpmpc/gp.py:72-85 gpytorch_predict2casadi over a NumPy casadi
+shim).  Rows a1, a2, a5 (K), a6 of SURVEY.md 8(a).  Run with -m gpu."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+COVSE = [f"covse_d{d}_{k}" for d in (1, 3, 16) for k in ("shared", "ard")]
+DEV = torch.device("cuda", 0)
+
+
+def _ell_vec(g, d):
+    ell = torch.from_numpy(g["ell"]).reshape(-1)
+    return ell.expand(d).clone() if ell.numel() == 1 else ell
+
+
+@pytest.mark.parametrize("name", COVSE)
+def test_cross_kernel_matches_reference_covse(name):
+    """gpk_cross_kernel (the kernel every CUDA path shares) against covSE_single / covSE_vectorized, element-wise."""
+    from gpmpc_b200 import engine as E
+
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    x, Z = torch.from_numpy(g["x"])[None].to(DEV), torch.from_numpy(g["Z"]).to(DEV)
+    d, sf2 = Z.shape[1], float(g["sf2"])
+    ell = _ell_vec(g, d)
+    center = Z.mean(dim=0).cpu()                      # the kernels centre their inputs (translation invariant)
+    fit = E.GPFit(X=Z, y=None, n=Z.shape[0], d=d, npad=E.round_up(Z.shape[0], E.TILE), center=center, ell=ell, sf2=sf2,
+                  noise=0.0, hyp=E.make_hyp(center, ell, sf2, 0.0, d, DEV), W=None, alpha=None)
+    k = E.cross_K(fit, x, Z).cpu().numpy()
+    for ref in (g["k_single"], g["k_vec"]):
+        assert k.shape == ref.shape
+        assert (np.abs(k - ref) / ref).max() < 5e-13, name       # element-wise relative (no cancellation in the kernel)
+
+
+@pytest.mark.parametrize("name", ["pred_d3_n45", "pred_d16_n300"])
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-6), (torch.float32, 1e-4)])
+def test_fused_mean_matches_reference_casadi_mean(name, dtype, tol):
+    """The fused CUDA mean (every prediction path) against the reference's exported CasADi "pred" function."""
+    from gpmpc_b200 import engine as E
+
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    X, y, Z = (torch.from_numpy(g[k]).to(DEV) for k in ("X", "y", "Z"))
+    ell, sf2, noise = _ell_vec(g, X.shape[1]), float(g["sf2"]), float(g["noise"])
+    fit, _ = E.factorize(X, y, ell, sf2, noise)
+    ref = g["mean"]
+    for kw in ({}, {"want_var": False}, {"want_var": False, "mj_path": "simt"}, {"var_path": "f64"}):
+        mean = E.predict(fit, Z.to(dtype), **kw)[0][0].double().cpu().numpy()
+        err = np.abs(mean - ref).max() / np.abs(ref).max()
+        assert err < (1e-9 if dtype == torch.float64 else tol), (name, kw, err)
+
+
+def test_repo_casadi_export_matches_reference_export(monkeypatch):
+    """gpmpc_b200.gp.gpytorch_predict2casadi (alpha from the GPU fit) evaluated over the NumPy casadi shim against the
+    reference's own function on the same GP; gp.K against K_f + noise I of the reference's kernel (gp.py:45)."""
+    import casadi_shim
+    from gpmpc_b200 import gp as G
+
+    monkeypatch.setattr(G, "cs", casadi_shim)
+    g = np.load(os.path.join(GOLD, "pred_d3_n45.npz"))
+    X, y = torch.from_numpy(g["X"]), torch.from_numpy(g["y"])
+    gp = G.GaussianProcess(X, y).double()             # float64 parameters: the fixture's values are not float32 numbers
+    gp.set_hyperparameters(torch.from_numpy(g["ell"]).reshape(-1), float(g["sf2"]), float(g["noise"]))
+    gp.eval()
+    pred = G.gpytorch_predict2casadi(gp)
+    assert pred.name() == "pred"
+    mean = np.array([float(np.asarray(pred(z=z)["mean"]).reshape(-1)[0]) for z in g["Z"]])
+    assert np.abs(mean - g["mean"]).max() / np.abs(g["mean"]).max() < 1e-9
+    K, K_inv = gp.compute_covariances()
+    assert np.abs(K.numpy() - g["K"]).max() < 1e-13 * np.abs(g["K"]).max()
+    assert np.abs(K_inv.numpy() - np.linalg.inv(g["K"])).max() < 1e-8 * np.abs(np.linalg.inv(g["K"])).max()
+    # the CasADi-free callable serves the same mean
+    call = G.predict_callable(gp)
+    assert np.abs(call(g["Z"])["mean"] - g["mean"]).max() / np.abs(g["mean"]).max() < 1e-9

@@ -187,6 +187,58 @@ def test_golden_fixtures_reproduce():
         assert o.rel_err(gl, g["g_raw_ell"]) < 1e-8 and o.rel_err(gn, g["g_raw_noise"]) < 1e-8, f
 
 
+# ---- rows a1 / a2 / a6: fixtures written by the reference's own covSE_* and gpytorch_predict2casadi ---------
+# (tests/golden/make_golden_covse.py runs the unmodified gpmpc/gp.py:12-21,72-85 over a NumPy casadi shim)
+COVSE = [f"covse_d{d}_{k}" for d in (1, 3, 16) for k in ("shared", "ard")]
+
+
+@pytest.mark.parametrize("name", COVSE)
+def test_oracle_kernel_matches_reference_covse(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    x, Z = torch.from_numpy(g["x"])[None], torch.from_numpy(g["Z"])
+    ell, sf2 = torch.from_numpy(g["ell"]).reshape(-1), float(g["sf2"])
+    assert np.array_equal(g["k_single"], g["k_vec"]) or np.abs(g["k_single"] - g["k_vec"]).max() < 1e-15
+    for fn in (o.se_kernel, o.se_kernel_gpytorch):
+        k = fn(x, Z, ell, sf2).numpy()
+        # element-wise relative error: the kernel is a product of exponentials, no cancellation
+        assert np.abs(k - g["k_single"]).max() < 1e-14 * sf2, (name, fn.__name__)
+        assert (np.abs(k - g["k_single"]) / g["k_single"]).max() < 2e-13, (name, fn.__name__)
+
+
+@pytest.mark.parametrize("name", ["pred_d3_n45", "pred_d16_n300"])
+def test_oracle_mean_matches_reference_casadi_mean(name):
+    """mean = k(z,X) @ K_inv @ y exactly as the reference's exported CasADi function evaluates it (gp.py:85, with
+    K_inv from torch.linalg.inv, gp.py:46) against the oracle's Cholesky form."""
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    X, y, Z = (torch.from_numpy(g[k]) for k in ("X", "y", "Z"))
+    ell, sf2, noise = torch.from_numpy(g["ell"]).reshape(-1), float(g["sf2"]), float(g["noise"])
+    st = o.fit_state(X, y, ell, sf2, noise)
+    mean, _, _ = o.predict(Z, X, ell, sf2, st["L"], st["alpha"])
+    assert o.rel_err(mean, g["mean"]) < 1e-10, name
+    if "K" in g:
+        assert o.rel_err(st["K"], g["K"]) < 1e-14, name
+
+
+def test_repo_casadi_twins_match_reference_bitwise(monkeypatch):
+    """gpmpc_b200.gp.covSE_single / covSE_vectorized executed over the same NumPy shim reproduce the reference's
+    outputs bit for bit (same operation order)."""
+    import casadi_shim
+    from gpmpc_b200 import gp as G
+
+    monkeypatch.setattr(G, "cs", casadi_shim)
+    for name in COVSE:
+        g = np.load(os.path.join(GOLD, name + ".npz"))
+        ks = np.asarray(G.covSE_single(g["x"][:, None], g["Z"].T, g["ell"].T, float(g["sf2"])))
+        kv = np.asarray(G.covSE_vectorized(g["x"][:, None], g["Z"], g["ell"].T, float(g["sf2"])))
+        assert np.array_equal(ks, g["k_single"]), name
+        assert np.array_equal(kv, g["k_vec"]), name
+    # symbolic use, as gpytorch_predict2casadi does: a Function of z
+    g = np.load(os.path.join(GOLD, "covse_d3_ard.npz"))
+    z = casadi_shim.SX.sym("z", 3)
+    f = casadi_shim.Function("K_xz", [z], [G.covSE_single(z, g["Z"].T, g["ell"].T, float(g["sf2"]))], ["z"], ["K"])
+    assert np.array_equal(np.asarray(f(z=g["x"])["K"]), g["k_single"])
+
+
 # ---- MPC-side rows (SURVEY.md 8f): fixtures written by the reference's own methods (make_golden_mpc.py) ------
 @pytest.mark.parametrize("name", ["tighten_T25", "tighten_T40"])
 def test_tightening_restatement_matches_reference_output(name):

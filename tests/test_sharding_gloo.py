@@ -146,6 +146,37 @@ def _worker(rank, world, port, q_total):
         t = torch.full((4,), float(rank))
         S.broadcast_tensors([t], src=1)
         assert torch.equal(t, torch.ones(4))
+        # --- replication of a fitted GPBatch from rank 0 (host logic only: CPU tensors stand in for the device state)
+        from gpmpc_b200 import engine as E
+
+        def fake_batch(seed):
+            gg = torch.Generator().manual_seed(seed)
+            Bn, nn, dd, npad, S_ = 2, 60, 3, 128, 5
+            fits = []
+            for k in range(Bn):
+                fits.append(E.GPFit(X=torch.rand(nn, dd, generator=gg, dtype=torch.float64), y=torch.rand(nn, generator=gg, dtype=torch.float64),
+                                    n=nn, d=dd, npad=npad, center=torch.rand(dd, generator=gg, dtype=torch.float64),
+                                    ell=torch.rand(dd, generator=gg, dtype=torch.float64) + 0.5, sf2=1.0 + k, noise=1e-2 * (k + 1),
+                                    hyp=torch.rand(72, generator=gg, dtype=torch.float64), W=torch.rand(npad, npad, generator=gg, dtype=torch.float64),
+                                    alpha=torch.rand(npad, generator=gg, dtype=torch.float64),
+                                    wimg=torch.randint(-128, 127, (S_ * npad * npad,), generator=gg, dtype=torch.int8),
+                                    wscale=torch.rand(npad, generator=gg, dtype=torch.float64), digits=S_, quad=3.0 + k, logdet=-7.0 * (k + 1)))
+            return E.GPBatch.from_fits(fits)
+
+        want = fake_batch(99)
+        for with_W in (False, True):
+            got, nbytes = S.replicate_batch(fake_batch(99) if rank == 0 else None, src=0, device=torch.device("cpu"), with_W=with_W)
+            assert nbytes > 0 and len(got.fits) == 2 and got.digits == 5 and (got.n, got.d, got.npad) == (60, 3, 128)
+            for name in ("X", "hyp", "alpha", "wimg", "wscale"):
+                assert torch.equal(getattr(got, name), getattr(want, name)), name
+            assert (got.W is not None and torch.equal(got.W, want.W)) if (with_W or rank == 0) else got.W is None
+            for fg, fw in zip(got.fits, want.fits):
+                assert torch.equal(fg.y, fw.y) and torch.equal(fg.ell, fw.ell) and torch.equal(fg.center, fw.center)
+                assert (fg.sf2, fg.noise, fg.quad, fg.logdet) == (fw.sf2, fw.noise, fw.quad, fw.logdet)
+                assert abs(fg.mll_per_n() - fw.mll_per_n()) == 0.0
+        # --- timed reducer keeps working without CUDA (no events on CPU tensors)
+        rst = S.rowsplit_grad_reduce(time_allreduce=True)
+        assert rst.allreduce_ms() == []
     finally:
         dist.destroy_process_group()
 
