@@ -19,6 +19,8 @@ _p, _l, _i, _d = C.c_void_p, C.c_long, C.c_int, C.c_double
 # name -> (restype, argtypes); must list every symbol include/gpmpc_b200.h declares
 SIGNATURES = {
     "gpk_abi_version": (_i, []),
+    "gpk_init": (_i, [_p]),
+    "gpk_shutdown": (_i, []),
     "gpk_last_error": (C.c_char_p, []),
     "gpk_launch_count": (_l, []),
     "gpk_reset_launch_count": (None, []),
@@ -57,7 +59,7 @@ SIGNATURES = {
     "gpk_oz_cross": (_i, [_i, _p, _l, _l, _l, _p, _l, _l, _l, _i, _p, _p, _l, _l, _l, _i, _i, _p]),
     "gpk_predict_i8_work_bytes": (_l, [_l, _l, _i, _i, _i]),
     "gpk_predict_i8": (_i, [_i, _p, _l, _l, _l, _i, _p, _p, _l, _l, _l, _p, _l, _p, _l, _p, _l, _l, _i,
-                            _p, _l, _p, _l, _l, _p, _l, _p, _l, _i, _p, _p]),
+                            _p, _l, _p, _l, _l, _p, _l, _p, _l, _i, _i, _p, _p]),
     "gpk_mean_jac_dmma_work_bytes": (_l, [_l, _i, _i]),
     "gpk_predict_mean_jac_dmma": (_i, [_i, _p, _l, _l, _l, _i, _p, _p, _l, _l, _l, _p, _l, _p, _l, _p, _l, _l, _p, _l, _i, _p]),
     "gpk_oz_var_partials": (_i, [_p, _l, _p, _l, _p, _l, _p, _l, _l, _i, _p, _l, _l, _i, _i, _p, _p]),

@@ -116,7 +116,12 @@ __device__ __forceinline__ double exp_neg_tab(double a0, const double* __restric
     const double e = __hiloint2double(__double2hiint(p) + ((m >> 10) << 20), __double2loint(p));
     return a0 < -708.0 ? 0.0 : e;
 }
-// the table in device memory (built once per device on first use; defined in ozaki.cu)
+// the table in device memory (built by gpk_init, or lazily on first use; defined in ozaki.cu)
 const double* exp_table(cudaStream_t st);
+// per-device library state released by gpk_shutdown (ozaki.cu, linalg.cu, ozgemm.cu)
+void exp_table_release();
+int fit_side_prepare(int events);
+void fit_side_release();
+void ozg_items_release();
 
 }  // namespace gpk

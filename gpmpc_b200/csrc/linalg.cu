@@ -533,6 +533,26 @@ struct FitSide {
 };
 static FitSide g_fit_side[64];
 
+// side stream + `events` pooled events of the current device (gpk_init); gpk_potrf_trtri creates them lazily otherwise
+int fit_side_prepare(int events) {
+    FitSide& fs = g_fit_side[current_device()];
+    if (!fs.side) GPK_CUDA(cudaStreamCreateWithFlags(&fs.side, cudaStreamNonBlocking));
+    while ((int)fs.pool.size() < events) {
+        cudaEvent_t ev;
+        GPK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        fs.pool.push_back(ev);
+    }
+    return 0;
+}
+void fit_side_release() {
+    FitSide& fs = g_fit_side[current_device()];
+    for (cudaEvent_t ev : fs.pool) cudaEventDestroy(ev);
+    fs.pool.clear();
+    fs.next = 0;
+    if (fs.side) cudaStreamDestroy(fs.side);
+    fs.side = nullptr;
+}
+
 struct RecBoth {
     Rec f;             // factorisation, on f.st (the caller's stream)
     RecInv v;          // inverse factor, on v.st (the side stream)
@@ -585,7 +605,24 @@ extern "C" {
 const char* gpk_last_error(void) { return g_err; }
 long gpk_launch_count(void) { return g_launches.load(); }
 void gpk_reset_launch_count(void) { g_launches.store(0); }
-int gpk_abi_version(void) { return 1; }
+int gpk_abi_version(void) { return 2; }
+
+// Per-device library state (what the compute entries would otherwise create on first use): the exp table of the
+// prediction front end (8 KB, one cudaMalloc + copy + synchronisation of `stream`), the side stream of
+// gpk_potrf_trtri and a pool of events for it.  Idempotent; call once per device before timing-sensitive work.
+int gpk_init(void* stream) {
+    GPK_ARG(exp_table((cudaStream_t)stream) != nullptr, "could not allocate the exp table");
+    return fit_side_prepare(1024);
+}
+// Frees the current device's library state: exp table, side stream, events, cached int8-GEMM item lists, and forgets
+// the registered int8-GEMM workspace (which stays the caller's).  The library can be used again afterwards.
+int gpk_shutdown(void) {
+    GPK_CUDA(cudaDeviceSynchronize());
+    exp_table_release();
+    fit_side_release();
+    ozg_items_release();
+    return 0;
+}
 
 int gpk_dgemm_nt(const double* A, long lda, const double* B, long ldb, double* C, long ldc, long M, long N, long K,
                  double alpha, double beta, int a_tri, int c_lower, void* stream) {

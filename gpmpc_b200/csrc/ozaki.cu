@@ -581,22 +581,31 @@ static int oz_sm_count() {
     return sms;
 }
 
-// 2^(j/1024) table of the front kernel's exp: computed once per device on the host in long double, rounded to double
+// 2^(j/1024) table of the front kernel's exp: computed on the host in long double, rounded to double.  Built by
+// gpk_init (or lazily by the first prediction on a device: one cudaMalloc + one stream synchronisation), freed by
+// gpk_shutdown.
+static double* g_exp_tab[64] = {nullptr};
 const double* gpk::exp_table(cudaStream_t st) {
-    static double* dev_tab[64] = {nullptr};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return nullptr;
-    if (!dev_tab[dev]) {
+    if (!g_exp_tab[dev]) {
         static double host_tab[EXP_TAB];
         for (int j = 0; j < EXP_TAB; j++) host_tab[j] = (double)exp2l((long double)j / EXP_TAB);
         double* p = nullptr;
         if (cudaMalloc(&p, sizeof(host_tab)) != cudaSuccess) return nullptr;
         if (cudaMemcpyAsync(p, host_tab, sizeof(host_tab), cudaMemcpyHostToDevice, st) != cudaSuccess) return nullptr;
         cudaStreamSynchronize(st);
-        dev_tab[dev] = p;
+        g_exp_tab[dev] = p;
     }
-    return dev_tab[dev];
+    return g_exp_tab[dev];
+}
+void gpk::exp_table_release() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !g_exp_tab[dev]) return;
+    cudaFree(g_exp_tab[dev]);
+    g_exp_tab[dev] = nullptr;
 }
 
 static int oz_pad_dim(int d) { return d <= 4 ? 4 : d <= 8 ? 8 : d <= 16 ? 16 : 32; }
@@ -855,9 +864,10 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
                    const double* X, long ldx, long n, long strideX, const double* alpha, long stride_alpha,
                    const void* Wimg, long strideW, const double* wscale, long stride_ws, long npad, int S,
                    void* mean, long stride_mean, void* jac, long ldj, long stride_jac, void* var, long stride_var,
-                   void* work, long work_bytes, int batch, void* mj_done_event, void* stream) {
+                   void* work, long work_bytes, int batch, int mul_digits, void* mj_done_event, void* stream) {
     GPK_ARG(dtype == 0 || dtype == 1, "dtype must be 0 (f32) or 1 (f64)");
     GPK_ARG(Z && hyp && X && Wimg && wscale && var && work, "null pointer");
+    GPK_ARG(mul_digits == 0 || (mul_digits >= OZ_MIN_S && mul_digits <= S), "mul_digits must be 0 or in [4, digits]");
     GPK_ARG((mean == nullptr) == (jac == nullptr), "mean and jac must both be given or both be NULL");
     GPK_ARG(mean == nullptr || (alpha != nullptr && ldj >= d), "alpha / ldj");
     GPK_ARG(d >= 1 && d <= HYP_MAXD, "d must be in [1, 32]");
@@ -865,11 +875,12 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
     GPK_ARG(S >= OZ_MIN_S && S <= OZ_MAX_S, "digits must be 4, 5 or 6");
     GPK_ARG(((uintptr_t)work % 16) == 0, "work must be 16-byte aligned");
     if (q == 0) return 0;
-    // float32 queries are held to 1e-4 (BASELINE.json): the leading 4 digits of both operands (10 digit products,
-    // ~7e-7 on the variance) are multiplied, whatever the W image carries; the digits are balanced, so dropping the
-    // trailing ones rounds
+    // mul_digits < digits multiplies only the leading mul_digits digits of both operands, whatever the W image carries
+    // (the digits are balanced, so dropping the trailing ones rounds): the caller's accuracy policy picks it, e.g. 4
+    // digits (10 digit products) for float32 queries held to 1e-4 when the fit's conditioning allows
+    // (engine.select_digits); there is no implicit cut by dtype
     const int S_img = S;
-    if (dtype == 0 && S > OZ_MIN_S && !getenv("GPK_OZ_F32_FULL_DIGITS")) S = OZ_MIN_S;
+    if (mul_digits) S = mul_digits;
     const bool mj = mean != nullptr;
     const int dp = oz_pad_dim(d);
     const long per_q = ((long)S * npad + OZ_SLOTS * 8 + (long)OZ_MAX_SPLITS * (dp + 1) * 8) * batch;

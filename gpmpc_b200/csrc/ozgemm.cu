@@ -18,6 +18,7 @@
 #include "gemm_params.cuh"
 #include <cstdlib>
 #include <map>
+#include <mutex>
 #include <tuple>
 #include <vector>
 
@@ -395,12 +396,15 @@ static int ozg_sm_count() {
 // Item list (A tile, C tile column) of a GEMM shape in the order the CTA pairs walk it (static round robin):
 // super-tiles of GM x GN tiles, so the ~74 items in flight share GM A tiles and GN B block pairs (L2 reuse); the
 // super-tile rows with the longest k-ranges come first.  Cached on the device per shape.
+using OzgItemKey = std::tuple<int, int, int, int, int>;
+static std::map<OzgItemKey, std::pair<int2*, int>> g_ozg_item_cache;
+static std::mutex g_ozg_item_mutex;
+
 static const int2* ozg_items(int tiles_m, int tiles_n, int a_tri, int c_lower, int* total, cudaStream_t st) {
-    using Key = std::tuple<int, int, int, int, int>;
-    static std::map<Key, std::pair<int2*, int>> cache;
-    const Key key{ozg_device(), tiles_m, tiles_n, a_tri, c_lower};
-    auto f = cache.find(key);
-    if (f != cache.end()) { *total = f->second.second; return f->second.first; }
+    std::lock_guard<std::mutex> lock(g_ozg_item_mutex);
+    const OzgItemKey key{ozg_device(), tiles_m, tiles_n, a_tri, c_lower};
+    auto f = g_ozg_item_cache.find(key);
+    if (f != g_ozg_item_cache.end()) { *total = f->second.second; return f->second.first; }
     const int GM = g_ozg_gm, GN = g_ozg_gn;
     std::vector<int2> items;
     items.reserve((size_t)tiles_m * tiles_n);
@@ -416,11 +420,16 @@ static const int2* ozg_items(int tiles_m, int tiles_n, int a_tri, int c_lower, i
                     items.push_back(make_int2(tm, tn));
                 }
     }
+    // first sight of a shape on a device: one cudaMalloc + copy + synchronisation of `st` (`items` dies at return);
+    // a fit of one size sees ~10 shapes, all during its first iteration.  Freed by gpk_shutdown.
     int2* dev = nullptr;
     if (cudaMalloc(&dev, items.size() * sizeof(int2)) != cudaSuccess) return nullptr;
-    if (cudaMemcpyAsync(dev, items.data(), items.size() * sizeof(int2), cudaMemcpyHostToDevice, st) != cudaSuccess) return nullptr;
-    cudaStreamSynchronize(st);                                        // `items` dies at return; once per shape
-    cache[key] = {dev, (int)items.size()};
+    if (cudaMemcpyAsync(dev, items.data(), items.size() * sizeof(int2), cudaMemcpyHostToDevice, st) != cudaSuccess) {
+        cudaFree(dev);
+        return nullptr;
+    }
+    cudaStreamSynchronize(st);
+    g_ozg_item_cache[key] = {dev, (int)items.size()};
     *total = (int)items.size();
     return dev;
 }
@@ -535,6 +544,21 @@ int ozg_try(const GemmParams& p, int batch, cudaStream_t st) {
     if (!ozg_shape_ok(p) || ozg_need_bytes(p, ws.digits) > ws.bytes) return 0;
     const int r = ozg_dispatch(p, ws.digits, static_cast<uint8_t*>(ws.ptr), st);
     return r == 0 ? 1 : r;
+}
+
+// gpk_shutdown: drop the current device's cached item lists and forget its registered workspace
+void ozg_items_release() {
+    std::lock_guard<std::mutex> lock(g_ozg_item_mutex);
+    const int dev = ozg_device();
+    for (auto it = g_ozg_item_cache.begin(); it != g_ozg_item_cache.end();) {
+        if (std::get<0>(it->first) == dev) {
+            cudaFree(it->second.first);
+            it = g_ozg_item_cache.erase(it);
+        } else {
+            ++it;
+        }
+    }
+    g_ozg_ws[dev] = OzgWorkspace{};
 }
 
 }  // namespace gpk

@@ -51,6 +51,29 @@ def _on_arg_device(fn):
     return wrapper
 
 
+_initialised: set = set()
+
+
+def init(device=None) -> torch.device:
+    """Create the library's per-device state up front (gpk_init: exp table, side stream, event pool) so that no later
+    compute entry allocates or synchronises for it; called by factorize() / predict() on first use of a device."""
+    dev = _lib.require_cuda(device)
+    if dev.index not in _initialised:
+        with torch.cuda.device(dev):
+            call("gpk_init", _lib.stream_ptr(dev))
+        _initialised.add(dev.index)
+    return dev
+
+
+def shutdown():
+    """Free the per-device library state and the engine's scratch caches (gpk_shutdown per initialised device)."""
+    release_scratch()
+    for idx in list(_initialised):
+        with torch.cuda.device(idx):
+            call("gpk_shutdown")
+    _initialised.clear()
+
+
 class NotPSDError(RuntimeError):
     """K + noise I was not positive definite even after the jitter retries (gpytorch's NotPSDError)."""
 
@@ -199,6 +222,8 @@ class GPFit:
     wimg: torch.Tensor = None  # (digits * npad * npad,) int8 digit image of W for the tcgen05 variance path
     wscale: torch.Tensor = None  # (npad,) power-of-two row scales of the image
     digits: int = 0
+    digits_f32: int = 0        # leading digits multiplied for float32 queries (0: all of them)
+    var_err: dict = field(default_factory=dict)   # probed |var_i8 - var_f64| per digit count (select_digits)
     quad: float = float("nan")
     logdet: float = float("nan")
     jitter: float = 0.0
@@ -251,6 +276,78 @@ def slice_w(W: torch.Tensor, npad: int, digits: int | None = None, wimg_out=None
     return wimg, wscale, digits
 
 
+# Accuracy policy of the int8 variance path.  The S-digit images quantise W = L^-1 (per row, relative to the row
+# maximum) and E = exp(-r^2/2) (absolute) to 8S-2 bits and drop the digit products below 2^-8S, so the ABSOLUTE error
+# of var_f grows with max|W| ~ 1/sqrt(noise) and sqrt(N) while the quantity the reference consumes, the predictive
+# variance var_f + noise (gpmpc/gpmpc.py:444-445), can be as small as the noise.  The digit count is therefore chosen
+# PER FIT by measurement: the int8 path is compared with the FP64 DMMA path on a probe set (training inputs, where
+# ||W k|| and with it the error is largest, plus perturbed copies) and S is the smallest count whose probed error,
+# times a safety factor, stays below rtol * noise -- i.e. 1e-6 (float64 queries) / 1e-4 (float32 queries) ELEMENT-WISE
+# relative on the predictive variance.  If no digit count qualifies (noise <= ~1e-4 with dense data) the fit carries no
+# image and predict() takes the DMMA path (var_path="f64").
+VAR_RTOL_F64 = 1e-6
+VAR_RTOL_F32 = 1e-4
+VAR_PROBE_SAFETY = 2.0
+VAR_PROBE_POINTS = 256
+
+
+def _probe_queries(fit: "GPFit") -> torch.Tensor:
+    """Probe set of select_digits: <= 256 training inputs spread over the set + the same points shifted by a third
+    of a lengthscale in every coordinate (deterministic)."""
+    n = fit.n
+    idx = torch.linspace(0, n - 1, min(n, VAR_PROBE_POINTS), device=fit.device).round().long()
+    Xp = fit.X[idx]
+    shift = (fit.ell.to(fit.device) / 3.0) * (1.0 - 2.0 * (torch.arange(fit.d, device=fit.device) % 2))
+    return torch.cat([Xp, Xp + shift]).contiguous()
+
+
+@_on_arg_device
+def select_digits(fits: list, candidates=(5, 6), wimg_out=None, wscale_out=None) -> int:
+    """Pick ONE digit count for the GPs in `fits` (same npad; a GPBatch shares its image format) by probing, build the
+    images, and record the probed errors in fit.var_err.  Returns the digit count (0: no image, DMMA path)."""
+    npad = fits[0].npad
+    wimg_out = wimg_out or [None] * len(fits)
+    wscale_out = wscale_out or [None] * len(fits)
+    refs = []
+    for f in fits:
+        Zp = _probe_queries(f)
+        saved = (f.wimg, f.wscale, f.digits)
+        f.wimg = f.wscale = None
+        f.digits = 0
+        refs.append((Zp, predict(f, Zp, var_path="f64")[1][0]))
+        f.wimg, f.wscale, f.digits = saved
+    for S in candidates:
+        if not i8_supported(npad, S):
+            continue
+        lib = _lib.load()
+        ok = True
+        errs = []
+        for f, (Zp, v_ref), wo, so in zip(fits, refs, wimg_out, wscale_out):
+            if wo is not None and wo.numel() != lib.gpk_oz_w_image_bytes(npad, S):
+                wo = None                                         # caller's buffer was sized for another digit count
+            f.wimg, f.wscale, f.digits = slice_w(f.W, npad, S, wo, so)
+            f.digits_f32 = 0
+            e = [(predict(f, Zp, want_mean_jac=False)[1][0] - v_ref).abs().max()]
+            if S > 4:
+                e.append((predict(f, Zp, want_mean_jac=False, mul_digits=4)[1][0] - v_ref).abs().max())
+            errs.append(torch.stack(e))
+        errs = torch.stack(errs).tolist()                          # one host round trip per candidate
+        for f, e in zip(fits, errs):
+            f.var_err[S] = e[0]
+            if len(e) > 1:
+                f.var_err[4] = e[1]
+            ok = ok and VAR_PROBE_SAFETY * e[0] <= VAR_RTOL_F64 * f.noise
+        if ok:
+            f32_ok = all(len(e) > 1 and VAR_PROBE_SAFETY * e[1] <= VAR_RTOL_F32 * f.noise for f, e in zip(fits, errs))
+            for f in fits:
+                f.digits_f32 = 4 if f32_ok else 0
+            return S
+    for f in fits:
+        f.wimg = f.wscale = None
+        f.digits = f.digits_f32 = 0
+    return 0
+
+
 def kinv_row_hull(r0: int, r1: int, npad: int) -> tuple[int, int]:
     """128-aligned hull of the row range [r0, r1) inside [0, npad] (the granularity of gpk_kinv_rows)."""
     if r1 <= r0:
@@ -270,7 +367,7 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
     behind gpmpc/gpmpc.py:444 (eval mode).  On a failed pivot the diagonal jitter policy of gpytorch's
     psd_safe_cholesky is applied (1e-8 for float64, x10 per retry, `max_tries` retries).
     """
-    dev = _lib.require_cuda(X.device if X.is_cuda else None)
+    dev = init(X.device if X.is_cuda else None)
     X = _as_device_f64(X, dev)
     y = _as_device_f64(y, dev).reshape(-1)
     n, d = X.shape
@@ -326,13 +423,16 @@ def factorize(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *
         if attempt == max_tries:
             raise NotPSDError(f"K + noise I not positive definite after jitter {jitter:g} (potrf info={info})")
         jitter = 1e-8 if jitter == 0.0 else jitter * 10.0
-    wimg = wscale = None
-    if want_image and i8_supported(npad, digits):
-        wimg, wscale, digits = slice_w(W, npad, digits, wimg_out, wscale_out)
     quad, logdet = ws.scal.tolist()
     fit = GPFit(X=X, y=y, n=n, d=d, npad=npad, center=center_h, ell=ell_t, sf2=float(sf2), noise=float(noise),
                 hyp=make_hyp(center_h, ell_t, sf2, noise, d, dev) if jitter else hyp, W=W, alpha=alpha,
-                quad=quad, logdet=logdet, jitter=jitter, wimg=wimg, wscale=wscale, digits=digits or 0)
+                quad=quad, logdet=logdet, jitter=jitter)
+    if want_image:
+        if digits is None:
+            select_digits([fit], wimg_out=[wimg_out], wscale_out=[wscale_out])
+        elif i8_supported(npad, digits):
+            fit.wimg, fit.wscale, fit.digits = slice_w(W, npad, digits, wimg_out, wscale_out)
+            fit.digits_f32 = min(fit.digits, 4)     # explicit digit count: the caller owns the accuracy decision
     return fit, ws
 
 
@@ -405,6 +505,12 @@ class GPBatch:
     _alpha: torch.Tensor = None   # (B, npad), stacked lazily
 
     @property
+    def digits_f32(self) -> int:
+        """Leading digits multiplied for float32 queries: 4 only if every GP of the batch qualified for it."""
+        d = [f.digits_f32 for f in self.fits]
+        return 0 if (0 in d or not d) else max(d)
+
+    @property
     def alpha(self) -> torch.Tensor:
         if self._alpha is None:
             self._alpha = torch.stack([f.alpha for f in self.fits])
@@ -474,17 +580,26 @@ def fit_batch(X: torch.Tensor, Y: torch.Tensor, ell, sf2, noise, digits: int | N
     npad = round_up(n, TILE)
     Wall = torch.empty(P, npad, npad, dtype=F64, device=dev)
     lib = _lib.load()
-    digits = lib.gpk_oz_default_digits() if digits is None else digits
-    Iall = (torch.empty(P, lib.gpk_oz_w_image_bytes(npad, digits), dtype=torch.int8, device=dev)
-            if i8_supported(npad, digits) else [None] * P)
     ell = torch.as_tensor(ell, dtype=F64)
     fits = []
     for p in range(P):
         ell_p = ell[p] if ell.dim() == 2 else ell
         sf2_p = float(sf2[p]) if hasattr(sf2, "__len__") else float(sf2)
         noise_p = float(noise[p]) if hasattr(noise, "__len__") else float(noise)
-        f, _ = factorize(X, Y[:, p], ell_p, sf2_p, noise_p, W_out=Wall[p], digits=digits, wimg_out=Iall[p])
+        f, _ = factorize(X, Y[:, p], ell_p, sf2_p, noise_p, W_out=Wall[p], want_image=False)
         fits.append(f)
+    # one image format for the batch: explicit digits, or the accuracy policy over all P GPs (select_digits)
+    S0 = lib.gpk_oz_default_digits() if digits is None else digits
+    if i8_supported(npad, S0):
+        Iall = torch.empty(P, lib.gpk_oz_w_image_bytes(npad, S0), dtype=torch.int8, device=dev)
+        if digits is None:
+            select_digits(fits, wimg_out=list(Iall))
+        else:
+            for p, f in enumerate(fits):
+                f.wimg, f.wscale, f.digits = slice_w(f.W, npad, digits, Iall[p])
+                f.digits_f32 = min(digits, 4)
+    elif digits is None:
+        select_digits(fits)
     return GPBatch.from_fits(fits)
 
 
@@ -494,7 +609,7 @@ VAR_WORK_BYTES = 4 << 30   # default scratch budget for the K_ZX chunks of the v
 @_on_arg_device
 def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_work_bytes: int | None = None,
             var_path: str = "i8", mj_event: torch.cuda.Event | None = None, mj_path: str = "auto",
-            want_mean_jac: bool = True):
+            want_mean_jac: bool = True, mul_digits: int | None = None):
     """Posterior mean (B,Q), latent variance var_f (B,Q) and input-Jacobian (B,Q,d) at queries Z.
 
     Z: (Q,d) shared by all GPs or (B,Q,d); float64 or float32 selects the prediction path.  The batched
@@ -504,7 +619,7 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
     if isinstance(gp, GPFit):
         gp = GPBatch.from_fits([gp])
     lib = _lib.load()
-    dev = gp.device
+    dev = init(gp.device)
     assert Z.dtype in DTYPE_CODE, "queries must be float32 or float64"
     dt = Z.dtype
     code = DTYPE_CODE[dt]
@@ -523,8 +638,11 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
     var = torch.empty(B, q, dtype=dt, device=dev) if want_var else None
     if q == 0:
         return mean, var, jac
-    if var_path == "i8" and gp.wimg is None and not i8_supported(npad, gp.digits or None):
-        var_path = "f64"                     # training set too large for exact int32 accumulation
+    if var_path == "i8" and gp.wimg is None:
+        # no digit image: the training set is too large for exact int32 accumulation, or no digit count met the
+        # accuracy policy at this fit's conditioning (select_digits) -> FP64 DMMA path
+        assert gp.W is not None, "fit carries neither a digit image nor W"
+        var_path = "f64"
     if not want_mean_jac and var_path != "i8":
         # variance alone exists on the int8 path only; the DMMA path computes mean and Jacobian on the way
         mean = torch.empty(B, q, dtype=dt, device=dev)
@@ -532,7 +650,10 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
     if want_var and var_path == "i8":
         # fused front end (kernel evaluated once for mean, Jacobian and the digit image) + variance contraction
         # on the tcgen05 int8 pipe (exact digit products, fp64 recombination)
-        assert gp.wimg is not None, "fit without digit image: factorize(..., want_image=True)"
+        if mul_digits is None:               # float32 queries: the leading digits the fit qualified for
+            mul_digits = gp.digits_f32 if dt == torch.float32 else 0
+        if mul_digits >= gp.digits:
+            mul_digits = 0
         budget = VAR_WORK_BYTES if var_work_bytes is None else var_work_bytes
         need = lib.gpk_predict_i8_work_bytes(q, npad, d, gp.digits, B)
         vbytes = max(min(need, budget), lib.gpk_predict_i8_work_bytes(128, npad, d, gp.digits, B))
@@ -542,7 +663,7 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
         call("gpk_predict_i8", code, ptr(Z), Z.stride(-2), q, strideZ, d, ptr(gp.hyp), ptr(gp.X), gp.X.stride(1), n,
              strideX, ptr(alpha), alpha.stride(0), ptr(gp.wimg), gp.wimg.stride(0) if B > 1 else 0, ptr(gp.wscale),
              gp.wscale.stride(0) if B > 1 else 0, npad, gp.digits, ptr(mean), q, ptr(jac), d, q * d, ptr(var), q,
-             ptr(vwork), vbytes, B, mj_event.cuda_event if mj_event is not None else None, st)
+             ptr(vwork), vbytes, B, int(mul_digits), mj_event.cuda_event if mj_event is not None else None, st)
         return mean, var, jac
     if not want_var and dt == F64 and d > 8 and mj_path != "simt":
         # mean + Jacobian alone in float64: the DMMA front kernel without the digit image (1.4x the SIMT kernel at d=16)

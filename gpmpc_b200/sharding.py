@@ -137,7 +137,8 @@ def replicate_batch(batch, src: int = 0, *, device=None, with_W: bool = False, g
                    "img_bytes": int(batch.wimg.shape[1]) if has_img else 0,
                    "with_W": bool(with_W and batch.W is not None),
                    "fits": [{"center": f.center, "ell": f.ell, "sf2": f.sf2, "noise": f.noise, "quad": f.quad,
-                             "logdet": f.logdet, "jitter": f.jitter} for f in batch.fits]}
+                             "logdet": f.logdet, "jitter": f.jitter, "digits_f32": f.digits_f32,
+                             "var_err": dict(f.var_err)} for f in batch.fits]}
         device = batch.device
     dist.broadcast_object_list(meta, src=src, group=group, device=device if device is not None and
                                torch.device(device).type == "cuda" else None)
@@ -165,7 +166,8 @@ def replicate_batch(batch, src: int = 0, *, device=None, with_W: bool = False, g
     fits = [E.GPFit(X=X[p], y=y[p], n=n, d=d, npad=npad, center=fm["center"], ell=fm["ell"], sf2=fm["sf2"],
                     noise=fm["noise"], hyp=hyp[p], W=W[p] if W is not None else None, alpha=alpha[p],
                     wimg=wimg[p] if wimg is not None else None, wscale=wscale[p] if wscale is not None else None,
-                    digits=m["digits"], quad=fm["quad"], logdet=fm["logdet"], jitter=fm["jitter"])
+                    digits=m["digits"], digits_f32=fm["digits_f32"], var_err=fm["var_err"], quad=fm["quad"],
+                    logdet=fm["logdet"], jitter=fm["jitter"])
             for p, fm in enumerate(m["fits"])]
     out = E.GPBatch(fits, X, W, hyp, wimg, wscale, m["digits"])
     out._alpha = alpha

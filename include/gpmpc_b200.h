@@ -4,8 +4,14 @@
  * pointers, explicit sizes / leading dimensions (in elements), an explicit cudaStream_t (passed as
  * void*), and returns int:  0 = ok,  < 0 = bad argument (-1) or CUDA error (-(1000 + cudaError_t));
  * numerical failure of the Cholesky is reported LAPACK-style through the device-side `info` word
- * (first non-positive pivot, 1-based; 0 = ok).  Nothing is allocated, nothing synchronises; scratch is
- * caller-provided.  gpk_last_error() returns the message of the last failing call on this thread.
+ * (first non-positive pivot, 1-based; 0 = ok).  Scratch is caller-provided and no compute entry allocates or
+ * synchronises in steady state.  The exceptions, all one-time per device and all avoidable by calling gpk_init first:
+ * the 8 KB exp table of the prediction front end (cudaMalloc + copy + one stream synchronisation), the library-owned
+ * side stream + event pool of gpk_potrf_trtri, and -- not covered by gpk_init -- the item list of an int8 fit GEMM
+ * the first time its SHAPE is seen on a device (cudaMalloc + copy + one stream synchronisation; a fit of one size
+ * sees about ten shapes, all in its first iteration).  gpk_shutdown frees all of it.  Per-device state is not
+ * thread-safe: one host thread (or process) per GPU, calls on one stream at a time (SURVEY.md 8b "Threading").
+ * gpk_last_error() returns the message of the last failing call on this thread.
  *
  * The reference has no FFI of its own: its GP layer is Python over gpytorch/torch.  Each
  * entry below names the reference call site (file:line under the gp-mpc tree) whose library work it
@@ -30,7 +36,9 @@ extern "C" {
 #endif
 
 /* ---- library info ------------------------------------------------------------------------- */
-int gpk_abi_version(void);
+int gpk_abi_version(void);              /* 2 */
+int gpk_init(void* stream);             /* create the current device's library state up front (see above); idempotent */
+int gpk_shutdown(void);                 /* free it (device-synchronising); the library stays usable */
 const char* gpk_last_error(void);
 long gpk_launch_count(void);            /* kernels launched by this library since load / last reset */
 void gpk_reset_launch_count(void);
@@ -157,7 +165,10 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
                    const double* X, long ldx, long n, long strideX, const double* alpha, long stride_alpha,
                    const void* Wimg, long strideW, const double* wscale, long stride_ws, long npad, int digits,
                    void* mean, long stride_mean, void* jac, long ldj, long stride_jac, void* var, long stride_var,
-                   void* work, long work_bytes, int batch, void* mj_done_event, void* stream);
+                   void* work, long work_bytes, int batch, int mul_digits, void* mj_done_event, void* stream);
+/* mul_digits: 0 = multiply all `digits` digits of the image; 4 <= mul_digits < digits multiplies only the leading
+ * mul_digits digits of both operands (fewer digit products, coarser variance: the caller's accuracy policy decides,
+ * nothing is cut implicitly by dtype). */
 /* mean + Jacobian alone on the same DMMA front kernel (no digit image, no variance): the want_var = false path in
  * float64 for d >= 9, where it is faster than the SIMT kernel of (6).  Takes X and alpha directly (no pack). */
 long gpk_mean_jac_dmma_work_bytes(long q_chunk, int d, int batch);

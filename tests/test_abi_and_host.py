@@ -19,7 +19,7 @@ def test_library_exports_every_declared_symbol():
     lib = _lib.load()           # raises if a declared symbol is not exported
     for name in declared:
         assert hasattr(lib, name)
-    assert lib.gpk_abi_version() == 1
+    assert lib.gpk_abi_version() == 2
     # size queries do no GPU work
     assert lib.gpk_pad_dim(1) == 1 and lib.gpk_pad_dim(5) == 8 and lib.gpk_pad_dim(16) == 16 and lib.gpk_pad_dim(33) == -1
     assert lib.gpk_hyp_stride() == 72

@@ -354,4 +354,4 @@ def test_variance_paths_agree(n, d, q, monkeypatch):
     m2, v2, j2 = E.predict(fit2, Z)
     assert torch.equal(v2[0].cpu(), v_f64)
     monkeypatch.undo()
-    assert E.i8_supported(26112) and not E.i8_supported(26240) and E.i8_supported(26240, 4) and not E.i8_supported(32768, 4)
+    assert E.i8_supported(32768) and not E.i8_supported(33024) and E.i8_supported(43904, 4) and not E.i8_supported(26496, 6)
