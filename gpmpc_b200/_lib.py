@@ -35,6 +35,9 @@ SIGNATURES = {
     "gpk_kinv": (_i, [_p, _l, _l, _p, _l, _p]),
     "gpk_kinv_rows": (_i, [_p, _l, _l, _l, _l, _l, _p, _l, _p]),
     "gpk_solve_alpha": (_i, [_p, _l, _p, _l, _p, _l, _l, _p, _p, _p, _p, _p]),
+    "gpk_mll_small_max_n": (_i, []),
+    "gpk_mll_small_out_stride": (_i, []),
+    "gpk_mll_small": (_i, [_p, _l, _l, _p, _l, _l, _i, _p, _p, _p, _l, _i, _p]),
     "gpk_grad_trace_work_elems": (_l, [_l, _i, _l, _l]),
     "gpk_mll_grad_reduce": (_i, [_p, _l, _l, _i, _p, _p, _l, _p, _l, _l, _p, _l, _p, _p]),
     "gpk_mll_grad_reduce_sym": (_i, [_p, _l, _l, _i, _p, _p, _l, _p, _l, _l, _p, _l, _p, _p]),

@@ -641,16 +641,24 @@ static int oz_launch_var(const OzArgs& a, cudaStream_t st) {
     return 0;
 }
 
-// splits of the training range per query tile: the power of two (<= 16, <= k blocks) that wastes the least in
-// the last wave of CTAs (one 256-thread CTA per SM)
+// splits of the training range per query tile (<= 16, <= k blocks).  Two 256-thread CTAs are resident per SM, so the
+// grid runs in waves of 2 x SMs CTAs; a CTA costs its k blocks plus a fixed part (exp table into shared memory, query
+// fragments, partial-sum stores: about 1.5 k blocks of time).  Picks the count that minimises waves x CTA cost:
+// few large CTAs when the tiles alone fill the waves, more splits only when they buy a fuller last wave.
 static int oz_front_splits(long qtiles_total, int kb_total) {
+    if (const char* e = getenv("GPK_OZ_FRONT_SPLITS")) {
+        const int ns = atoi(e);
+        if (ns >= 1 && ns <= 16 && ns <= kb_total) return ns;
+    }
+    const long slots = 2L * oz_sm_count();
     int best = 1;
-    double best_waste = 1e30;
-    for (int ns = 1; ns <= 16 && ns <= kb_total; ns *= 2) {
+    double best_cost = 1e30;
+    for (int ns = 1; ns <= 16 && ns <= kb_total; ns++) {
         const long ctas = qtiles_total * ns;
-        const long waves = (ctas + oz_sm_count() - 1) / oz_sm_count();
-        const double waste = (double)(waves * oz_sm_count()) / (double)ctas + 0.004 * ns;
-        if (waste < best_waste) { best_waste = waste; best = ns; }
+        const long waves = (ctas + slots - 1) / slots;
+        const int kb_per_cta = (kb_total + ns - 1) / ns;
+        const double cost = (double)waves * (kb_per_cta + 1.5);
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = ns; }
     }
     return best;
 }

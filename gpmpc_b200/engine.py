@@ -289,6 +289,9 @@ VAR_RTOL_F64 = 1e-6
 VAR_RTOL_F32 = 1e-4
 VAR_PROBE_SAFETY = 2.0
 VAR_PROBE_POINTS = 256
+# below this padded size (N <= 128: the reference's own shapes, N <= 45) the policy builds no image at all: one
+# 128-tile of DMMA work is as fast as the tensor-pipe path and the probing would dominate the fit
+VAR_IMAGE_MIN_NPAD = 256
 
 
 def _probe_queries(fit: "GPFit") -> torch.Tensor:
@@ -306,6 +309,8 @@ def select_digits(fits: list, candidates=(5, 6), wimg_out=None, wscale_out=None)
     """Pick ONE digit count for the GPs in `fits` (same npad; a GPBatch shares its image format) by probing, build the
     images, and record the probed errors in fit.var_err.  Returns the digit count (0: no image, DMMA path)."""
     npad = fits[0].npad
+    if npad < VAR_IMAGE_MIN_NPAD:
+        return 0
     wimg_out = wimg_out or [None] * len(fits)
     wscale_out = wscale_out or [None] * len(fits)
     refs = []
@@ -464,6 +469,42 @@ def loss_and_grad_from_partials(fit: GPFit, partials: torch.Tensor):
     g_sf2 = -(0.5 * p[1] / fit.sf2) / n
     g_ell = [-(0.5 * p[2 + j] / float(fit.ell[j])) / n for j in range(fit.d)]
     return loss, g_noise, g_sf2, g_ell
+
+
+@_on_arg_device
+def small_loss_and_grad(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *, center=None,
+                        max_tries: int = 3):
+    """loss = -MLL/N and d loss / d (noise, sf2, ell_j) for ONE small GP (N <= 128) in one launch and one host round
+    trip (gpk_mll_small): what fit_gp's iteration needs at the reference's own sizes (gpmpc/gp.py:59-63, N <= 45).
+    Same jitter policy as factorize().  Returns (loss, g_noise, g_sf2, g_ell, jitter)."""
+    lib = _lib.load()
+    dev = init(X.device if X.is_cuda else None)
+    X = _as_device_f64(X, dev)
+    y = _as_device_f64(y, dev).reshape(-1)
+    n, d = X.shape
+    assert n <= lib.gpk_mll_small_max_n(), "small_loss_and_grad handles N <= 128"
+    ell_t = torch.as_tensor(ell, dtype=F64).reshape(-1).cpu()
+    if ell_t.numel() == 1:
+        ell_t = ell_t.expand(d).clone()
+    center_h = torch.as_tensor(X.mean(dim=0) if center is None else center, dtype=F64).reshape(-1).cpu()
+    out = torch.empty(lib.gpk_mll_small_out_stride(), dtype=F64, device=dev)
+    jitter = 0.0
+    for attempt in range(max_tries + 1):
+        hyp = make_hyp(center_h, ell_t, sf2, noise + jitter, d, dev)
+        call("gpk_mll_small", ptr(X), X.stride(0), 0, ptr(y), 0, n, d, ptr(hyp), ptr(out), None, 0, 1,
+             _lib.stream_ptr(dev))
+        o = out.tolist()                    # the one host round trip of the iteration
+        if int(o[0]) == 0:
+            break
+        if attempt == max_tries:
+            raise NotPSDError(f"K + noise I not positive definite after jitter {jitter:g} (potrf info={int(o[0])})")
+        jitter = 1e-8 if jitter == 0.0 else jitter * 10.0
+    quad, logdet, p = o[1], o[2], o[4:]
+    loss = 0.5 * (quad + logdet + n * LOG_2PI) / n
+    g_noise = -(0.5 * p[0]) / n
+    g_sf2 = -(0.5 * p[1] / float(sf2)) / n
+    g_ell = [-(0.5 * p[2 + j] / float(ell_t[j])) / n for j in range(d)]
+    return loss, g_noise, g_sf2, g_ell, jitter
 
 
 @_on_arg_device
@@ -638,7 +679,7 @@ def predict(gp: GPBatch | GPFit, Z: torch.Tensor, *, want_var: bool = True, var_
     var = torch.empty(B, q, dtype=dt, device=dev) if want_var else None
     if q == 0:
         return mean, var, jac
-    if var_path == "i8" and gp.wimg is None:
+    if want_var and var_path == "i8" and gp.wimg is None:
         # no digit image: the training set is too large for exact int32 accumulation, or no digit count met the
         # accuracy policy at this fit's conditioning (select_digits) -> FP64 DMMA path
         assert gp.W is not None, "fit carries neither a digit image nor W"

@@ -30,6 +30,7 @@ except ImportError:  # pragma: no cover - casadi is absent in the build image
     cs = None
 
 NOISE_LOWER_BOUND = 1e-6  # GreaterThan(1e-6), gpmpc/gp.py:31
+SMALL_FIT_MAX_N = 128     # fit_gp iterations of GPs up to this size run as ONE fused kernel (engine.small_loss_and_grad)
 
 
 def _need_casadi():
@@ -348,15 +349,20 @@ def _loss_and_set_grads(gp: GaussianProcess, dev: torch.device, W_buf: torch.Ten
         Xd = X.detach().to(dev, torch.float64).contiguous()
         cache = gp._fit_cache = (X, Xd, gp.train_targets.detach().to(dev, torch.float64).contiguous(), Xd.mean(dim=0).cpu(),
                                  gp.train_targets)
-    # a row-split reducer (sharding.RowSplitGradReduce) names the rows of K^-1 this rank needs; everyone else gets all
-    want_kinv = grad_reduce.rows(gp.n_ind_points) if hasattr(grad_reduce, "rows") else True
-    fit, ws = E.factorize(cache[1], cache[2], ell, sf2, noise, center=cache[3], want_kinv=want_kinv, W_out=W_buf,
-                          want_image=False)
-    if grad_reduce is None:
-        partials = E.grad_partials(fit, ws)
+    fit = None
+    if grad_reduce is None and gp.n_ind_points <= SMALL_FIT_MAX_N:
+        # the reference's own sizes (N <= 45): the whole iteration is one launch and one host round trip
+        loss, g_noise, g_sf2, g_ell, _ = E.small_loss_and_grad(cache[1], cache[2], ell, sf2, noise, center=cache[3])
     else:
-        partials = grad_reduce(fit, ws)    # sharding layer: row-split + all-reduce
-    loss, g_noise, g_sf2, g_ell = E.loss_and_grad_from_partials(fit, partials)
+        # a row-split reducer (sharding.RowSplitGradReduce) names the rows of K^-1 this rank needs; everyone else gets all
+        want_kinv = grad_reduce.rows(gp.n_ind_points) if hasattr(grad_reduce, "rows") else True
+        fit, ws = E.factorize(cache[1], cache[2], ell, sf2, noise, center=cache[3], want_kinv=want_kinv, W_out=W_buf,
+                              want_image=False)
+        if grad_reduce is None:
+            partials = E.grad_partials(fit, ws)
+        else:
+            partials = grad_reduce(fit, ws)    # sharding layer: row-split + all-reduce
+        loss, g_noise, g_sf2, g_ell = E.loss_and_grad_from_partials(fit, partials)
     rn = gp.likelihood.noise_covar.raw_noise
     rs = gp.covar_module.raw_outputscale
     rl = gp.covar_module.base_kernel.raw_lengthscale
@@ -387,7 +393,8 @@ def fit_gp(gp: GaussianProcess, n_train=500, lr=0.01, device: str = "cpu", *, co
     gp.train().to(device)
     optim = torch.optim.Adam(gp.parameters(), lr=lr)
     npad = E.round_up(gp.n_ind_points, E.TILE)
-    W_buf = torch.empty(npad, npad, dtype=torch.float64, device=dev)
+    small = grad_reduce is None and gp.n_ind_points <= SMALL_FIT_MAX_N
+    W_buf = None if small else torch.empty(npad, npad, dtype=torch.float64, device=dev)
     last_loss = math.inf
     gp.fit_losses = []
     for _ in range(n_train):

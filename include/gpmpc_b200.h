@@ -91,6 +91,19 @@ int gpk_solve_alpha(const double* W, long ldw, const double* U, long ldu, const 
                     long npad, const double* y, double* t_work, double* alpha, double* scal,
                     void* stream);
 
+/* ---- (2-5 fused) one-launch MLL + gradient for small GPs -------------------------------------------
+ * The whole iteration of gpmpc/gp.py:59-63 (assembly, Cholesky, alpha, y^T K^-1 y, log det K, K^-1, gradient trace)
+ * for n <= gpk_mll_small_max_n() = 128 training points -- the reference's own sizes, N <= 45
+ * (scripts/gp_mpc_config.yaml:24,30) -- by ONE CTA per GP out of shared memory; `batch` GPs of identical (n, d) run
+ * concurrently (the three GPs gpmpc/gpmpc.py:159-162 fits one after the other).
+ *   out[gp][0] = potrf info (first non-positive pivot, 1-based; 0 = ok), [1] = y^T K^-1 y, [2] = log det K,
+ *   out[gp][4 + v] = the gpk_pad_dim(d) + 2 sums of gpk_mll_grad_reduce; stride gpk_mll_small_out_stride() doubles.
+ *   alpha (may be NULL) receives K^-1 y, n entries per GP. */
+int gpk_mll_small_max_n(void);
+int gpk_mll_small_out_stride(void);
+int gpk_mll_small(const double* X, long ldx, long strideX, const double* y, long stride_y, long n, int d,
+                  const double* hyp, double* out, double* alpha, long stride_alpha, int batch, void* stream);
+
 /* ---- (5) MLL gradient trace reduction --------------------------------------------------------
  * With G = alpha alpha^T - K^-1, over rows [r0, r1) and all columns < n:
  *   out[0] = sum G_aa, out[1] = sum G_ab K_f,ab, out[2+j] = sum G_ab K_f,ab ((x_aj - x_bj)/ell_j)^2.

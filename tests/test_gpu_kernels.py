@@ -189,3 +189,48 @@ def test_mll_gradient_matches_oracle(n, d, ard):
     assert abs(gn - float(gn_ref)) < TOL64 * max(abs(float(gn_ref)), 1e-3)
     assert abs(gs - float(gs_ref)) < TOL64 * max(abs(float(gs_ref)), 1e-3)
     assert o.rel_err(gl, gl_ref) < TOL64
+
+
+@pytest.mark.parametrize("n,d", [(15, 1), (30, 3), (45, 3), (100, 16), (128, 5)])
+def test_fused_small_mll_matches_blocked_path_and_oracle(n, d):
+    """gpk_mll_small (one CTA per GP, one launch per Adam iteration at the reference's sizes) against the blocked
+    factorize + grad_partials path and the oracle's closed-form gradient; batch of three GPs in one launch."""
+    from gpmpc_b200 import engine as E
+    from gpmpc_b200._lib import call, ptr
+
+    p = o.synthetic_problem(n, d, 1, p=3, seed=7 * n + d)
+    X, Y = p["X"], p["Y"]
+    g = torch.Generator().manual_seed(n)
+    rn = torch.randn(1, generator=g, dtype=torch.float64) - 2.0
+    rs = torch.randn((), generator=g, dtype=torch.float64)
+    rl = torch.randn(1, d, generator=g, dtype=torch.float64) + 1.0
+    noise, sf2, ell = o.constrained(rn, rs, rl)
+    ell = ell.reshape(-1)
+    Xd, Yd = X.to(_dev()), Y.to(_dev())
+    loss, g_noise, g_sf2, g_ell, jit = E.small_loss_and_grad(Xd, Yd[:, 0], ell, float(sf2), float(noise))
+    fit, ws = E.factorize(Xd, Yd[:, 0], ell, float(sf2), float(noise), want_kinv=True, want_image=False)
+    l2, gn2, gs2, ge2 = E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
+    assert jit == 0.0 and abs(loss - l2) < 1e-10 * abs(l2)
+    assert abs(g_noise - gn2) < 1e-8 * max(abs(gn2), 1e-3) and abs(g_sf2 - gs2) < 1e-8 * max(abs(gs2), 1e-3)
+    assert o.rel_err(torch.tensor(g_ell), torch.tensor(ge2)) < 1e-8
+    lo, gno, gso, glo = o.loss_and_grad(X, Y[:, 0], rn, rs, rl)
+    assert abs(loss - float(lo)) < 1e-6 * abs(float(lo))
+    assert abs(g_noise * float(torch.sigmoid(rn)) - float(gno)) < 1e-6 * max(abs(float(gno)), 1e-3)
+    assert o.rel_err(torch.tensor(g_ell).reshape(1, -1) * torch.sigmoid(rl), glo) < 1e-6
+    # three GPs in one launch straight through the C ABI, with alpha
+    lib = _lib().load()
+    hyp = torch.stack([E.make_hyp(X.mean(0), ell, float(sf2), float(noise), d, _dev())] * 3)
+    Yt = Yd.T.contiguous()
+    out = torch.empty(3, lib.gpk_mll_small_out_stride(), dtype=torch.float64, device=_dev())
+    alpha = torch.empty(3, n, dtype=torch.float64, device=_dev())
+    call("gpk_mll_small", ptr(Xd), Xd.stride(0), 0, ptr(Yt), Yt.stride(0), n, d, ptr(hyp), ptr(out), ptr(alpha), n, 3,
+         torch.cuda.current_stream().cuda_stream)
+    for k in range(3):
+        st = o.fit_state(X, Y[:, k], ell, sf2, noise)
+        assert o.rel_err(alpha[k].cpu(), st["alpha"]) < 1e-8
+        assert abs(float(out[k, 1]) - float(st["quad"])) < 1e-9 * abs(float(st["quad"]))
+        assert abs(float(out[k, 2]) - float(st["logdet"])) < 1e-9 * max(abs(float(st["logdet"])), 1.0)
+    assert abs(float(out[0, 1]) - fit.quad) < 1e-10 * abs(fit.quad)
+    # not positive definite -> info > 0 surfaces as NotPSDError after the jitter retries
+    with pytest.raises(E.NotPSDError):
+        E.small_loss_and_grad(Xd, Yd[:, 0], ell, float(sf2), -0.5)
