@@ -526,6 +526,8 @@ def measure_roofline(gb, Z, ctx, steps):
     peak = 2.0 * (bf16 or FALLBACK_BF16_TFLOPS)
     dmma_peak = peaks.get("dmma_tflops_bps8", 37.1)
     prof = f"ncu_oz_var_kernel_S{S}_r02_n{n}.csv"
+    if not os.path.exists(os.path.join(ROOT, "profiles", prof)) and n == 2048 and S == 5:
+        prof = "ncu_oz_var_kernel_S5_r01_v6.csv"        # same kernel, same shape, captured in round 1
     out = {"kernel": f"oz_var_kernel<{S}> (variance contraction W K_ZX^T, {S}-digit int8 slices on tcgen05, int32 TMEM "
                      "accumulators, fp64 recombination)",
            "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
@@ -856,6 +858,16 @@ def measure_single_gpu_extras(ctx, gb, workload):
         pairs = npreds * n_train / (msj * 1e-3)
         mj[name] = {"preds_per_s": npreds / (msj * 1e-3), "pairs_per_s": pairs, "tflops_at_68_per_pair": pairs * 68e-12,
                     "pipe_peak_tflops": pk, "frac": pairs * 68e-12 / pk}
+    # the same at config 5's per-stage batch (Q = 65536): enough CTAs to fill the waves, per-CTA set-up amortised
+    pz = make_problem(n_train, 65536)["Z"].to(dev)
+    for name, zz, pk in (("f64_q65536", pz, peaks.get("dmma_tflops_bps8", 37.1)), ("f32_q65536", pz.float(), peaks.get("ffma_tflops_bps8", 72.5))):
+        for _ in range(3):
+            E.predict(gb, zz, want_var=False)
+        msj = timed_steps(lambda: E.predict(gb, zz, want_var=False), 10, flush, dev) / 10
+        pairs = N_GP * 65536 * n_train / (msj * 1e-3)
+        mj[name] = {"preds_per_s": N_GP * 65536 / (msj * 1e-3), "pairs_per_s": pairs, "tflops_at_68_per_pair": pairs * 68e-12,
+                    "pipe_peak_tflops": pk, "frac": pairs * 68e-12 / pk}
+    del pz
     out["mean_jac_only"] = mj
     out.update(measure_mpc_rows(gb, problem, flush, dev))
     out.update(measure_config1(ctx))

@@ -95,26 +95,27 @@ __device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_sr
                  : "memory");
 }
 
-// exp(a) for a <= 0 to ~2^-51 relative error, branch-free, 10 FP64 operations: a log2(e) 1024 = m + f with
+// exp(a) for a <~ 0 to ~2^-50 relative error, branch-free, 9 FP64 operations: a log2(e) 1024 = m + f with
 // m = 1024 n + j, so exp(a) = 2^n * T[j] * exp(r), T[j] = 2^(j/1024) from a shared-memory table, r = a - m ln2/1024
-// (Cody-Waite, |r| <= 3.4e-4) and a degree-4 polynomial; 2^n goes straight into the exponent field (normal
-// results down to a = -708; below that the result is 0, where the library exp is subnormal or 0).
+// (Cody-Waite, |r| <= 3.4e-4: the cubic's truncation error r^4/24 is 5.6e-16) evaluated as T + (T r)(1 + r/2 + r^2/6);
+// 2^n goes straight into the exponent field.  Results below 2^-1021 are flushed to 0 by an integer compare (where
+// the library exp is subnormal or 0); arguments a few ulps above 0 (rounding of -r^2/2) are fine.
 constexpr int EXP_TAB = 1024;
 __device__ __forceinline__ double exp_neg_tab(double a0, const double* __restrict__ tab) {
-    const double a = fmax(a0, -708.0);
+    const double a = fmax(a0, -745.0);                   // keeps m inside int32 for any input, NaN-free
     const double MAGIC = 6755399441055744.0;             // 1.5 * 2^52
     const double tm = fma(a, 1477.3197218702985, MAGIC); // 1024 / ln 2
     const double md = tm - MAGIC;
-    double r = fma(md, -0.0006769015433292225, a);  // ln2/1024 hi (32 significant bits: exact products)
-    r = fma(md, -1.8634911418658083e-13, r);            // ln2/1024 lo
-    double p = fma(r, 4.16666666666666666667e-02, 1.66666666666666666667e-01);
-    p = fma(p, r, 0.5);
-    p = fma(p, r, 1.0);
-    p = fma(p, r, 1.0);
-    const int m = __double2loint(tm);                     // integer part of tm sits in the low mantissa word
-    p *= tab[m & (EXP_TAB - 1)];
-    const double e = __hiloint2double(__double2hiint(p) + ((m >> 10) << 20), __double2loint(p));
-    return a0 < -708.0 ? 0.0 : e;
+    double r = fma(md, -0.0006769015433292225, a);       // ln2/1024 hi (32 significant bits: exact products)
+    r = fma(md, -1.8634911418658083e-13, r);             // ln2/1024 lo
+    const int m = __double2loint(tm);                    // integer part of tm sits in the low mantissa word
+    const double T = tab[m & (EXP_TAB - 1)];
+    double q = fma(r, 1.66666666666666666667e-01, 0.5);
+    q = fma(q, r, 1.0);
+    const double p = fma(T * r, q, T);
+    const int n = m >> 10;
+    const double e = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+    return n < -1021 ? 0.0 : e;
 }
 // the table in device memory (built by gpk_init, or lazily on first use; defined in ozaki.cu)
 const double* exp_table(cudaStream_t st);

@@ -173,9 +173,21 @@ struct MeanJacArgs {
 };
 
 constexpr int MJ_THREADS = 128;
+// tuning hooks (A/B builds) of the float32 d = 16 kernel: resident CTAs per SM it is compiled for, queries per thread,
+// inner unroll.  Measured on B200 (tools/time_mj_variants.py, N = 2048): (1 CTA, 2 queries, unroll 2) 422 / 601 G pairs/s
+// at Q = 8192 / 65536, (4, 1, 4) 460 / 640: one query per thread at 120 registers keeps 16 warps per SM resident
+#ifndef MJ_F32_MINB
+#define MJ_F32_MINB 4
+#endif
+#ifndef MJ_F32_RQ
+#define MJ_F32_RQ 1
+#endif
+#ifndef MJ_UNROLL
+#define MJ_UNROLL 4
+#endif
 
 template <typename T, int DP, int RQ>
-__global__ void __launch_bounds__(MJ_THREADS)
+__global__ void __launch_bounds__(MJ_THREADS, (sizeof(T) == 4 && DP == 16) ? MJ_F32_MINB : 1)
 mean_jac_kernel(const MeanJacArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int TILE_ELEMS = TP * (DP + 2);
@@ -250,7 +262,8 @@ mean_jac_kernel(const MeanJacArgs a) {
         const T* xs = buf + cur * TILE_ELEMS;
         const T* es = xs + TP * DP;
         const T* as = es + TP;
-#pragma unroll 2
+        constexpr int UNR = (sizeof(T) == 4 && DP == 16) ? MJ_UNROLL : 2;
+#pragma unroll UNR
         for (int i = 0; i < TP; i++) {
             T x[DP];
             load_row<T, DP>(xs + i * DP, x);
@@ -378,7 +391,7 @@ static int launch_mean_jac(const MeanJacArgs& a, int dp, int batch, cudaStream_t
         case 3: return launch_mean_jac_t<T, 3, RQ>(a, batch, st);
         case 4: return launch_mean_jac_t<T, 4, RQ>(a, batch, st);
         case 8: return launch_mean_jac_t<T, 8, RQ>(a, batch, st);
-        case 16: return launch_mean_jac_t<T, 16, RQ>(a, batch, st);
+        case 16: return launch_mean_jac_t<T, 16, sizeof(T) == 4 ? MJ_F32_RQ : 1>(a, batch, st);
         case 32: return launch_mean_jac_t<T, 32, 1>(a, batch, st);
         default: return fail(-1, "mean_jac: unsupported padded dimension %d", dp);
     }
@@ -601,7 +614,7 @@ int gpk_predict_mean_jac(int dtype, const void* Z, long ldz, long q, long stride
     a.n_tiles = (int)((n + TP - 1) / TP);
     a.mean = mean; a.stride_mean = stride_mean; a.jac = jac; a.ldj = ldj; a.stride_jac = stride_jac;
     // split the training set over CTAs when the query count alone cannot fill the machine (~2 waves)
-    const long per_block = MJ_THREADS * (dtype == 0 && dp < 32 ? 2 : 1);
+    const long per_block = MJ_THREADS * (dtype == 0 ? (dp < 16 ? 2 : dp == 16 ? MJ_F32_RQ : 1) : 1);
     const long qblocks = (q + per_block - 1) / per_block * batch;
     int n_split = (int)((148L * 8 + qblocks - 1) / qblocks);
     if (n_split > a.n_tiles) n_split = a.n_tiles;

@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
                 }
                 double e[4];
 #pragma unroll
-                for (int i = 0; i < 4; i++) e[i] = qv[mb] ? exp_neg_tab(fmin(c[i >> 1][i & 1], 0.0), exp_tab) : 0.0;
+                for (int i = 0; i < 4; i++) e[i] = qv[mb] ? exp_neg_tab(c[i >> 1][i & 1], exp_tab) : 0.0;
                 if (write_img) {
                     uint32_t w[S];
                     oz_pack_digits4<S>(e, w);
