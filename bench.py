@@ -613,11 +613,17 @@ def measure_fit_configs(ctx, n_big: int = 32768):
             fit, ws = E.factorize(Xn, yn, ell, 1.0, 1e-2, want_kinv=True, want_image=False)
             return E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
 
-        ms, res, clk = timed_iters(it, 20 if n <= 4096 else 3, ctx)
+        ms_plain, res, clk = timed_iters(it, 20 if n <= 4096 else 3, ctx)
+        # the same iteration replayed as a CUDA graph (what fit_gp does from its third iteration on)
+        gm = E.GraphedMLL(Xn, yn)
+        for _ in range(E.GRAPH_FIT_WARMUP + 1):
+            gm(ell, 1.0, 1e-2)
+        ms, res_g, clk = timed_iters(lambda: gm(ell, 1.0, 1e-2), 20 if n <= 4096 else 3, ctx)
         mll["points"].append({"n": n, "value": 1e3 / ms, "ms_per_iter": ms, "tflops_of_n3": float(n) ** 3 / ms * 1e-9,
-                              "frac_of_fp64_dmma_peak": float(n) ** 3 / ms * 1e-9 / dmma_peak, "loss": res[0],
-                              "sm_mhz": clk.get("sm_mhz")})
-        del Xn, yn
+                              "frac_of_fp64_dmma_peak": float(n) ** 3 / ms * 1e-9 / dmma_peak, "loss": res_g[0],
+                              "path": "CUDA graph replay (engine.GraphedMLL)", "stream_launch_ms_per_iter": ms_plain,
+                              "loss_stream_launch": res[0], "sm_mhz": clk.get("sm_mhz")})
+        del Xn, yn, gm
         E.release_scratch()
 
     # (a) one GP per rank (different targets per rank): no collective
@@ -921,7 +927,8 @@ def measure_config1(ctx):
         n_it = 0
         for p in range(3):
             gp = G.GaussianProcess(Xs[p], Y[:, p].contiguous())
-            G.fit_gp(gp, n_train=500, lr=1e-3, device=str(ctx.dev))
+            G.fit_gp(gp, n_train=500, lr=1e-3, device="cpu")    # gp_mpc_config.yaml:19 device: "cpu" (tensors stay on the
+                                                                # host, the arithmetic runs on the current CUDA device)
             n_it += len(gp.fit_losses)
         return n_it, gp
 
@@ -931,7 +938,7 @@ def measure_config1(ctx):
     iters, gp = gpu_fit()
     torch.cuda.synchronize()
     t_gpu = time.perf_counter() - t0
-    gp2 = G.GaussianProcess(Xs[1].to(ctx.dev), y1.to(ctx.dev)).to(ctx.dev)
+    gp2 = G.GaussianProcess(Xs[1], y1)
     gp2.train()
     opt = torch.optim.Adam(gp2.parameters(), lr=1e-3)
     for _ in range(5):
@@ -945,7 +952,7 @@ def measure_config1(ctx):
         gp2._invalidate()
     torch.cuda.synchronize()
     gpu_iter_ms = (time.perf_counter() - t0) / 200 * 1e3
-    z = (torch.rand(25, 3, generator=g, dtype=torch.float64) - 0.5).to(ctx.dev)
+    z = torch.rand(25, 3, generator=g, dtype=torch.float64) - 0.5
     gp.eval()
     torch.diag(gp.likelihood(gp(z)).covariance_matrix).cpu()      # first call builds the prediction state
     t0 = time.perf_counter()

@@ -30,6 +30,7 @@ except ImportError:  # pragma: no cover - casadi is absent in the build image
     cs = None
 
 NOISE_LOWER_BOUND = 1e-6  # GreaterThan(1e-6), gpmpc/gp.py:31
+USE_FIT_GRAPH = True      # fit_gp iterations at N >= engine.GRAPH_FIT_MIN_N replay a CUDA graph (engine.GraphedMLL)
 SMALL_FIT_MAX_N = 128     # fit_gp iterations of GPs up to this size run as ONE fused kernel (engine.small_loss_and_grad)
 
 
@@ -353,6 +354,12 @@ def _loss_and_set_grads(gp: GaussianProcess, dev: torch.device, W_buf: torch.Ten
     if grad_reduce is None and gp.n_ind_points <= SMALL_FIT_MAX_N:
         # the reference's own sizes (N <= 45): the whole iteration is one launch and one host round trip
         loss, g_noise, g_sf2, g_ell, _ = E.small_loss_and_grad(cache[1], cache[2], ell, sf2, noise, center=cache[3])
+    elif grad_reduce is None and gp.n_ind_points >= E.GRAPH_FIT_MIN_N and USE_FIT_GRAPH:
+        # mid / large N: the iteration's ~170+ launches on two streams replayed as one CUDA graph
+        graphed = getattr(gp, "_fit_graph", None)
+        if graphed is None or graphed.key is not cache[1]:
+            graphed = gp._fit_graph = E.GraphedMLL(cache[1], cache[2], center=cache[3])
+        loss, g_noise, g_sf2, g_ell, _ = graphed(ell, sf2, noise)
     else:
         # a row-split reducer (sharding.RowSplitGradReduce) names the rows of K^-1 this rank needs; everyone else gets all
         want_kinv = grad_reduce.rows(gp.n_ind_points) if hasattr(grad_reduce, "rows") else True
@@ -393,7 +400,8 @@ def fit_gp(gp: GaussianProcess, n_train=500, lr=0.01, device: str = "cpu", *, co
     gp.train().to(device)
     optim = torch.optim.Adam(gp.parameters(), lr=lr)
     npad = E.round_up(gp.n_ind_points, E.TILE)
-    small = grad_reduce is None and gp.n_ind_points <= SMALL_FIT_MAX_N
+    small = grad_reduce is None and (gp.n_ind_points <= SMALL_FIT_MAX_N or
+                                     (USE_FIT_GRAPH and gp.n_ind_points >= E.GRAPH_FIT_MIN_N))
     W_buf = None if small else torch.empty(npad, npad, dtype=torch.float64, device=dev)
     last_loss = math.inf
     gp.fit_losses = []
@@ -408,6 +416,7 @@ def fit_gp(gp: GaussianProcess, n_train=500, lr=0.01, device: str = "cpu", *, co
         last_loss = loss
     del W_buf
     gp._fit_cache = None
+    gp._fit_graph = None
     if compute_covariances:
         gp.K, gp.K_inv = gp.compute_covariances()
 

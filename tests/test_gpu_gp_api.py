@@ -355,3 +355,31 @@ def test_variance_paths_agree(n, d, q, monkeypatch):
     assert torch.equal(v2[0].cpu(), v_f64)
     monkeypatch.undo()
     assert E.i8_supported(32768) and not E.i8_supported(33024) and E.i8_supported(43904, 4) and not E.i8_supported(26496, 6)
+
+
+@pytest.mark.parametrize("n", [600, 1500])
+def test_graphed_mll_iteration_is_bit_identical_and_fit_gp_uses_it(n):
+    """engine.GraphedMLL: the MLL + gradient iteration replayed as a CUDA graph gives the same numbers as the stream
+    launches, survives changing hyper-parameters and a non-PD request; fit_gp follows the oracle loop with it."""
+    from gpmpc_b200 import engine as E
+    from gpmpc_b200.gp import GaussianProcess, fit_gp
+
+    dev = torch.device("cuda", 0)
+    p = o.synthetic_problem(n, 5, 1, p=1, seed=n)
+    X, y = p["X"].to(dev), p["Y"][:, 0].to(dev)
+    gm = E.GraphedMLL(X, y)
+    for k, (ell, sf2, noise) in enumerate([(1.0, 1.0, 1e-2), (0.8, 1.3, 3e-2), (1.4, 0.7, 5e-3), (0.9, 1.1, 2e-2)]):
+        ell_t = torch.full((5,), ell, dtype=torch.float64)
+        got = gm(ell_t, sf2, noise)
+        fit, ws = E.factorize(X, y, ell_t, sf2, noise, center=gm.center, want_kinv=True, want_image=False)
+        ref = E.loss_and_grad_from_partials(fit, E.grad_partials(fit, ws))
+        assert (gm.graph is not None) == (k >= E.GRAPH_FIT_WARMUP)
+        assert got[0] == ref[0] and got[1] == ref[1] and got[2] == ref[2] and got[3] == ref[3], k
+    with pytest.raises(E.NotPSDError):
+        gm(torch.full((5,), 1.0, dtype=torch.float64), 1.0, -0.5)
+    Xs, ys = p["X"][:520], p["Y"][:520, 0]
+    gp = GaussianProcess(Xs, ys)
+    fit_gp(gp, n_train=8, lr=0.05, device="cuda:0", compute_covariances=False)
+    ref = o.fit_hyperparameters(Xs, ys, n_train=8, lr=0.05)
+    assert len(gp.fit_losses) == len(ref["losses"])
+    assert o.rel_err(torch.tensor(gp.fit_losses), torch.tensor(ref["losses"])) < 1e-5
