@@ -37,7 +37,7 @@ SIGNATURES = {
     "gpk_solve_alpha": (_i, [_p, _l, _p, _l, _p, _l, _l, _p, _p, _p, _p, _p]),
     "gpk_mll_small_max_n": (_i, []),
     "gpk_mll_small_out_stride": (_i, []),
-    "gpk_mll_small": (_i, [_p, _l, _l, _p, _l, _l, _i, _p, _p, _p, _l, _i, _p]),
+    "gpk_mll_small": (_i, [_p, _l, _l, _p, _l, _l, _i, _p, _p, _p, _l, _p, _p, _l, _l, _i, _p]),
     "gpk_grad_trace_work_elems": (_l, [_l, _i, _l, _l]),
     "gpk_mll_grad_reduce": (_i, [_p, _l, _l, _i, _p, _p, _l, _p, _l, _l, _p, _l, _p, _p]),
     "gpk_mll_grad_reduce_sym": (_i, [_p, _l, _l, _i, _p, _p, _l, _p, _l, _l, _p, _l, _p, _p]),

@@ -28,6 +28,7 @@ struct SmallArgs {
     int n, d, dp;
     double* out;                               // [batch][SM_OUT]
     double* alpha; long stride_alpha;          // optional [batch][n]
+    double* K; double* Kinv; long ldk, strideK; // optional dense [batch][n][ldk] outputs: K_f + noise I and its inverse
 };
 
 __global__ void __launch_bounds__(SM_THREADS, 1) mll_small_kernel(const SmallArgs a) {
@@ -62,7 +63,12 @@ __global__ void __launch_bounds__(SM_THREADS, 1) mll_small_kernel(const SmallArg
                 const double df = Xs[i * d + k] - Xs[j * d + k];
                 r2 = fma(df, df, r2);
             }
-            Lp[tri(i, j)] = i == j ? sf2 + noise : sf2 * exp(-0.5 * r2);
+            const double kv = i == j ? sf2 + noise : sf2 * exp(-0.5 * r2);
+            Lp[tri(i, j)] = kv;
+            if (a.K) {
+                a.K[gp * a.strideK + (long)i * a.ldk + j] = kv;
+                a.K[gp * a.strideK + (long)j * a.ldk + i] = kv;
+            }
         }
     __syncthreads();
     // ---- Cholesky, right-looking, in place; one column per step --------------------------------------
@@ -126,6 +132,10 @@ __global__ void __launch_bounds__(SM_THREADS, 1) mll_small_kernel(const SmallArg
         for (int j = lane; j <= i; j += 32) {
             double kinv = 0.0;
             for (int r = i; r < n; r++) kinv = fma(Wp[tri(r, i)], Wp[tri(r, j)], kinv);
+            if (a.Kinv) {
+                a.Kinv[gp * a.strideK + (long)i * a.ldk + j] = kinv;
+                a.Kinv[gp * a.strideK + (long)j * a.ldk + i] = kinv;
+            }
             const double g = ys[i] * ys[j] - kinv;
             double r2 = 0.0;
             for (int k = 0; k < d; k++) {
@@ -180,12 +190,16 @@ int gpk_mll_small_out_stride(void) { return SM_OUT; }
 
 // out[gp][0] = potrf info (first non-positive pivot, 1-based, 0 = ok), [1] = y^T K^-1 y, [2] = log det K,
 // [4 + v] = the d + 2 gradient sums of gpk_mll_grad_reduce (padded to gpk_pad_dim(d) + 2 entries).  alpha (optional)
-// receives K^-1 y.  One CTA per GP; n <= gpk_mll_small_max_n(), 1 <= d <= 32.
+// receives K^-1 y; K / Kinv (optional, both or neither) receive the dense n x n matrices K_f + noise I and its inverse
+// (gp.K, gp.K_inv of gpmpc/gp.py:43-46), row stride ldk, GP stride strideK.  One CTA per GP; n <= gpk_mll_small_max_n().
 int gpk_mll_small(const double* X, long ldx, long strideX, const double* y, long stride_y, long n, int d, const double* hyp,
-                  double* out, double* alpha, long stride_alpha, int batch, void* stream) {
+                  double* out, double* alpha, long stride_alpha, double* K, double* Kinv, long ldk, long strideK,
+                  int batch, void* stream) {
     GPK_ARG(X && y && hyp && out, "null pointer");
     GPK_ARG(n >= 1 && n <= SM_MAXN && d >= 1 && d <= HYP_MAXD && ldx >= d && batch >= 1, "n / d / ldx / batch");
+    GPK_ARG((K == nullptr) == (Kinv == nullptr) && (K == nullptr || ldk >= n), "K and Kinv go together, ldk >= n");
     SmallArgs a{};
+    a.K = K; a.Kinv = Kinv; a.ldk = ldk; a.strideK = strideK;
     a.X = X; a.ldx = ldx; a.strideX = strideX; a.y = y; a.stride_y = stride_y; a.hyp = hyp;
     a.n = (int)n; a.d = d; a.dp = small_pad_dim(d); a.out = out; a.alpha = alpha; a.stride_alpha = stride_alpha;
     const int ntri = (int)(n * (n + 1) / 2);

@@ -169,17 +169,29 @@ class FitScratch:
 _scratch_cache: dict = {}
 
 
+SCRATCH_KEEP_BYTES = 2 << 30     # several fit-scratch sizes stay cached per device while they total less than this
+
+
+def _scratch_bytes(npad: int) -> int:
+    return 4 * npad * npad * 8       # L, U, K^-1, T/gemm images: order of magnitude
+
+
 def get_fit_scratch(npad: int, device: torch.device) -> FitScratch:
+    """Fit scratch of one padded size on one device, reused across GPs and MLL iterations.  Small sizes are kept side
+    by side (a FITC set-up alternates between M inducing points and N training points); a size is evicted (oldest
+    first) only when the cached scratch of the device would exceed SCRATCH_KEEP_BYTES -- the big configs need the
+    memory back.  Single-stream contract: the scratch is keyed by device, not by stream (include/gpmpc_b200.h)."""
     key = (npad, device.index, int(FIT_GEMM_DIGITS), int(FIT_GEMM_MIN_NPAD))
-    if key not in _scratch_cache:
-        # keep at most one size per device alive: the big configs need the memory back
-        for k in [k for k in _scratch_cache if k[1] == device.index]:
-            with torch.cuda.device(device):
-                _register_fit_gemm_workspace(None)
-            del _scratch_cache[k]
-        _scratch_cache[key] = FitScratch(npad, device)
-        _scratch_cache[key].activate()
-    return _scratch_cache[key]
+    ws = _scratch_cache.pop(key, None)
+    if ws is None:
+        budget = SCRATCH_KEEP_BYTES - _scratch_bytes(npad)
+        mine = [k for k in _scratch_cache if k[1] == device.index]
+        while mine and sum(_scratch_bytes(k[0]) for k in mine) > max(budget, 0):
+            del _scratch_cache[mine.pop(0)]          # dict order = least recently used first
+        ws = FitScratch(npad, device)
+    _scratch_cache[key] = ws                          # most recently used last
+    ws.activate()                                     # the library's GEMM dispatcher follows the scratch in use
+    return ws
 
 
 def release_scratch():
@@ -590,10 +602,11 @@ class GraphedMLL:
 
 @_on_arg_device
 def small_loss_and_grad(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise: float, *, center=None,
-                        max_tries: int = 3):
+                        max_tries: int = 3, covariances: dict | None = None):
     """loss = -MLL/N and d loss / d (noise, sf2, ell_j) for ONE small GP (N <= 128) in one launch and one host round
     trip (gpk_mll_small): what fit_gp's iteration needs at the reference's own sizes (gpmpc/gp.py:59-63, N <= 45).
-    Same jitter policy as factorize().  Returns (loss, g_noise, g_sf2, g_ell, jitter)."""
+    Same jitter policy as factorize().  Returns (loss, g_noise, g_sf2, g_ell, jitter); a dict passed as `covariances`
+    receives the dense K = K_f + noise I and K^-1 (device tensors) of the same launch."""
     lib = _lib.load()
     dev = init(X.device if X.is_cuda else None)
     X = _as_device_f64(X, dev)
@@ -608,14 +621,20 @@ def small_loss_and_grad(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise
     jitter = 0.0
     for attempt in range(max_tries + 1):
         hyp = make_hyp(center_h, ell_t, sf2, noise + jitter, d, dev)
-        call("gpk_mll_small", ptr(X), X.stride(0), 0, ptr(y), 0, n, d, ptr(hyp), ptr(out), None, 0, 1,
-             _lib.stream_ptr(dev))
+        K = Kinv = None
+        if covariances is not None:         # gp.K, gp.K_inv from the same launch (compute_covariances, gpmpc/gp.py:43-46)
+            K = torch.empty(n, n, dtype=F64, device=dev)
+            Kinv = torch.empty(n, n, dtype=F64, device=dev)
+        call("gpk_mll_small", ptr(X), X.stride(0), 0, ptr(y), 0, n, d, ptr(hyp), ptr(out), None, 0, ptr(K), ptr(Kinv), n, 0,
+             1, _lib.stream_ptr(dev))
         o = out.tolist()                    # the one host round trip of the iteration
         if int(o[0]) == 0:
             break
         if attempt == max_tries:
             raise NotPSDError(f"K + noise I not positive definite after jitter {jitter:g} (potrf info={int(o[0])})")
         jitter = 1e-8 if jitter == 0.0 else jitter * 10.0
+    if covariances is not None:
+        covariances["K"], covariances["K_inv"] = K, Kinv
     quad, logdet, p = o[1], o[2], o[4:]
     loss = 0.5 * (quad + logdet + n * LOG_2PI) / n
     g_noise = -(0.5 * p[0]) / n

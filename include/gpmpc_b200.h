@@ -98,11 +98,13 @@ int gpk_solve_alpha(const double* W, long ldw, const double* U, long ldu, const 
  * concurrently (the three GPs gpmpc/gpmpc.py:159-162 fits one after the other).
  *   out[gp][0] = potrf info (first non-positive pivot, 1-based; 0 = ok), [1] = y^T K^-1 y, [2] = log det K,
  *   out[gp][4 + v] = the gpk_pad_dim(d) + 2 sums of gpk_mll_grad_reduce; stride gpk_mll_small_out_stride() doubles.
- *   alpha (may be NULL) receives K^-1 y, n entries per GP. */
+ *   alpha (may be NULL) receives K^-1 y, n entries per GP.  K / Kinv (both or neither) receive the dense n x n
+ *   matrices K_f + noise I and its inverse -- gp.K, gp.K_inv of compute_covariances, gpmpc/gp.py:43-46. */
 int gpk_mll_small_max_n(void);
 int gpk_mll_small_out_stride(void);
 int gpk_mll_small(const double* X, long ldx, long strideX, const double* y, long stride_y, long n, int d,
-                  const double* hyp, double* out, double* alpha, long stride_alpha, int batch, void* stream);
+                  const double* hyp, double* out, double* alpha, long stride_alpha, double* K, double* Kinv,
+                  long ldk, long strideK, int batch, void* stream);
 
 /* ---- (5) MLL gradient trace reduction --------------------------------------------------------
  * With G = alpha alpha^T - K^-1, over rows [r0, r1) and all columns < n:

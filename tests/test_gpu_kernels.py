@@ -223,8 +223,12 @@ def test_fused_small_mll_matches_blocked_path_and_oracle(n, d):
     Yt = Yd.T.contiguous()
     out = torch.empty(3, lib.gpk_mll_small_out_stride(), dtype=torch.float64, device=_dev())
     alpha = torch.empty(3, n, dtype=torch.float64, device=_dev())
-    call("gpk_mll_small", ptr(Xd), Xd.stride(0), 0, ptr(Yt), Yt.stride(0), n, d, ptr(hyp), ptr(out), ptr(alpha), n, 3,
-         torch.cuda.current_stream().cuda_stream)
+    Kd = torch.empty(3, n, n, dtype=torch.float64, device=_dev())
+    Kinv = torch.empty(3, n, n, dtype=torch.float64, device=_dev())
+    call("gpk_mll_small", ptr(Xd), Xd.stride(0), 0, ptr(Yt), Yt.stride(0), n, d, ptr(hyp), ptr(out), ptr(alpha), n,
+         ptr(Kd), ptr(Kinv), n, n * n, 3, torch.cuda.current_stream().cuda_stream)
+    K_ref = o.assemble_K(X, ell, sf2, noise)
+    assert o.rel_err(Kd[2].cpu(), K_ref) < 1e-13 and o.rel_err(Kinv[1].cpu(), torch.linalg.inv(K_ref)) < 1e-7
     for k in range(3):
         st = o.fit_state(X, Y[:, k], ell, sf2, noise)
         assert o.rel_err(alpha[k].cpu(), st["alpha"]) < 1e-8
