@@ -9,5 +9,9 @@ from .gp import (  # noqa: F401
     covSE_single,
     covSE_vectorized,
     fit_gp,
+    gp_casadi_callback,
     gpytorch_predict2casadi,
+    predict_batch,
+    predict_callable,
+    predict_host,
 )

@@ -361,8 +361,39 @@ __global__ void mean_jac_finalize_kernel(const MeanJacArgs a) {
         }
 }
 
+// Split of the training tiles over CTAs.  The grid runs in waves of (SMs x resident CTAs) -- the resident count comes
+// from the occupancy API for this instantiation -- and a CTA costs its tiles plus about half a tile of set-up (queries,
+// first TMA round trip, partial-sum stores): pick the split count that minimises waves x CTA cost.  (Config 2 in
+// float32: 192 query blocks, 592 slots, 8 tiles -> 3 splits of 3 tiles fill ONE wave; the old "about two waves of
+// CTAs" rule took 4 splits = 1.3 waves.)
 template <typename T, int DP, int RQ>
-static int launch_mean_jac_t(MeanJacArgs a, int batch, cudaStream_t st) {
+static int mj_pick_split(long qblocks, int n_tiles, long q, int batch, const void* work, long work_bytes) {
+    constexpr int smem = 2 * TP * (DP + 2) * (int)sizeof(T);
+    static int resident_dev[64] = {};
+    int& resident = resident_dev[current_device()];
+    if (resident == 0) {
+        int nb = 0, sms = 148;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, mean_jac_kernel<T, DP, RQ>, MJ_THREADS, smem);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, current_device());
+        resident = (nb > 0 ? nb : 1) * (sms > 0 ? sms : 148);
+    }
+    int best = 1;
+    double best_cost = 1e30;
+    for (int ns = 1; ns <= n_tiles && ns <= 64; ns++) {
+        const int tps = (n_tiles + ns - 1) / ns;
+        const int real_ns = (n_tiles + tps - 1) / tps;
+        if (real_ns != ns) continue;                               // same split as a smaller count
+        const long need = (long)ns * q * (DP + 1) * (long)sizeof(T) * batch;
+        if (ns > 1 && (work == nullptr || work_bytes < need)) break;
+        const long waves = (qblocks * ns + resident - 1) / resident;
+        const double cost = (double)waves * (tps + 0.5);
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = ns; }
+    }
+    return best;
+}
+
+template <typename T, int DP, int RQ>
+static int launch_mean_jac_t(MeanJacArgs a, int batch, long work_bytes, cudaStream_t st) {
     constexpr int smem = 2 * TP * (DP + 2) * (int)sizeof(T);
     static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
     bool& attr_done = attr_dev[current_device()];
@@ -371,7 +402,12 @@ static int launch_mean_jac_t(MeanJacArgs a, int batch, cudaStream_t st) {
         attr_done = true;
     }
     const long per_block = (long)MJ_THREADS * RQ;
-    dim3 grid((unsigned)((a.q + per_block - 1) / per_block), (unsigned)a.n_split, (unsigned)batch);
+    const long qblocks_1 = (a.q + per_block - 1) / per_block;
+    const int n_split = mj_pick_split<T, DP, RQ>(qblocks_1 * batch, a.n_tiles, a.q, batch, a.work, work_bytes);
+    a.tiles_per_split = (a.n_tiles + n_split - 1) / n_split;
+    a.n_split = (a.n_tiles + a.tiles_per_split - 1) / a.tiles_per_split;
+    a.stride_work = (long)a.n_split * a.q * (DP + 1);
+    dim3 grid((unsigned)qblocks_1, (unsigned)a.n_split, (unsigned)batch);
     mean_jac_kernel<T, DP, RQ><<<grid, MJ_THREADS, smem, st>>>(a);
     GPK_LAUNCHED();
     if (a.n_split > 1) {
@@ -383,16 +419,16 @@ static int launch_mean_jac_t(MeanJacArgs a, int batch, cudaStream_t st) {
 }
 
 template <typename T>
-static int launch_mean_jac(const MeanJacArgs& a, int dp, int batch, cudaStream_t st) {
+static int launch_mean_jac(const MeanJacArgs& a, int dp, int batch, long work_bytes, cudaStream_t st) {
     constexpr int RQ = sizeof(T) == 4 ? 2 : 1;
     switch (dp) {
-        case 1: return launch_mean_jac_t<T, 1, RQ>(a, batch, st);
-        case 2: return launch_mean_jac_t<T, 2, RQ>(a, batch, st);
-        case 3: return launch_mean_jac_t<T, 3, RQ>(a, batch, st);
-        case 4: return launch_mean_jac_t<T, 4, RQ>(a, batch, st);
-        case 8: return launch_mean_jac_t<T, 8, RQ>(a, batch, st);
-        case 16: return launch_mean_jac_t<T, 16, sizeof(T) == 4 ? MJ_F32_RQ : 1>(a, batch, st);
-        case 32: return launch_mean_jac_t<T, 32, 1>(a, batch, st);
+        case 1: return launch_mean_jac_t<T, 1, RQ>(a, batch, work_bytes, st);
+        case 2: return launch_mean_jac_t<T, 2, RQ>(a, batch, work_bytes, st);
+        case 3: return launch_mean_jac_t<T, 3, RQ>(a, batch, work_bytes, st);
+        case 4: return launch_mean_jac_t<T, 4, RQ>(a, batch, work_bytes, st);
+        case 8: return launch_mean_jac_t<T, 8, RQ>(a, batch, work_bytes, st);
+        case 16: return launch_mean_jac_t<T, 16, sizeof(T) == 4 ? MJ_F32_RQ : 1>(a, batch, work_bytes, st);
+        case 32: return launch_mean_jac_t<T, 32, 1>(a, batch, work_bytes, st);
         default: return fail(-1, "mean_jac: unsupported padded dimension %d", dp);
     }
 }
@@ -613,22 +649,9 @@ int gpk_predict_mean_jac(int dtype, const void* Z, long ldz, long q, long stride
     }
     a.n_tiles = (int)((n + TP - 1) / TP);
     a.mean = mean; a.stride_mean = stride_mean; a.jac = jac; a.ldj = ldj; a.stride_jac = stride_jac;
-    // split the training set over CTAs when the query count alone cannot fill the machine (~2 waves)
-    const long per_block = MJ_THREADS * (dtype == 0 ? (dp < 16 ? 2 : dp == 16 ? MJ_F32_RQ : 1) : 1);
-    const long qblocks = (q + per_block - 1) / per_block * batch;
-    int n_split = (int)((148L * 8 + qblocks - 1) / qblocks);
-    if (n_split > a.n_tiles) n_split = a.n_tiles;
-    if (n_split < 1) n_split = 1;
-    const long need = (long)n_split * q * (dp + 1) * esz * batch;
-    if (n_split > 1 && (work == nullptr || work_bytes < need)) {
-        n_split = 1;   // caller gave no scratch: fall back to one CTA row per query block
-    }
-    a.tiles_per_split = (a.n_tiles + n_split - 1) / n_split;
-    a.n_split = (a.n_tiles + a.tiles_per_split - 1) / a.tiles_per_split;
-    a.work = work;
-    a.stride_work = (long)a.n_split * q * (dp + 1);
-    if (dtype == 0) return launch_mean_jac<float>(a, dp, batch, (cudaStream_t)stream);
-    return launch_mean_jac<double>(a, dp, batch, (cudaStream_t)stream);
+    a.work = work;       // the split of the training tiles over CTAs is chosen per kernel instantiation (mj_pick_split)
+    if (dtype == 0) return launch_mean_jac<float>(a, dp, batch, work_bytes, (cudaStream_t)stream);
+    return launch_mean_jac<double>(a, dp, batch, work_bytes, (cudaStream_t)stream);
 }
 
 int gpk_var_finalize(int dtype, const double* colsq, long ld, long stride_colsq, int tiles_m, long q,

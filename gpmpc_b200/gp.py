@@ -462,6 +462,63 @@ def predict_callable(gp: GaussianProcess):
     return pred
 
 
+def gp_casadi_callback(gp: GaussianProcess, name: str = "pred_gpu"):
+    """CasADi bridge: a `casadi.Callback` z (d,) -> mean (1,) whose value AND Jacobian come from
+    the fused CUDA mean + Jacobian kernel, so that a CasADi graph (an NLP solved with ipopt / sqpmethod, or
+    `cs.Function`s evaluated in Python) can use the GPU posterior in place of the symbolic `pred` of
+    gpytorch_predict2casadi (gpmpc/gp.py:72-85, called at gpmpc/gpmpc.py:189-191).  Needs casadi.
+
+    Scope note: acados generates C from the symbolic expression graph of `AcadosModel.disc_dyn_expr`; a Callback has
+    no C source, so the acados OCP of `setup_acados_model` keeps using the symbolic export (or gets its stage
+    linearisations from mpc.StageDynamics directly).  The Callback serves CasADi-side consumers."""
+    _need_casadi()
+    d = gp.input_dimension
+    pred = predict_callable(gp)
+
+    class _GPJacobian(cs.Callback):
+        """Jacobian function in CasADi's convention: inputs (z, mean), output d mean / d z (1, d)."""
+
+        def __init__(self, cname):
+            cs.Callback.__init__(self)
+            self.construct(cname, {})
+
+        def get_n_in(self): return 2
+        def get_n_out(self): return 1
+        def get_sparsity_in(self, i): return cs.Sparsity.dense(d, 1) if i == 0 else cs.Sparsity.dense(1, 1)
+        def get_sparsity_out(self, i): return cs.Sparsity.dense(1, d)
+
+        def eval(self, arg):
+            import numpy as np
+            z = np.asarray(arg[0], dtype=np.float64).reshape(-1)
+            return [pred(z)["jac"].reshape(1, d)]
+
+    class _GPMean(cs.Callback):
+        def __init__(self, cname):
+            cs.Callback.__init__(self)
+            self._jac = None
+            self.construct(cname, {"enable_fd": False})
+
+        def get_n_in(self): return 1
+        def get_n_out(self): return 1
+        def get_name_in(self, i): return "z"
+        def get_name_out(self, i): return "mean"
+        def get_sparsity_in(self, i): return cs.Sparsity.dense(d, 1)
+        def get_sparsity_out(self, i): return cs.Sparsity.dense(1, 1)
+
+        def eval(self, arg):
+            import numpy as np
+            z = np.asarray(arg[0], dtype=np.float64).reshape(-1)
+            return [np.asarray(pred(z)["mean"]).reshape(1, 1)]
+
+        def has_jacobian(self): return True
+
+        def get_jacobian(self, jname, inames, onames, opts):
+            self._jac = _GPJacobian(jname)       # kept alive by the owning callback, as CasADi requires
+            return self._jac
+
+    return _GPMean(name)
+
+
 _copy_streams: dict = {}
 
 

@@ -133,3 +133,45 @@ class Function:
             return res
         out = [res[n] for n in self.out_names]
         return out[0] if len(out) == 1 else out
+
+
+class Sparsity:
+    """Only the dense pattern is needed by the Callback bridge: a (rows, cols) shape."""
+
+    def __init__(self, n, m):
+        self.shape = (n, m)
+
+    @staticmethod
+    def dense(n, m=1):
+        return Sparsity(n, m)
+
+
+class Callback:
+    """casadi.Callback's protocol as far as gpmpc_b200.gp.gp_casadi_callback uses it: construct(name, opts) finalises,
+    calling the object evaluates `eval` on numeric inputs shaped by get_sparsity_in, `jacobian()` returns the Function
+    get_jacobian builds (CasADi calls it with the nominal inputs followed by the nominal outputs)."""
+
+    def __init__(self):
+        self._name = None
+
+    def construct(self, name, opts=None):
+        self._name, self._opts = name, dict(opts or {})
+
+    def name(self):
+        return self._name
+
+    def __call__(self, *args, **kw):
+        n_in = self.get_n_in()
+        if kw:
+            names = [self.get_name_in(i) if hasattr(self, "get_name_in") else f"i{i}" for i in range(n_in)]
+            args = [kw[n] for n in names]
+        vals = [np.asarray(a, dtype=np.float64).reshape(self.get_sparsity_in(i).shape) for i, a in enumerate(args)]
+        out = [np.asarray(o, dtype=np.float64).reshape(self.get_sparsity_out(i).shape) for i, o in enumerate(self.eval(vals))]
+        if kw:
+            onames = [self.get_name_out(i) if hasattr(self, "get_name_out") else f"o{i}" for i in range(len(out))]
+            return dict(zip(onames, out))
+        return out[0] if len(out) == 1 else out
+
+    def jacobian(self):
+        assert self.has_jacobian()
+        return self.get_jacobian("jac_" + self._name, None, None, {})

@@ -75,3 +75,29 @@ def test_repo_casadi_export_matches_reference_export(monkeypatch):
     # the CasADi-free callable serves the same mean
     call = G.predict_callable(gp)
     assert np.abs(call(g["Z"])["mean"] - g["mean"]).max() / np.abs(g["mean"]).max() < 1e-9
+
+
+def test_casadi_callback_bridge_serves_mean_and_jacobian(monkeypatch):
+    """gp_casadi_callback over the shim's Callback protocol: value == the reference's exported mean,
+    Jacobian == the oracle's analytic input-Jacobian (what CasADi AD of gp.py:12-14, 85 yields)."""
+    import casadi_shim
+    from gpmpc_b200 import gp as G
+    from oracle import gp_oracle as o
+
+    monkeypatch.setattr(G, "cs", casadi_shim)
+    g = np.load(os.path.join(GOLD, "pred_d3_n45.npz"))
+    X, y = torch.from_numpy(g["X"]), torch.from_numpy(g["y"])
+    ell, sf2, noise = torch.from_numpy(g["ell"]).reshape(-1), float(g["sf2"]), float(g["noise"])
+    gp = G.GaussianProcess(X, y).double()
+    gp.set_hyperparameters(ell, sf2, noise)
+    gp.eval()
+    cb = G.gp_casadi_callback(gp)
+    assert cb.name() == "pred_gpu" and cb.get_n_in() == 1 and cb.has_jacobian()
+    jac_fn = cb.jacobian()
+    st = o.fit_state(X, y, ell.expand(3), sf2, noise)
+    _, _, j_ref = o.predict(torch.from_numpy(g["Z"]), X, ell.expand(3), sf2, st["L"], st["alpha"])
+    for i, z in enumerate(g["Z"][:8]):
+        m = float(cb(z=z)["mean"].reshape(-1)[0])
+        assert abs(m - g["mean"][i]) < 1e-9 * np.abs(g["mean"]).max()
+        J = jac_fn(z, m)
+        assert J.shape == (1, 3) and np.abs(J.reshape(-1) - j_ref[i].numpy()).max() < 1e-8 * float(j_ref.abs().max())
