@@ -9,6 +9,7 @@ from .gp import (  # noqa: F401
     covSE_single,
     covSE_vectorized,
     fit_gp,
+    fit_gps,
     gp_casadi_callback,
     gpytorch_predict2casadi,
     predict_batch,

@@ -644,6 +644,45 @@ def small_loss_and_grad(X: torch.Tensor, y: torch.Tensor, ell, sf2: float, noise
 
 
 @_on_arg_device
+def small_batch_loss_and_grad(Xpad: torch.Tensor, Y: torch.Tensor, centers: torch.Tensor, ells: list, sf2s: list,
+                              noises: list, covariances: dict | None = None):
+    """small_loss_and_grad for B small GPs of the same N in ONE launch (gpk_mll_small, one CTA per GP): the reference's
+    thrust / roll / pitch GPs (gpmpc/gpmpc.py:159-162 fits them one after the other).  Xpad (B, n, dp): inputs zero-padded
+    to a common dimension (a zero column with lengthscale 1 leaves every kernel value unchanged); ells[b] has the GP's own
+    d_b entries.  Returns a list of (loss, g_noise, g_sf2, g_ell[:d_b], info); info > 0 = that GP's K was not positive
+    definite (the caller retries it alone, with jitter).  `covariances` receives K, K_inv as (B, n, n) device tensors."""
+    lib = _lib.load()
+    dev = init(Xpad.device)
+    B, n, dp = Xpad.shape
+    assert n <= lib.gpk_mll_small_max_n() and Y.shape == (B, n)
+    stride = lib.gpk_hyp_stride()
+    h = torch.zeros(B, stride, dtype=F64)
+    for b in range(B):
+        e = torch.ones(dp, dtype=F64)
+        e[: len(ells[b])] = torch.as_tensor(ells[b], dtype=F64).reshape(-1)
+        h[b] = make_hyp_host(centers[b], e, sf2s[b], noises[b], dp)
+    hyp = h.to(dev)
+    so = lib.gpk_mll_small_out_stride()
+    out = torch.empty(B, so, dtype=F64, device=dev)
+    K = Kinv = None
+    if covariances is not None:
+        K = torch.empty(B, n, n, dtype=F64, device=dev)
+        Kinv = torch.empty(B, n, n, dtype=F64, device=dev)
+    call("gpk_mll_small", ptr(Xpad), Xpad.stride(1), Xpad.stride(0), ptr(Y), Y.stride(0), n, dp, ptr(hyp), ptr(out), None, 0,
+         ptr(K), ptr(Kinv), n, n * n, B, _lib.stream_ptr(dev))
+    o = out.tolist()                        # the one host round trip for all B GPs
+    if covariances is not None:
+        covariances["K"], covariances["K_inv"] = K, Kinv
+    res = []
+    for b in range(B):
+        quad, logdet, p = o[b][1], o[b][2], o[b][4:]
+        d_b = len(ells[b])
+        res.append((0.5 * (quad + logdet + n * LOG_2PI) / n, -(0.5 * p[0]) / n, -(0.5 * p[1] / float(sf2s[b])) / n,
+                    [-(0.5 * p[2 + j] / float(ells[b][j])) / n for j in range(d_b)], int(o[b][0])))
+    return res
+
+
+@_on_arg_device
 def dense_K(fit: GPFit) -> torch.Tensor:
     """K_f(X,X) + noise I as a dense (N,N) tensor (gpmpc/gp.py:45)."""
     n, npad = fit.n, round_up(fit.n, 64)

@@ -429,6 +429,85 @@ def fit_gp(gp: GaussianProcess, n_train=500, lr=0.01, device: str = "cpu", *, co
         gp.K, gp.K_inv = gp.compute_covariances()
 
 
+def _set_raw_grads(gp: GaussianProcess, g_noise: float, g_sf2: float, g_ell: list):
+    """Chain rule through softplus onto the raw parameters' .grad (closed form instead of loss.backward(), gp.py:63)."""
+    rn = gp.likelihood.noise_covar.raw_noise
+    rs = gp.covar_module.raw_outputscale
+    rl = gp.covar_module.base_kernel.raw_lengthscale
+    with torch.no_grad():
+        g_ell_t = torch.tensor(g_ell, dtype=torch.float64)
+        g_ell_t = g_ell_t.sum().reshape(1, 1) if rl.shape[1] == 1 else g_ell_t.reshape(1, -1)
+        rn.grad = (g_noise * torch.sigmoid(rn.detach().double())).to(rn.dtype).reshape(rn.shape).to(rn.device)
+        rs.grad = (g_sf2 * torch.sigmoid(rs.detach().double())).to(rs.dtype).reshape(rs.shape).to(rs.device)
+        rl.grad = (g_ell_t.to(rl.device) * torch.sigmoid(rl.detach().double())).to(rl.dtype)
+
+
+def fit_gps(gps: list, n_train=500, lr=0.01, device: str = "cpu", *, compute_covariances: bool = True):
+    """fit_gp for several small GPs AT ONCE (no reference counterpart: gpmpc/gpmpc.py:159-162 calls fit_gp for its three
+    GPs one after the other).  Every GP keeps its own Adam state and its own early stop (|delta loss| < 1e-3, gp.py:65), so
+    the result equals three fit_gp calls; per iteration ALL GPs are evaluated by one launch and one host round trip
+    (engine.small_batch_loss_and_grad).  Needs the same number of training points N <= 128 in every GP (the reference
+    draws the same samples for all three); anything else falls back to fit_gp per GP."""
+    assert all(isinstance(gp, GaussianProcess) for gp in gps), "gps must be GaussianProcess objects"
+    n = gps[0].n_ind_points
+    if len(gps) < 2 or n > SMALL_FIT_MAX_N or any(gp.n_ind_points != n for gp in gps):
+        for gp in gps:
+            fit_gp(gp, n_train=n_train, lr=lr, device=device, compute_covariances=compute_covariances)
+        return
+    dev = E._lib.require_cuda(device if "cuda" in str(device) else None)
+    B, dp = len(gps), max(gp.input_dimension for gp in gps)
+    Xpad = torch.zeros(B, n, dp, dtype=torch.float64, device=dev)
+    Y = torch.empty(B, n, dtype=torch.float64, device=dev)
+    for b, gp in enumerate(gps):
+        gp.train_inputs = (gp.train_inputs[0].to(device),)
+        gp.train_targets = gp.train_targets.to(device)
+        gp.train().to(device)
+        Xpad[b, :, : gp.input_dimension] = gp.train_inputs[0].to(dev, torch.float64)
+        Y[b] = gp.train_targets.to(dev, torch.float64)
+        gp.fit_losses = []
+    centers = Xpad.mean(dim=1).cpu()
+    optims = [torch.optim.Adam(gp.parameters(), lr=lr) for gp in gps]
+    last = [math.inf] * B
+    active = [True] * B
+
+    def evaluate(cov=None):
+        hp = [gp.hyperparameters() for gp in gps]
+        res = E.small_batch_loss_and_grad(Xpad, Y, centers, [h[0] for h in hp], [h[1] for h in hp], [h[2] for h in hp],
+                                          covariances=cov)
+        for b, r in enumerate(res):
+            if r[4] != 0:       # not positive definite: this GP alone, with the jitter retries
+                ell, sf2, noise = hp[b]
+                res[b] = (*E.small_loss_and_grad(Xpad[b, :, : gps[b].input_dimension].contiguous(), Y[b], ell, sf2, noise)[:4], -1)
+        return res
+
+    for _ in range(n_train):
+        if not any(active):
+            break
+        res = evaluate()
+        for b, gp in enumerate(gps):
+            if not active[b]:
+                continue
+            loss, g_noise, g_sf2, g_ell, _ = res[b]
+            optims[b].zero_grad()
+            _set_raw_grads(gp, g_noise, g_sf2, g_ell)
+            optims[b].step()
+            gp._invalidate()
+            gp.fit_losses.append(loss)
+            if abs(last[b] - loss) < 1e-3:          # early stopping if converged (gpmpc/gp.py:65)
+                active[b] = False
+            last[b] = loss
+    if compute_covariances:
+        cov = {}
+        res = evaluate(cov)
+        for b, gp in enumerate(gps):
+            if res[b][4] == 0:
+                x = gp.train_inputs[0]
+                K, K_inv = cov["K"][b].clone(), cov["K_inv"][b].clone()
+                gp.K, gp.K_inv = (K, K_inv) if x.is_cuda else (K.to(x.device), K_inv.to(x.device))
+            else:
+                gp.K, gp.K_inv = gp.compute_covariances()
+
+
 # --------------------------------------------------------------------------------------------------
 # exports of the fitted mean (gpmpc/gp.py:72-85)
 # --------------------------------------------------------------------------------------------------

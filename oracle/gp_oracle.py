@@ -6,14 +6,21 @@ Nothing under `gpmpc_b200/` may import it: only `tests/`, `__graft_entry__.smoke
 `cpu_baseline` / `--impl reference` legs of `bench.py` use it, and only as the checker / the timed CPU
 baseline, never as the product path.
 
-PARITY UNPINNED.  The reference ships no tests, fixtures or golden vectors, and
-its arithmetic lives in third-party packages that are not installed and not installable here
-(gpytorch==1.12.0 pinned in reference `pyproject.toml:12`, `linear_operator`, casadi).  The restatement
-below therefore follows (a) the only place the reference spells the math out, `gpmpc/gp.py:12-14`
-(`covSE_single`) and `gpmpc/gp.py:85` (mean = k(z,X) K^-1 y), and (b) the published gpytorch 1.12.0
-semantics listed in SURVEY.md section 8c.  It is pinned only against independent re-derivations
-(`tests/test_oracle.py`: torch autograd, explicit-inverse formulas, an 80-bit long-double loop
-implementation, finite differences and analytic known-answer cases).
+PARITY STATUS.  The reference ships no tests, fixtures or golden vectors, and most of its
+arithmetic lives in third-party packages that are not installed and not installable here (gpytorch==1.12.0 pinned in
+reference `pyproject.toml:12`, `linear_operator`, casadi).
+  PINNED to outputs of the reference's own code (fixtures under tests/golden/, generating scripts committed):
+    * se_kernel / se_kernel_gpytorch  <- unmodified `covSE_single`, `covSE_vectorized` (gpmpc/gp.py:12-21) executed over a
+      NumPy casadi shim: covse_*.npz (make_golden_covse.py), <= 2e-13 element-wise
+    * assemble_K, the posterior mean  <- unmodified `gpytorch_predict2casadi` (gpmpc/gp.py:72-85) with K_inv from
+      torch.linalg.inv as at gp.py:46: pred_*.npz, <= 1e-10
+    * propagate_constraint_limits, fitc_posterior_mean  <- unmodified GPMPC methods (gpmpc/gpmpc.py:377-400, 425-507):
+      tighten_*.npz, fitc_*.npz (make_golden_mpc.py)
+  PARITY UNPINNED: what gpytorch does internally (softplus constraints and the 1e-6 noise floor, MLL / N, Cholesky,
+    the variance of the prediction strategy, the Adam loop).  These follow the published gpytorch 1.12.0 semantics listed
+    in SURVEY.md section 8c and are checked only against independent re-derivations (`tests/test_oracle.py`: torch
+    autograd, explicit-inverse formulas, an 80-bit long-double loop implementation, finite differences and analytic
+    known-answer cases).
 
 Conventions (reference file:line in brackets):
   K_f(a, b) = sf2 * exp(-1/2 * sum_j (a_j - b_j)^2 / ell_j^2)              [gpmpc/gp.py:12-14, 17-21]

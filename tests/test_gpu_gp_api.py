@@ -383,3 +383,32 @@ def test_graphed_mll_iteration_is_bit_identical_and_fit_gp_uses_it(n):
     ref = o.fit_hyperparameters(Xs, ys, n_train=8, lr=0.05)
     assert len(gp.fit_losses) == len(ref["losses"])
     assert o.rel_err(torch.tensor(gp.fit_losses), torch.tensor(ref["losses"])) < 1e-5
+
+
+def test_fit_gps_batched_equals_three_fit_gp_calls():
+    """fit_gps: the reference's three GPs (d = 1, 3, 3, same N) fitted in lockstep, one launch per Adam iteration for all
+    of them, with per-GP early stop -- same losses, parameters, K and K^-1 as three fit_gp calls and as the oracle loop."""
+    from gpmpc_b200.gp import GaussianProcess, fit_gp, fit_gps
+
+    g = torch.Generator().manual_seed(4)
+    N = 45
+    X = torch.rand(N, 7, generator=g, dtype=torch.float64) - 0.5
+    Y = 0.3 * torch.sin(3 * X[:, :3]) + 0.01 * torch.randn(N, 3, generator=g, dtype=torch.float64)
+    idx = ([0], [1, 2, 3], [4, 5, 6])
+    mk = lambda: [GaussianProcess(X[:, i].contiguous(), Y[:, p].contiguous()) for p, i in enumerate(idx)]
+    a, b = mk(), mk()
+    fit_gps(a, n_train=40, lr=0.05, device="cpu")
+    for gp in b:
+        fit_gp(gp, n_train=40, lr=0.05, device="cpu")
+    for p, (ga, gb) in enumerate(zip(a, b)):
+        ref = o.fit_hyperparameters(X[:, idx[p]].contiguous(), Y[:, p].contiguous(), n_train=40, lr=0.05)
+        assert len(ga.fit_losses) == len(gb.fit_losses) == len(ref["losses"])
+        assert o.rel_err(torch.tensor(ga.fit_losses), torch.tensor(gb.fit_losses)) < 1e-9
+        assert o.rel_err(torch.tensor(ga.fit_losses), torch.tensor(ref["losses"])) < 1e-5
+        for pa, pb in zip(ga.parameters(), gb.parameters()):
+            assert torch.allclose(pa, pb, atol=1e-6)
+        assert ga.K.shape == (N, N) and o.rel_err(ga.K, gb.K) < 1e-9 and o.rel_err(ga.K_inv, gb.K_inv) < 1e-6
+    # different N per GP: falls back to one fit_gp per GP
+    c = [GaussianProcess(X[:30, [0]].contiguous(), Y[:30, 0].contiguous()), GaussianProcess(X[:, [1, 2, 3]].contiguous(), Y[:, 1].contiguous())]
+    fit_gps(c, n_train=3, lr=0.05)
+    assert all(len(gp.fit_losses) >= 1 and gp.K is not None for gp in c)
