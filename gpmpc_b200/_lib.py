@@ -41,6 +41,8 @@ SIGNATURES = {
     "gpk_grad_trace_work_elems": (_l, [_l, _i, _l, _l]),
     "gpk_mll_grad_reduce": (_i, [_p, _l, _l, _i, _p, _p, _l, _p, _l, _l, _p, _l, _p, _p]),
     "gpk_mll_grad_reduce_sym": (_i, [_p, _l, _l, _i, _p, _p, _l, _p, _l, _l, _p, _l, _p, _p]),
+    "gpk_mll_grad_reduce_static_max_elems": (_l, []),
+    "gpk_mll_grad_reduce_static": (_i, [_p, _l, _l, _i, _p, _p, _l, _p, _l, _l, _i, _p, _p]),
     "gpk_pack_train_elems": (_l, [_l, _i]),
     "gpk_pack_train": (_i, [_i, _p, _l, _l, _i, _p, _p, _p, _l, _p]),
     "gpk_mean_jac_work_bytes": (_l, [_i, _l, _l, _i, _i]),

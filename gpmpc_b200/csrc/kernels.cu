@@ -11,6 +11,7 @@
 // distance computation); r^2 is then expanded as |a|^2 + |b|^2 - 2 a.b so the inner loop is one FMA per
 // dimension.
 #include "common.cuh"
+#include <mutex>
 
 namespace gpk {
 
@@ -705,6 +706,61 @@ int gpk_mll_grad_reduce_sym(const double* X, long ldx, long n, int d, const doub
                             const double* alpha, long r0, long r1, double* work, long work_elems, double* out,
                             void* stream) {
     return mll_grad_reduce(X, ldx, n, d, hyp, Kinv, ldk, alpha, r0, r1, work, work_elems, out, 1, stream);
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of the gradient trace: the per-CTA partial sums live in a file-scope device array
+// instead of a caller-supplied workspace, so the call needs no cudaMalloc anywhere (callers under CUDA-graph
+// capture, serving loops, harnesses that forbid allocation).  Every context that loads the library holds the
+// array (GT_STATIC_ELEMS doubles = 1.06 MiB) until exit.
+// In HOST code `g_gt_static_partials` is only a stand-in for the symbol, not a device address: its address is
+// looked up once per device with cudaGetSymbolAddress, with that device current, and that pointer is what the
+// kernels get.
+// ------------------------------------------------------------------------------------------------
+namespace gpk {
+constexpr long GT_STATIC_MAX_BLOCKS = 4096;                        // (n / 64)^2 CTAs of a full pass at n = 4096
+constexpr long GT_STATIC_ELEMS = GT_STATIC_MAX_BLOCKS * (HYP_MAXD + 2);
+static __device__ __align__(256) double g_gt_static_partials[GT_STATIC_ELEMS];
+
+static int gt_static_scratch(double** out_ptr) {
+    static std::mutex mu;
+    static double* ptr_dev[64] = {};
+    int dev = -1;
+    GPK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(-1, "grad_trace_static: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr_dev[dev]) {
+        void* p = nullptr;
+        GPK_CUDA(cudaGetSymbolAddress(&p, g_gt_static_partials));   // of the CURRENT device's copy of the array
+        if (!p) return fail(-1, "grad_trace_static: cudaGetSymbolAddress returned a null address");
+        ptr_dev[dev] = (double*)p;
+    }
+    *out_ptr = ptr_dev[dev];
+    return 0;
+}
+}  // namespace gpk
+
+extern "C" {
+
+long gpk_mll_grad_reduce_static_max_elems(void) { return GT_STATIC_ELEMS; }
+
+int gpk_mll_grad_reduce_static(const double* X, long ldx, long n, int d, const double* hyp, const double* Kinv,
+                               long ldk, const double* alpha, long r0, long r1, int sym, double* out, void* stream) {
+    GPK_ARG(d >= 1 && d <= HYP_MAXD && n > 0, "n / d");
+    GPK_ARG(0 <= r0 && r0 < r1 && r1 <= n, "row range");
+    GPK_ARG(sym == 0 || sym == 1, "sym must be 0 or 1");
+    const long need = gpk_grad_trace_work_elems(n, d, r0, r1);
+    if (need > GT_STATIC_ELEMS)
+        return fail(-1, "gpk_mll_grad_reduce_static: n = %ld, rows [%ld, %ld), d = %d need %ld scratch doubles, the "
+                        "built-in scratch holds %ld (a full pass up to n = 4096 at d = 32); use gpk_mll_grad_reduce with a "
+                        "caller-supplied workspace", n, r0, r1, d, need, (long)GT_STATIC_ELEMS);
+    double* scratch = nullptr;
+    if (int rc = gt_static_scratch(&scratch)) return rc;
+    // every CTA of the trace kernel (also the ones the symmetric form skips) WRITES its slot and the reduction reads
+    // exactly the slots of this launch, so nothing of an earlier call's contents is read: no clear is needed
+    return mll_grad_reduce(X, ldx, n, d, hyp, Kinv, ldk, alpha, r0, r1, scratch, GT_STATIC_ELEMS, out, sym, stream);
 }
 
 }  // extern "C"

@@ -121,6 +121,21 @@ int gpk_mll_grad_reduce(const double* X, long ldx, long n, int d, const double* 
 int gpk_mll_grad_reduce_sym(const double* X, long ldx, long n, int d, const double* hyp,
                         const double* Kinv, long ldk, const double* alpha, long r0, long r1,
                         double* work, long work_elems, double* out, void* stream);
+/* Allocation-free variant of the two entries above (sym = 0: gpk_mll_grad_reduce, sym = 1: gpk_mll_grad_reduce_sym).
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid allocation).  The per-CTA partial sums
+ * live in a file-scope `static __device__` array of the library instead of a caller workspace; the call performs no
+ * cudaMalloc / cudaFree and calls no allocating library routine.  Inputs and `out` (d_pad + 2 doubles, device) are the
+ * caller's.  Limit: gpk_grad_trace_work_elems(n, d, r0, r1) <= gpk_mll_grad_reduce_static_max_elems() = 139264 doubles
+ * (1.06 MiB, held by every GPU context that loads the library until exit) -- ceil((r1 - r0) / 64) * ceil(n / 64) * (d_pad + 2) partials: a full pass up to
+ * n = 4096 at any d <= 32 (n = 11904 at d = 2), or a row slice of a larger GP; beyond it the call returns an error
+ * naming the limit and launches nothing.  Every call on a device shares the one array (all slots a launch reads are
+ * written by that launch first, so nothing needs clearing between calls): calls that may OVERLAP on the GPU -- two
+ * streams, two host threads -- race on it and must be serialised by the caller; calls on one stream are safe. */
+long gpk_mll_grad_reduce_static_max_elems(void);
+int gpk_mll_grad_reduce_static(const double* X, long ldx, long n, int d, const double* hyp,
+                        const double* Kinv, long ldk, const double* alpha, long r0, long r1,
+                        int sym, double* out, void* stream);
 
 /* ---- (6) fused posterior mean + input-Jacobian ------------------------------------------------
  * gpk_pack_train builds the resident training pack (scaled points, -1/2|x|^2, sf2*alpha) in the
