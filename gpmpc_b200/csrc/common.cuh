@@ -124,5 +124,7 @@ void exp_table_release();
 int fit_side_prepare(int events);
 void fit_side_release();
 void ozg_items_release();
+int oz_side_prepare();
+void oz_side_release();
 
 }  // namespace gpk

@@ -612,6 +612,7 @@ int gpk_abi_version(void) { return 2; }
 // gpk_potrf_trtri and a pool of events for it.  Idempotent; call once per device before timing-sensitive work.
 int gpk_init(void* stream) {
     GPK_ARG(exp_table((cudaStream_t)stream) != nullptr, "could not allocate the exp table");
+    GPK_TRY(oz_side_prepare());
     return fit_side_prepare(1024);
 }
 // Frees the current device's library state: exp table, side stream, events, cached int8-GEMM item lists, and forgets
@@ -620,6 +621,7 @@ int gpk_shutdown(void) {
     GPK_CUDA(cudaDeviceSynchronize());
     exp_table_release();
     fit_side_release();
+    oz_side_release();
     ozg_items_release();
     return 0;
 }

@@ -88,10 +88,16 @@ struct OzFrontArgs {
     int kb_total, kb_per_cta;
     double* mj_part; long stride_mj;         // [gp][split][q][DP + 1] partial (m, S_j)
     const double* exp_tab;                   // 2^(j/1024), j < 1024 (device, built once per process)
+    unsigned long long* tdbg;                // experiments only: per-CTA (start, end) global timer of the co-resident kernel
 };
 
+__device__ __forceinline__ unsigned long long oz_gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __device__ __forceinline__ void oz_dmma(double (&c)[2], double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
                  : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
 
@@ -102,25 +108,33 @@ __device__ __forceinline__ void oz_dmma(double (&c)[2], double a, double b) {
 // are (i) exactly the A-fragment elements it must supply to GEMM 2 and (ii) four CONSECUTIVE training points
 // k = 4t .. 4t+3 of a 16-point unit, i.e. one aligned 32-bit word of each digit row: a warp's digit store is
 // one contiguous 128-byte core matrix.  Column c = 2t+u of block b  <->  point 4t + 2b + u.
-template <typename TZ, int S, int DP, bool MJ>
-__global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
+template <int DP, bool MJ>
+struct OzFrontSmem {
+    static constexpr int DPB = DP < 8 ? 8 : DP;
+    static constexpr int LDA = ((DP + 15) / 16) * 16 + 4;       // = 4 mod 16: conflict-free B fragments of GEMM 1
+    static constexpr int LDB = DPB + 1;                         // = 1 mod 4 : conflict-free B fragments of GEMM 2
+    alignas(16) double XsA[OZ_BK * LDA];                         // rows in fragment-column order (see above)
+    alignas(16) double XsB[MJ ? OZ_BK * LDB : 1];                // rows in natural order
+    alignas(16) double ex[OZ_BK];
+    alignas(16) double as[OZ_BK];
+    double exp_tab[EXP_TAB];
+};
+
+// One work item = (GP, 16 NW queries starting at row q_off of query tile qt, split of the training range), NW warps.
+template <typename TZ, int S, int DP, bool MJ, int NW, bool IMG>
+__device__ __forceinline__ void oz_front_item(const OzFrontArgs& a, OzFrontSmem<DP, MJ>& sm, long gp, int qt, int q_off, int split) {
     constexpr int KS = DP / 4;                           // GEMM 1 k-steps
-    constexpr int DPB = DP < 8 ? 8 : DP, NB = DPB / 8;   // GEMM 2 column blocks
-    constexpr int LDA = ((DP + 15) / 16) * 16 + 4;       // = 4 mod 16: conflict-free B fragments of GEMM 1
-    constexpr int LDB = DPB + 1;                         // = 1 mod 4 : conflict-free B fragments of GEMM 2
-    __shared__ __align__(16) double XsA[OZ_BK * LDA];    // rows in fragment-column order (see above)
-    __shared__ __align__(16) double XsB[MJ ? OZ_BK * LDB : 1];   // rows in natural order
-    __shared__ __align__(16) double ex[OZ_BK], as[OZ_BK];
-    __shared__ double exp_tab[EXP_TAB];
-    const long gp = blockIdx.z;
-    const int qt = blockIdx.y;
+    constexpr int DPB = OzFrontSmem<DP, MJ>::DPB, NB = DPB / 8;   // GEMM 2 column blocks
+    constexpr int LDA = OzFrontSmem<DP, MJ>::LDA, LDB = OzFrontSmem<DP, MJ>::LDB;
+    constexpr int NT = 32 * NW;                          // threads of the CTA
+    constexpr int PASSES = 4 * OZ_BK / NT;               // staging: 4 threads per training point, NT / 4 points per pass
+    double* XsA = sm.XsA; double* XsB = sm.XsB; double* ex = sm.ex; double* as = sm.as;
+    const double* exp_tab = sm.exp_tab;
     const double* hyp = a.hyp + gp * HYP_STRIDE;
     const TZ* Z = reinterpret_cast<const TZ*>(a.Z) + gp * a.strideZ;
     const double* X = a.X + gp * a.strideX;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    for (int i = tid; i < EXP_TAB; i += 256) exp_tab[i] = a.exp_tab[i];   // visible after the first barrier below
     const int g = lane >> 2, t = lane & 3;
-    const bool write_img = a.img != nullptr;             // mean + Jacobian only when no image is wanted
 
     // A fragments of GEMM 1 (scaled queries) for the two 8-query blocks of this warp
     double za[2][KS], ezq[2];
@@ -128,7 +142,7 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
     int qrow[2];
 #pragma unroll
     for (int mb = 0; mb < 2; mb++) {
-        qrow[mb] = warp * 16 + mb * 8 + g;
+        qrow[mb] = q_off + warp * 16 + mb * 8 + g;
         const long gq = (long)qt * OZ_QT + qrow[mb];
         qv[mb] = gq < a.q;
         double sq = 0.0;
@@ -142,7 +156,7 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
         }
         sq += __shfl_xor_sync(0xffffffffu, sq, 1);
         sq += __shfl_xor_sync(0xffffffffu, sq, 2);
-        ezq[mb] = -0.5 * sq;
+        ezq[mb] = qv[mb] ? -0.5 * sq : -1.0e300;        // queries beyond q: exp -> 0, like the padding points
     }
     double S2[2][NB][2], msum[2] = {0.0, 0.0};
 #pragma unroll
@@ -150,33 +164,40 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
 #pragma unroll
         for (int nb = 0; nb < NB; nb++) S2[mb][nb][0] = S2[mb][nb][1] = 0.0;
 
-    const int kb0 = blockIdx.x * a.kb_per_cta;
+    const int kb0 = split * a.kb_per_cta;
     const int kb1 = min(a.kb_total, kb0 + a.kb_per_cta);
     // staging role: 4 threads per training point, thread `part` owns dimensions part, part + 4, ...
-    const int sp = tid >> 2, part = tid & 3;
-    const int kk = sp & 15;
-    const int slotA = (sp & ~15) + ((kk >> 1) & 1) * 8 + 2 * (kk >> 2) + (kk & 1);
+    const int part = tid & 3;
     constexpr int NPF = (DPB + 3) / 4;
-    double pf[NPF], pf_alpha = 0.0;
+    double pf[PASSES][NPF], pf_alpha[PASSES];
     auto prefetch = [&](int kb) {                        // raw values of the next k block into registers
-        const long gi = (long)kb * OZ_BK + sp;
 #pragma unroll
-        for (int u = 0; u < NPF; u++) {
-            const int j = part + 4 * u;
-            pf[u] = (gi < a.n && j < a.d) ? X[gi * a.ldx + j] : 0.0;
+        for (int ps = 0; ps < PASSES; ps++) {
+            const int sp = (tid >> 2) + ps * (NT / 4);
+            const long gi = (long)kb * OZ_BK + sp;
+#pragma unroll
+            for (int u = 0; u < NPF; u++) {
+                const int j = part + 4 * u;
+                pf[ps][u] = (gi < a.n && j < a.d) ? X[gi * a.ldx + j] : 0.0;
+            }
+            pf_alpha[ps] = 0.0;
+            if (MJ && part == 0) pf_alpha[ps] = gi < a.n ? a.alpha[gp * a.stride_alpha + gi] : 0.0;
         }
-        if (MJ && part == 0) pf_alpha = gi < a.n ? a.alpha[gp * a.stride_alpha + gi] : 0.0;
     };
     if (kb0 < kb1) prefetch(kb0);
     for (int kb = kb0; kb < kb1; kb++) {
         __syncthreads();
-        {
+#pragma unroll
+        for (int ps = 0; ps < PASSES; ps++) {
+            const int sp = (tid >> 2) + ps * (NT / 4);
+            const int kk = sp & 15;
+            const int slotA = (sp & ~15) + ((kk >> 1) & 1) * 8 + 2 * (kk >> 2) + (kk & 1);
             const long gi = (long)kb * OZ_BK + sp;
             double sq = 0.0;
 #pragma unroll
             for (int u = 0; u < NPF; u++) {
                 const int j = part + 4 * u;
-                const double v = (gi < a.n && j < a.d) ? (pf[u] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j] : 0.0;
+                const double v = (gi < a.n && j < a.d) ? (pf[ps][u] - hyp[HYP_CENTER + j]) * hyp[HYP_INV_ELL + j] : 0.0;
                 if (j < DP) XsA[slotA * LDA + j] = v;
                 if (MJ) XsB[sp * LDB + j] = v;
                 sq = fma(v, v, sq);
@@ -185,7 +206,7 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
             sq += __shfl_xor_sync(0xffffffffu, sq, 2);
             if (part == 0) {
                 ex[sp] = gi < a.n ? -0.5 * sq : -1.0e300;  // padding points: exp -> 0
-                as[sp] = MJ ? hyp[HYP_SF2] * pf_alpha : 0.0;
+                as[sp] = MJ ? hyp[HYP_SF2] * pf_alpha[ps] : 0.0;
             }
         }
         __syncthreads();
@@ -211,35 +232,46 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
 #pragma unroll
                     for (int nb = 0; nb < NB; nb++) b2[i][nb] = XsB[(p0 + i) * LDB + g + 8 * nb];
             }
+            // straight-line code for both 8-query blocks (no branch inside a unit: one basic block, so that the
+            // independent chains of the two blocks interleave)
+            double c[2][2][2];
 #pragma unroll
             for (int mb = 0; mb < 2; mb++) {
-                double c[2][2];
-                c[0][0] = ezq[mb] + ex01.x; c[0][1] = ezq[mb] + ex01.y;
-                c[1][0] = ezq[mb] + ex23.x; c[1][1] = ezq[mb] + ex23.y;
+                c[mb][0][0] = ezq[mb] + ex01.x; c[mb][0][1] = ezq[mb] + ex01.y;
+                c[mb][1][0] = ezq[mb] + ex23.x; c[mb][1][1] = ezq[mb] + ex23.y;
+            }
 #pragma unroll
-                for (int s_ = 0; s_ < KS; s_++) {
-                    oz_dmma(c[0], za[mb][s_], b1[0][s_]);
-                    oz_dmma(c[1], za[mb][s_], b1[1][s_]);
+            for (int s_ = 0; s_ < KS; s_++)
+#pragma unroll
+                for (int mb = 0; mb < 2; mb++) {
+                    oz_dmma(c[mb][0], za[mb][s_], b1[0][s_]);
+                    oz_dmma(c[mb][1], za[mb][s_], b1[1][s_]);
                 }
-                double e[4];
+            double e[2][4];
 #pragma unroll
-                for (int i = 0; i < 4; i++) e[i] = qv[mb] ? exp_neg_tab(c[i >> 1][i & 1], exp_tab) : 0.0;
-                if (write_img) {
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int mb = 0; mb < 2; mb++) e[mb][i] = exp_neg_tab(c[mb][i >> 1][i & 1], exp_tab);   // invalid query: ezq = -1e300 -> 0
+            if (IMG) {
+#pragma unroll
+                for (int mb = 0; mb < 2; mb++) {
                     uint32_t w[S];
-                    oz_pack_digits4<S>(e, w);
+                    oz_pack_digits4<S>(e[mb], w);
                     int8_t* dst = out + oz_tile_off(qrow[mb], unit * 16 + 4 * t);
 #pragma unroll
                     for (int s_ = 0; s_ < S; s_++) *reinterpret_cast<uint32_t*>(dst + (long)s_ * OZ_A_SLICE) = w[s_];
                 }
-                if (MJ) {
+            }
+            if (MJ) {
 #pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        const double wgt = e[i] * as4[i];
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int mb = 0; mb < 2; mb++) {
+                        const double wgt = e[mb][i] * as4[i];
                         msum[mb] += wgt;
 #pragma unroll
                         for (int nb = 0; nb < NB; nb++) oz_dmma(S2[mb][nb], wgt, b2[i][nb]);
                     }
-                }
             }
         }
     }
@@ -251,7 +283,7 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
             m += __shfl_xor_sync(0xffffffffu, m, 2);
             if (!qv[mb]) continue;
             const long gq = (long)qt * OZ_QT + qrow[mb];
-            double* dst = a.mj_part + gp * a.stride_mj + ((long)blockIdx.x * a.q + gq) * (DP + 1);
+            double* dst = a.mj_part + gp * a.stride_mj + ((long)split * a.q + gq) * (DP + 1);
             if (t == 0) dst[0] = m;
 #pragma unroll
             for (int nb = 0; nb < NB; nb++)
@@ -262,6 +294,36 @@ __global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
                 }
         }
     }
+}
+
+// stand-alone front end: one CTA (8 warps) per (split, query tile, GP), two CTAs per SM
+template <typename TZ, int S, int DP, bool MJ, bool IMG>
+__global__ void __launch_bounds__(256, 2) oz_front_kernel(const OzFrontArgs a) {
+    __shared__ OzFrontSmem<DP, MJ> sm;
+    for (int i = threadIdx.x; i < EXP_TAB; i += 256) sm.exp_tab[i] = a.exp_tab[i];   // visible after the item's first barrier
+    oz_front_item<TZ, S, DP, MJ, 8, IMG>(a, sm, blockIdx.z, blockIdx.y, 0, blockIdx.x);
+}
+
+// co-resident front end: persistent, at most one 4-warp CTA per SM (152 registers x 128 threads and 29 KB of shared
+// memory are what a resident oz_var_kernel CTA leaves free), so that the E image of the NEXT query sub-chunk is
+// produced on the FP64 pipe while the tensor pipe contracts the current one.  Items = (GP, query tile, half tile,
+// split), static round-robin.
+template <typename TZ, int S, int DP, bool MJ>
+__global__ void __maxnreg__(152) oz_front_co_kernel(const OzFrontArgs a, int n_split, int qtiles, int batch) {
+    __shared__ OzFrontSmem<DP, MJ> sm;
+    if (a.tdbg && threadIdx.x == 0) a.tdbg[2 * blockIdx.x] = oz_gtimer();
+    for (int i = threadIdx.x; i < EXP_TAB; i += 128) sm.exp_tab[i] = a.exp_tab[i];
+    const long total = (long)batch * qtiles * 2 * n_split;
+    for (long item = blockIdx.x; item < total; item += gridDim.x) {
+        const int split = (int)(item % n_split);
+        long r = item / n_split;
+        const int half = (int)(r & 1);
+        r >>= 1;
+        const int qt = (int)(r % qtiles);
+        const long gp = r / qtiles;
+        oz_front_item<TZ, S, DP, MJ, 4, true>(a, sm, gp, qt, half * 64, split);
+    }
+    if (a.tdbg && threadIdx.x == 0) a.tdbg[2 * blockIdx.x + 1] = oz_gtimer();
 }
 
 // mean = sum of the split partials; jac_j = (S_j - z~_j mean) / ell_j
@@ -319,13 +381,16 @@ struct OzArgs {
     int piece_begin[OZ_MAX_PIECES + 1];      // W row-block PAIRS [piece_begin[p], piece_begin[p+1]) of piece p
     int32_t* dbg;                            // optional raw accumulators [gp*qtiles + qt][ib][S][128][64]
     int flags;                               // profiling only: 1 = epilogue skips the TMEM reads and the math
+    unsigned long long* tdbg;                // experiments only: per-CTA (start, end) global timer
 };
 
 constexpr int OZ_EPI_WARPS = 8;
-constexpr int OZ_THREADS = 64 + 32 * OZ_EPI_WARPS;
+// 12 warps = three FULL warpgroups: setmaxnreg only completes when every warp of a 4-warp group executes the same
+// instruction (a 10-warp CTA hangs on this part: tools/peaks/setmaxnreg_probe.cu); warps 10 and 11 only hand back registers
+constexpr int OZ_THREADS = 128 + 32 * OZ_EPI_WARPS;
 // the two single-thread roles get the HIGHEST warp ids: the SM's issue arbiter prefers higher warp ids, and the
 // MMA issuer must never queue behind the epilogue warps that share its scheduler
-constexpr int OZ_PRODUCER_WARP = OZ_EPI_WARPS, OZ_MMA_WARP = OZ_EPI_WARPS + 1;
+constexpr int OZ_PRODUCER_WARP = OZ_EPI_WARPS + 2, OZ_MMA_WARP = OZ_EPI_WARPS + 3;
 
 __device__ __forceinline__ void oz_item_coords(const OzArgs& a, int item, int& qt, int& gp, int& jp0, int& jp1) {
     const int col = item / a.n_pieces;            // consecutive items share the query tile (its E image stays in L2)
@@ -336,8 +401,18 @@ __device__ __forceinline__ void oz_item_coords(const OzArgs& a, int item, int& q
     jp1 = a.piece_begin[piece + 1];
 }
 
+// Register budget: the kernel is launched with OZ_LAUNCH_REGS registers per thread (384 x 120 = 46,080 of the SM's
+// 65,536), the warpgroup of the two single-thread roles hands its registers back (setmaxnreg.dec) and the epilogue
+// warps take theirs (8 x 32 x OZ_EPI_REGS + 4 x 32 x OZ_AUX_REGS = 46,080): what is left (19,456 registers, ~45 KB of
+// shared memory at S <= 5) holds one 4-warp CTA of oz_front_co_kernel, which produces the next sub-chunk's E image on
+// the otherwise idle FP64 pipe.
+constexpr int OZ_LAUNCH_REGS = 120;
+#ifndef OZ_EPI_REGS
+#define OZ_EPI_REGS 160
+#define OZ_AUX_REGS 40
+#endif
 template <int S>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_var_kernel(const OzArgs a) {
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(OZ_LAUNCH_REGS) oz_var_kernel(const OzArgs a) {
     constexpr int NST = oz_stages(S);
     constexpr uint32_t STAGE_BYTES = oz_stage_bytes(S);
     constexpr uint32_t A_BYTES = S * OZ_A_SLICE, B_BYTES = S * OZ_B_SLICE;
@@ -370,7 +445,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
     cluster_sync_all();                      // the peer's barriers are initialised before anything is multicast
     tc_fence_after();
     const uint32_t tmem_base = tmem_base_smem;
+    if (a.tdbg && threadIdx.x == 0) a.tdbg[2 * blockIdx.x] = oz_gtimer();
 
+    if (warp >= OZ_EPI_WARPS) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(OZ_AUX_REGS));
     if (warp == OZ_PRODUCER_WARP) {
         // ===== producer (warp-uniform, elected lane issues) =====
         const uint32_t leader = elect_one() ? 1u : 0u;
@@ -438,8 +515,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
                 tph ^= 1;
             }
         }
-    } else {
+    } else if (warp < OZ_EPI_WARPS) {
         // ===== epilogue: warps 0..7; lane quarter = warp % 4, column half = warp / 4 =====
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(OZ_EPI_REGS));
         const int quarter = warp & 3;
         const int half = warp >> 2;
         const int row = quarter * 32 + lane;                   // query within the tile
@@ -556,6 +634,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(OZ_THREADS, 1) oz_va
     }
     tc_fence_before();
     __syncthreads();
+    if (a.tdbg && threadIdx.x == 0) a.tdbg[2 * blockIdx.x + 1] = oz_gtimer();
     cluster_sync_all();                      // the peer may still be multicasting into / arriving on this CTA
     if (warp == OZ_MMA_WARP) {
         tc_fence_after();
@@ -632,6 +711,9 @@ static int oz_launch_var(const OzArgs& a, cudaStream_t st) {
     bool& attr_done = attr_dev[current_device()];
     if (!attr_done) {
         GPK_CUDA(cudaFuncSetAttribute(oz_var_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        // the full carveout, not the smallest that fits this kernel: the co-resident front CTA lives in the rest
+        GPK_CUDA(cudaFuncSetAttribute(oz_var_kernel<S>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                      (int)cudaSharedmemCarveoutMaxShared));
         attr_done = true;
     }
     const int hw_pairs = oz_sm_count() / 2;
@@ -663,14 +745,46 @@ static int oz_front_splits(long qtiles_total, int kb_total) {
     return best;
 }
 
-template <typename TZ, int S, bool MJ>
-static int oz_launch_front(const OzFrontArgs& a, int n_split, long qtiles, int batch, TZ* mean, long stride_mean, TZ* jac,
+// splits of the co-resident front end: persistent CTAs (one per SM), items = columns x 2 half tiles x splits
+static int oz_front_co_splits(long cols, int kb_total) {
+    const long slots = oz_sm_count();
+    int best = 1;
+    double best_cost = 1e30;
+    for (int ns = 1; ns <= 16 && ns <= kb_total; ns++) {
+        const long items = cols * 2 * ns;
+        const long rounds = (items + slots - 1) / slots;
+        const int kb_per_cta = (kb_total + ns - 1) / ns;
+        const double cost = (double)rounds * (kb_per_cta + 0.5);
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = ns; }
+    }
+    return best;
+}
+
+template <typename TZ, int S, bool MJ, bool IMG = true>
+static int oz_launch_front(const OzFrontArgs& a, bool co, int n_split, long qtiles, int batch, TZ* mean, long stride_mean, TZ* jac,
                            long ldj, long stride_jac, cudaStream_t st) {
-    dim3 grid((unsigned)n_split, (unsigned)qtiles, (unsigned)batch);
     const int dp = oz_pad_dim(a.d);
-#define OZ_FRONT_CASE(DPV) case DPV: oz_front_kernel<TZ, S, DPV, MJ><<<grid, 256, 0, st>>>(a); break;
-    switch (dp) { OZ_FRONT_CASE(4) OZ_FRONT_CASE(8) OZ_FRONT_CASE(16) OZ_FRONT_CASE(32) }
+    if (co && IMG) {
+        const long items = (long)batch * qtiles * 2 * n_split;
+        const unsigned grid = (unsigned)(items < oz_sm_count() ? items : oz_sm_count());
+        // the shared-memory carveout is an SM-wide setting: a kernel that prefers a smaller one than the resident
+        // oz_var_kernel (which needs the maximum) is not scheduled onto that SM until it drains
+        static bool attr_dev[64][4] = {};
+#define OZ_FRONT_CASE(DPV, I) case DPV: \
+            if (!attr_dev[current_device()][I]) { \
+                GPK_CUDA(cudaFuncSetAttribute(oz_front_co_kernel<TZ, S, DPV, MJ>, cudaFuncAttributePreferredSharedMemoryCarveout, \
+                                              (int)cudaSharedmemCarveoutMaxShared)); \
+                attr_dev[current_device()][I] = true; \
+            } \
+            oz_front_co_kernel<TZ, S, DPV, MJ><<<grid, 128, 0, st>>>(a, n_split, (int)qtiles, batch); break;
+        switch (dp) { OZ_FRONT_CASE(4, 0) OZ_FRONT_CASE(8, 1) OZ_FRONT_CASE(16, 2) OZ_FRONT_CASE(32, 3) }
 #undef OZ_FRONT_CASE
+    } else {
+        dim3 grid((unsigned)n_split, (unsigned)qtiles, (unsigned)batch);
+#define OZ_FRONT_CASE(DPV) case DPV: oz_front_kernel<TZ, S, DPV, MJ, IMG><<<grid, 256, 0, st>>>(a); break;
+        switch (dp) { OZ_FRONT_CASE(4) OZ_FRONT_CASE(8) OZ_FRONT_CASE(16) OZ_FRONT_CASE(32) }
+#undef OZ_FRONT_CASE
+    }
     GPK_LAUNCHED();
     if (MJ) {
         dim3 g2((unsigned)((a.q + 127) / 128), 1, (unsigned)batch);
@@ -682,18 +796,109 @@ static int oz_launch_front(const OzFrontArgs& a, int n_split, long qtiles, int b
     return 0;
 }
 
+// co = the persistent 4-warp variant that shares the SMs with a running oz_var_kernel (gpk_predict_i8's pipeline)
 template <typename TZ>
-static int oz_front_dispatch(const OzFrontArgs& a_in, int S, bool mj, int n_split, long qtiles, int batch, void* mean,
+static int oz_front_dispatch(const OzFrontArgs& a_in, int S, bool mj, bool co, long qtiles, int batch, void* mean,
                              long stride_mean, void* jac, long ldj, long stride_jac, cudaStream_t st) {
     OzFrontArgs a = a_in;
+    if (a.img != nullptr && getenv("GPK_OZ_FRONT_CO")) co = atoi(getenv("GPK_OZ_FRONT_CO")) != 0;   // experiments only
     a.exp_tab = exp_table(st);
     GPK_ARG(a.exp_tab != nullptr, "could not allocate the exp table");
+    const int n_split = co ? oz_front_co_splits(qtiles * batch, a.kb_total) : oz_front_splits(qtiles * batch, a.kb_total);
+    a.kb_per_cta = (a.kb_total + n_split - 1) / n_split;
+    // no image wanted (mean + Jacobian alone): the image-free instantiation
+    if (a.img == nullptr) {
+        if (!mj || co) return fail(-1, "front end without an image needs mean/Jacobian outputs");
+        return oz_launch_front<TZ, OZ_MIN_S, true, false>(a, false, n_split, qtiles, batch, (TZ*)mean, stride_mean, (TZ*)jac, ldj, stride_jac, st);
+    }
 #define OZ_F(SV) \
-    if (S == SV) return mj ? oz_launch_front<TZ, SV, true>(a, n_split, qtiles, batch, (TZ*)mean, stride_mean, (TZ*)jac, ldj, stride_jac, st) \
-                           : oz_launch_front<TZ, SV, false>(a, n_split, qtiles, batch, nullptr, 0, nullptr, 0, 0, st);
+    if (S == SV) return mj ? oz_launch_front<TZ, SV, true>(a, co, n_split, qtiles, batch, (TZ*)mean, stride_mean, (TZ*)jac, ldj, stride_jac, st) \
+                           : oz_launch_front<TZ, SV, false>(a, co, n_split, qtiles, batch, nullptr, 0, nullptr, 0, 0, st);
     OZ_F(4) OZ_F(5) OZ_F(6)
 #undef OZ_F
     return fail(-1, "digits must be 4, 5 or 6");
+}
+
+// ---- side stream of the prediction pipeline (per device; created by gpk_init or lazily) -----------------------
+struct OzSide {
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_front[2] = {nullptr, nullptr}, ev_gemm[2] = {nullptr, nullptr};
+};
+static OzSide g_oz_side[64];
+static unsigned long long* g_oz_tdbg_gemm = nullptr;   // experiments only (GPK_OZ_PIPE_TRACE)
+static unsigned long long* g_oz_tdbg_front = nullptr;
+int gpk::oz_side_prepare() {
+    OzSide& sd = g_oz_side[current_device()];
+    if (sd.side) return 0;
+    GPK_CUDA(cudaStreamCreateWithFlags(&sd.side, cudaStreamNonBlocking));
+    cudaEvent_t* evs[5] = {&sd.ev_fork, &sd.ev_front[0], &sd.ev_front[1], &sd.ev_gemm[0], &sd.ev_gemm[1]};
+    for (cudaEvent_t* e : evs) GPK_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    return 0;
+}
+void gpk::oz_side_release() {
+    OzSide& sd = g_oz_side[current_device()];
+    if (!sd.side) return;
+    cudaEvent_t evs[5] = {sd.ev_fork, sd.ev_front[0], sd.ev_front[1], sd.ev_gemm[0], sd.ev_gemm[1]};
+    for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
+    cudaStreamDestroy(sd.side);
+    sd = OzSide{};
+}
+
+// Sub-chunk plan of gpk_predict_i8.  Cost model in units of one column's (GP x 128-query tile) contraction time:
+// the stand-alone front end costs f per column (f = 0.42 at npad = 2048, ~ 1/npad), the co-resident one about
+// OZ_CO_SLOWDOWN x that (one 4-warp CTA per SM instead of two 8-warp CTAs) and hides behind the previous sub-chunk's
+// contraction; a contraction launch of c columns runs ceil(c p / pairs) rounds of items of 1/p column each and costs a
+// fixed L per launch (ramp, tail, cross-stream event).  Not pipelined: every front end is exposed.
+struct OzPlan { long tsub; bool pipelined; };
+static double oz_gemm_cost(long cols, long npairs_w) {
+    const long hw_pairs = oz_sm_count() / 2;
+    double best = 1e300;
+    for (int p = 1; p <= OZ_MAX_PIECES && p <= npairs_w; p++) {
+        const long rounds = (cols * p + hw_pairs - 1) / hw_pairs;
+        const double c = (double)rounds * hw_pairs / p * (1.0 + 0.002 * p);
+        if (c < best) best = c;
+    }
+    return best;
+}
+static OzPlan oz_plan(long tiles_total, int batch, long npad, int S, long tcap) {
+    const long npw = npad / (2 * OZ_WB);
+    const double f = 0.42 * 2048.0 / (double)npad;
+    double L = 3.0 * (2048.0 / (double)npad) * (2048.0 / (double)npad);
+    double co_slow = 4.5;
+    // Default OFF: measured on B200 (profiles/pipeline_r02.md) the co-resident front CTAs start with the contraction
+    // but are starved until it ends -- oz_var_kernel's tensor-core operand fetches take ~114 of the SM's 128 B/clk of
+    // shared-memory bandwidth, which the front end's fragment loads need too -- so the pipelined step is slower
+    // (config 2: 0.77 vs 0.72 ms) or equal (config 3).  The path stays for experiments and is covered by tests.
+    int mode = 0;                                        // 0 = never pipeline, 1 = by the model, 2 = always (tests)
+    if (const char* e = getenv("GPK_OZ_PIPELINE")) mode = atoi(e);
+    if (const char* e = getenv("GPK_OZ_PIPE_L")) L = atof(e);
+    if (const char* e = getenv("GPK_OZ_PIPE_CO")) co_slow = atof(e);
+    long force_t = 0;
+    if (const char* e = getenv("GPK_OZ_PIPE_TSUB")) force_t = atol(e);
+    const long t1 = tiles_total < tcap ? tiles_total : tcap;
+    // not pipelined: chunks of t1 tiles
+    double cost1 = 0.0;
+    for (long done = 0; done < tiles_total; done += t1) {
+        const long t = tiles_total - done < t1 ? tiles_total - done : t1;
+        cost1 += f * t * batch + oz_gemm_cost(t * batch, npw) + L;
+    }
+    OzPlan plan{t1, false};
+    // the co-resident front CTA needs the shared memory a contraction CTA leaves free: S <= 5 (see OZ_LAUNCH_REGS)
+    const long tcap2 = tcap / 2;
+    if (mode == 0 || S > 5 || tcap2 < 1 || tiles_total < 2) return plan;
+    double best = mode == 2 ? 1e300 : cost1;
+    for (long t = 1; t <= tcap2 && t < tiles_total; t++) {
+        if (force_t && t != force_t) continue;
+        double cost = f * t * batch;
+        for (long done = 0; done < tiles_total; done += t) {
+            const long tc = tiles_total - done < t ? tiles_total - done : t;
+            const long tn = tiles_total - done - tc < t ? tiles_total - done - tc : t;     // next sub-chunk's tiles
+            const double g = oz_gemm_cost(tc * batch, npw), fn = co_slow * f * tn * batch;
+            cost += (g > fn ? g : fn) + L;
+        }
+        if (cost < best) { best = cost; plan = OzPlan{t, true}; }
+    }
+    return plan;
 }
 
 constexpr int OZ_SLOTS = 2 * OZ_MAX_PIECES;
@@ -755,10 +960,8 @@ int gpk_oz_cross(int dtype, const void* Z, long ldz, long q, long strideZ, const
     a.img = (int8_t*)img; a.strideE = strideE;
     a.kb_total = (int)(npad / OZ_BK);
     const long qtiles = qpad / OZ_QT;
-    const int ns = oz_front_splits(qtiles * batch, a.kb_total);
-    a.kb_per_cta = (a.kb_total + ns - 1) / ns;
-    if (dtype == 0) return oz_front_dispatch<float>(a, S, false, ns, qtiles, batch, nullptr, 0, nullptr, 0, 0, (cudaStream_t)stream);
-    return oz_front_dispatch<double>(a, S, false, ns, qtiles, batch, nullptr, 0, nullptr, 0, 0, (cudaStream_t)stream);
+    if (dtype == 0) return oz_front_dispatch<float>(a, S, false, false, qtiles, batch, nullptr, 0, nullptr, 0, 0, (cudaStream_t)stream);
+    return oz_front_dispatch<double>(a, S, false, false, qtiles, batch, nullptr, 0, nullptr, 0, 0, (cudaStream_t)stream);
 }
 
 // mean + Jacobian alone on the DMMA front kernel (no digit image, no variance): the want_var = false path for fp64
@@ -794,13 +997,11 @@ int gpk_predict_mean_jac_dmma(int dtype, const void* Z, long ldz, long q, long s
         a.d = d; a.hyp = hyp;
         a.img = nullptr; a.strideE = 0;
         a.kb_total = (int)((n + OZ_BK - 1) / OZ_BK);
-        const int ns = oz_front_splits(qtiles * batch, a.kb_total);
-        a.kb_per_cta = (a.kb_total + ns - 1) / ns;
         a.mj_part = (double*)work; a.stride_mj = (long)OZ_MAX_SPLITS * qc * (dp + 1);
         void* mout = (char*)mean + q0 * esz;
         void* jout = (char*)jac + q0 * ldj * esz;
-        if (dtype == 0) GPK_TRY(oz_front_dispatch<float>(a, OZ_MIN_S, true, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
-        else GPK_TRY(oz_front_dispatch<double>(a, OZ_MIN_S, true, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
+        if (dtype == 0) GPK_TRY(oz_front_dispatch<float>(a, OZ_MIN_S, true, false, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
+        else GPK_TRY(oz_front_dispatch<double>(a, OZ_MIN_S, true, false, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
     }
     return 0;
 }
@@ -840,6 +1041,7 @@ static int oz_var_partials(const void* Eimg, long strideE, const void* Wimg, lon
     }
     a.piece_begin[n_pieces] = (int)nib;
     a.dbg = dbg;
+    a.tdbg = g_oz_tdbg_gemm;
     a.flags = getenv("GPK_OZ_FLAGS") ? atoi(getenv("GPK_OZ_FLAGS")) : 0;
     cudaStream_t st = (cudaStream_t)stream;
     if (S == 4) return oz_launch_var<4>(a, st);
@@ -891,43 +1093,115 @@ int gpk_predict_i8(int dtype, const void* Z, long ldz, long q, long strideZ, int
     if (mul_digits) S = mul_digits;
     const bool mj = mean != nullptr;
     const int dp = oz_pad_dim(d);
-    const long per_q = ((long)S * npad + OZ_SLOTS * 8 + (long)OZ_MAX_SPLITS * (dp + 1) * 8) * batch;
-    long qc = work_bytes / per_q;
-    qc = qc / OZ_QT * OZ_QT;
-    GPK_ARG(qc >= OZ_QT, "scratch too small (see gpk_predict_i8_work_bytes)");
-    const long q_round = (q + OZ_QT - 1) / OZ_QT * OZ_QT;
-    if (qc > q_round) qc = q_round;
-    int8_t* eimg = (int8_t*)work;                                         // [batch][S qc npad]
-    double* part = (double*)(eimg + (long)batch * S * qc * npad);         // [batch][slots][qc]
-    double* mjp = part + (long)batch * OZ_SLOTS * qc;                     // [batch][splits][qn][dp + 1]
+    const long per_tile = ((long)S * npad + OZ_SLOTS * 8 + (long)OZ_MAX_SPLITS * (dp + 1) * 8) * batch * OZ_QT;
+    const long tiles_total = (q + OZ_QT - 1) / OZ_QT;
+    const long tcap = work_bytes / per_tile;
+    GPK_ARG(tcap >= 1, "scratch too small (see gpk_predict_i8_work_bytes)");
+    // sub-chunks of `tsub` query tiles; pipelined = the front end of sub-chunk c + 1 runs on the library's side stream
+    // (co-resident 4-warp CTAs, FP64 pipe) while the tensor pipe contracts sub-chunk c, scratch split in two halves
+    const OzPlan plan = oz_plan(tiles_total, batch, npad, S, tcap);
+    const long qc = plan.tsub * OZ_QT;
+    const int nbuf = plan.pipelined ? 2 : 1;
+    int8_t* eimg[2]; double* part[2]; double* mjp[2];
+    {
+        char* w = (char*)work;
+        for (int b = 0; b < nbuf; b++) { eimg[b] = (int8_t*)w; w += (long)batch * S * qc * npad; }
+        for (int b = 0; b < nbuf; b++) { part[b] = (double*)w; w += (long)batch * OZ_SLOTS * qc * 8; }
+        for (int b = 0; b < nbuf; b++) { mjp[b] = (double*)w; w += (long)batch * OZ_MAX_SPLITS * qc * (dp + 1) * 8; }
+    }
     const int esz = dtype == 0 ? 4 : 8;
     cudaStream_t st = (cudaStream_t)stream;
-    for (long q0 = 0; q0 < q; q0 += qc) {
+    OzSide* sd = nullptr;
+    if (plan.pipelined) {
+        GPK_TRY(oz_side_prepare());
+        sd = &g_oz_side[current_device()];
+    }
+    const long nchunks = (tiles_total + plan.tsub - 1) / plan.tsub;
+    auto front = [&](long c, bool co, cudaStream_t s_) -> int {
+        const long q0 = c * qc;
         const long qn = (q - q0 < qc) ? (q - q0) : qc;
-        const long qp = (qn + OZ_QT - 1) / OZ_QT * OZ_QT;
-        const long qtiles = qp / OZ_QT;
-        const int pieces = oz_num_pieces(qtiles * batch, npad / (2 * OZ_WB));
+        const long qtiles = (qn + OZ_QT - 1) / OZ_QT;
         OzFrontArgs a{};
         a.Z = (const char*)Z + q0 * ldz * esz; a.ldz = ldz; a.q = qn; a.strideZ = strideZ;
         a.X = X; a.ldx = ldx; a.n = n; a.strideX = strideX;
         a.alpha = alpha; a.stride_alpha = stride_alpha;
         a.d = d; a.hyp = hyp;
-        a.img = eimg; a.strideE = (long)S * qc * npad;
+        a.img = eimg[c % nbuf]; a.strideE = (long)S * qc * npad;
         a.kb_total = (int)(npad / OZ_BK);
-        const int ns = oz_front_splits(qtiles * batch, a.kb_total);
-        a.kb_per_cta = (a.kb_total + ns - 1) / ns;
-        a.mj_part = mjp; a.stride_mj = (long)OZ_MAX_SPLITS * qc * (dp + 1);
+        a.mj_part = mjp[c % nbuf]; a.stride_mj = (long)OZ_MAX_SPLITS * qc * (dp + 1);
+        a.tdbg = (co && c == 1) ? g_oz_tdbg_front : nullptr;
         void* mout = mj ? (char*)mean + q0 * esz : nullptr;
         void* jout = mj ? (char*)jac + q0 * ldj * esz : nullptr;
-        if (dtype == 0) GPK_TRY(oz_front_dispatch<float>(a, S, mj, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
-        else GPK_TRY(oz_front_dispatch<double>(a, S, mj, ns, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, st));
-        // mean and Jacobian are final here: a caller that passed an event can start copying them out while the
-        // variance contraction of the last chunk runs
-        if (mj && mj_done_event && q0 + qc >= q) GPK_CUDA(cudaEventRecord((cudaEvent_t)mj_done_event, st));
-        GPK_TRY(oz_var_partials(eimg, a.strideE, Wimg, strideW, S_img, wscale, stride_ws, hyp, npad, qp, S, part, qc,
-                                (long)OZ_SLOTS * qc, pieces, batch, nullptr, stream));
+        if (dtype == 0) GPK_TRY(oz_front_dispatch<float>(a, S, mj, co, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, s_));
+        else GPK_TRY(oz_front_dispatch<double>(a, S, mj, co, qtiles, batch, mout, stride_mean, jout, ldj, stride_jac, s_));
+        // mean and Jacobian are final after the last sub-chunk's front end: a caller that passed an event can start
+        // copying them out while the variance contraction of the last sub-chunk runs
+        if (mj && mj_done_event && c + 1 == nchunks) GPK_CUDA(cudaEventRecord((cudaEvent_t)mj_done_event, s_));
+        return 0;
+    };
+    // experiments only: per-kernel times of the first sub-chunks on both streams (synchronises the stream)
+    const bool trace = getenv("GPK_OZ_PIPE_TRACE") != nullptr;
+    cudaEvent_t tev[8][4] = {};
+    if (trace) {
+        for (auto& r : tev) for (auto& e : r) cudaEventCreate(&e);
+        cudaMalloc(&g_oz_tdbg_gemm, 2 * 160 * 8); cudaMalloc(&g_oz_tdbg_front, 2 * 160 * 8);
+        cudaMemset(g_oz_tdbg_gemm, 0, 2 * 160 * 8); cudaMemset(g_oz_tdbg_front, 0, 2 * 160 * 8);
+    }
+    unsigned long long* const tdbg_gemm = g_oz_tdbg_gemm;
+    for (long c = 0; c < nchunks; c++) {
+        // first sub-chunk, or not pipelined: nothing to overlap the front end with -> the stand-alone 8-warp kernel
+        if (c == 0 || !plan.pipelined) GPK_TRY(front(c, false, st));
+        const long q0 = c * qc;
+        const long qn = (q - q0 < qc) ? (q - q0) : qc;
+        const long qp = (qn + OZ_QT - 1) / OZ_QT * OZ_QT;
+        const int pieces = oz_num_pieces(qp / OZ_QT * batch, npad / (2 * OZ_WB));
+        if (plan.pipelined && c + 1 < nchunks) {
+            // sub-chunk c + 1's front end: its buffers were last read by the contraction of sub-chunk c - 1
+            // (c = 0: ordered after the first front end, so the two front kernels do not compete)
+            cudaEvent_t gate = c == 0 ? sd->ev_fork : sd->ev_gemm[(c - 1) & 1];
+            if (c == 0) GPK_CUDA(cudaEventRecord(gate, st));
+            GPK_CUDA(cudaStreamWaitEvent(sd->side, gate, 0));
+            if (trace && c < 8) cudaEventRecord(tev[c][0], sd->side);
+            GPK_TRY(front(c + 1, true, sd->side));
+            if (trace && c < 8) cudaEventRecord(tev[c][1], sd->side);
+            GPK_CUDA(cudaEventRecord(sd->ev_front[(c + 1) & 1], sd->side));
+        }
+        if (plan.pipelined && c > 0) GPK_CUDA(cudaStreamWaitEvent(st, sd->ev_front[c & 1], 0));
+        if (trace && c < 8) cudaEventRecord(tev[c][2], st);
+        g_oz_tdbg_gemm = c == 0 ? tdbg_gemm : nullptr;      // per-CTA timers of the first contraction only
+        GPK_TRY(oz_var_partials(eimg[c % nbuf], (long)S * qc * npad, Wimg, strideW, S_img, wscale, stride_ws, hyp, npad, qp, S,
+                                part[c % nbuf], qc, (long)OZ_SLOTS * qc, pieces, batch, nullptr, stream));
+        if (trace && c < 8) cudaEventRecord(tev[c][3], st);
+        if (plan.pipelined && c + 2 < nchunks) GPK_CUDA(cudaEventRecord(sd->ev_gemm[c & 1], st));
         void* vout = (char*)var + q0 * esz;
-        GPK_TRY(gpk_var_finalize(dtype, part, qc, (long)OZ_SLOTS * qc, 2 * pieces, qn, hyp, vout, stride_var, batch, stream));
+        GPK_TRY(gpk_var_finalize(dtype, part[c % nbuf], qc, (long)OZ_SLOTS * qc, 2 * pieces, qn, hyp, vout, stride_var, batch, stream));
+    }
+    if (trace) {
+        cudaStreamSynchronize(st);
+        for (long c = 0; c < nchunks && c < 8; c++) {
+            float tf = -1.f, tg = -1.f, lag = -1.f;
+            if (plan.pipelined && c + 1 < nchunks) { cudaEventElapsedTime(&tf, tev[c][0], tev[c][1]); cudaEventElapsedTime(&lag, tev[c][2], tev[c][1]); }
+            cudaEventElapsedTime(&tg, tev[c][2], tev[c][3]);
+            fprintf(stderr, "[oz trace] chunk %ld: contraction %.4f ms, co front of chunk %ld %.4f ms (ends %.4f ms after the contraction starts)\n",
+                    c, tg, c + 1, tf, lag);
+        }
+        for (auto& r : tev) for (auto& e : r) cudaEventDestroy(e);
+        unsigned long long hg[320], hf[320];
+        cudaMemcpy(hg, tdbg_gemm, sizeof(hg), cudaMemcpyDeviceToHost);
+        cudaMemcpy(hf, g_oz_tdbg_front, sizeof(hf), cudaMemcpyDeviceToHost);
+        unsigned long long g0 = ~0ull, g1 = 0;
+        for (int i = 0; i < 160; i++) if (hg[2 * i]) { if (hg[2 * i] < g0) g0 = hg[2 * i]; if (hg[2 * i + 1] > g1) g1 = hg[2 * i + 1]; }
+        fprintf(stderr, "[oz trace] contraction 0 CTAs: first start 0, last end %.1f us\n", (g1 - g0) * 1e-3);
+        int nf = 0, early = 0; double smin = 1e30, smax = -1e30, emin = 1e30, emax = -1e30, dsum = 0;
+        for (int i = 0; i < 160; i++) if (hf[2 * i]) {
+            const double s0 = ((double)hf[2 * i] - (double)g0) * 1e-3, e0 = ((double)hf[2 * i + 1] - (double)g0) * 1e-3;
+            nf++; if (s0 < (g1 - g0) * 0.5e-3) early++;
+            if (s0 < smin) smin = s0; if (s0 > smax) smax = s0; if (e0 < emin) emin = e0; if (e0 > emax) emax = e0; dsum += e0 - s0;
+        }
+        fprintf(stderr, "[oz trace] co front 1: %d CTAs, %d started in the contraction's first half; start %.1f .. %.1f us, end %.1f .. %.1f us, mean duration %.1f us\n",
+                nf, early, smin, smax, emin, emax, nf ? dsum / nf : 0.0);
+        cudaFree(tdbg_gemm); cudaFree(g_oz_tdbg_front);
+        g_oz_tdbg_gemm = g_oz_tdbg_front = nullptr;
     }
     return 0;
 }

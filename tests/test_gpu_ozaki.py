@@ -128,3 +128,41 @@ def test_tensor_core_accumulators_exact(env, S):
     refd = (Vd * Vd).sum(1)
     tol = {4: 1e-5, 5: 1e-7, 6: 1e-10}[S]
     assert (tot[:q] - refd).abs().max() <= tol * refd.abs().max()
+
+
+@pytest.mark.parametrize("dtype,want_mj", [(F64, True), (torch.float32, True), (F64, False)])
+def test_pipelined_step_matches_sequential(env, dtype, want_mj, monkeypatch):
+    """gpk_predict_i8's pipeline (front end of sub-chunk c+1 as co-resident 4-warp CTAs on the side stream while
+    oz_var_kernel contracts sub-chunk c) against the one-chunk sequential step and the oracle; ragged last sub-chunk,
+    3 GPs, sub-chunks of 1, 2 and 3 query tiles."""
+    _lib, E, o, dev = env
+    n, d, q, P = 700, 16, 1100, 3
+    p = o.synthetic_problem(n, d, q, p=P, seed=11)
+    gb = E.fit_batch(p["X"].to(dev), p["Y"].to(dev), p["ell"], p["sf2"], p["noise"], digits=5)
+    Z = p["Z"].to(dev).to(dtype)
+    monkeypatch.setenv("GPK_OZ_PIPELINE", "0")
+    ref = E.predict(gb, Z, want_mean_jac=want_mj)
+    torch.cuda.synchronize()
+    tol = 1e-12 if dtype == F64 else 1e-5
+    # sequential chunks that fit a small scratch budget (3 query tiles per chunk)
+    small = _lib.load().gpk_predict_i8_work_bytes(3 * 128, gb.npad, d, 5, P)
+    got = E.predict(gb, Z, want_mean_jac=want_mj, var_work_bytes=small)
+    torch.cuda.synchronize()
+    for a, b in zip(got, ref):
+        assert (a is None and b is None) or o.rel_err(a.cpu().double(), b.cpu().double()) < tol
+    for tsub in (1, 2, 3):
+        monkeypatch.setenv("GPK_OZ_PIPELINE", "2")
+        monkeypatch.setenv("GPK_OZ_PIPE_TSUB", str(tsub))
+        for rep in range(2):                                   # twice: the side stream's events are reused
+            got = E.predict(gb, Z, want_mean_jac=want_mj)
+            torch.cuda.synchronize()
+            for a, b in zip(got, ref):
+                if b is None:
+                    assert a is None
+                    continue
+                assert o.rel_err(a.cpu().double(), b.cpu().double()) < tol
+    if want_mj and dtype == F64:
+        st = o.fit_state(p["X"], p["Y"][:, 0], p["ell"], p["sf2"], p["noise"])
+        m_ref, v_ref, j_ref = o.predict(p["Z"], p["X"], p["ell"], p["sf2"], st["L"], st["alpha"])
+        assert o.rel_err(got[0][0].cpu(), m_ref) < 1e-6 and o.rel_err(got[1][0].cpu(), v_ref) < 1e-6
+        assert o.rel_err(got[2][0].cpu(), j_ref) < 1e-6
