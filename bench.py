@@ -65,6 +65,7 @@ def parse_args():
     ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
     ap.add_argument("--queries", type=int, default=0, help="global queries per step (default: the workload's)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--equal-shards", action="store_true", help="N > 1: equal query blocks instead of speed-weighted ones")
     ap.add_argument("--no-extras", action="store_true", help="skip the other configs / side measurements")
     return ap.parse_args()
 
@@ -375,12 +376,31 @@ def run_b200(args):
     assert check < 1e-11, f"sharded prediction deviates from the unsharded one: {check:.3e}"
     del full, gathered
 
+    bounds = [S.shard_bounds(q_total, world, r) for r in range(world)]
+
     def step():
-        return S.predict_sharded(lambda z: E.predict(gb, z), Zd)
+        return S.predict_sharded(lambda z: E.predict(gb, z), Zd, bounds=bounds)
 
     # ---- value: inputs resident in HBM ----------------------------------------------------------
     for _ in range(warmup):
         step()
+    # Speed-weighted blocks: the GPUs of one box hold different clocks under the power cap (the step ends with the
+    # slowest), so every rank times TWO more warm-up steps on its equal block (rank-local CUDA events), the speeds are
+    # all-gathered once -- outside the step -- and the blocks are re-cut in proportion (sharding.weighted_bounds,
+    # 128-query granularity).  The timed steps still contain no collective.
+    shard_weights = None
+    if world > 1 and not args.equal_shards:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ctx.barrier()
+        e0.record()
+        step()
+        step()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        shard_weights = S.measured_weights(2 * (hi - lo), e0.elapsed_time(e1) * 1e-3)
+        bounds = S.weighted_bounds(q_total, shard_weights, 128)
+        lo, hi = bounds[rank]
+        step()                                         # one warm-up step on the new blocks
     ctx.barrier()
     sampler = ClockSampler(dev.index).start()
     ctx.lib.gpk_reset_launch_count()
@@ -401,7 +421,7 @@ def run_b200(args):
         def fn(z_host):
             out_h[0] = predict_host(gb, z_host, out_h[0])      # returns after the results are on the host
             return out_h[0]
-        return S.predict_sharded(fn, Zh)
+        return S.predict_sharded(fn, Zh, bounds=bounds)
 
     for _ in range(2):
         e2e_step()
@@ -424,7 +444,11 @@ def run_b200(args):
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_string(args.workload, n_train, q_total), "global_queries": q_total,
-                   "queries_per_rank": hi - lo,
+                   "queries_per_rank": [b[1] - b[0] for b in bounds],
+                   "shard_speeds_preds_per_s": shard_weights,
+                   "sharding": ("equal contiguous blocks" if shard_weights is None else
+                                "contiguous blocks proportional to each rank's measured speed on two warm-up steps "
+                                "(sharding.measured_weights + weighted_bounds, 128-query granularity)"),
                    "parallelism": f"sharding.predict_sharded: contiguous query blocks over {world} rank(s), fitted state "
                                   "fitted on rank 0 and replicated (sharding.replicate_batch), no collective in the step",
                    "l2": "flushed (256 MB write) before every timed step; the step's operands (W image "

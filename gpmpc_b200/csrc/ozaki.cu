@@ -78,6 +78,9 @@ oz_slice_w_kernel(const double* __restrict__ W, long ldw, int npad, const double
 // the balanced base-256 digits into the plain BYTES of that integer (two's complement = byte ^ 0x80), and
 // byte permutes -- the FP64 pipe only sees the GEMMs, exp, and the mean accumulation.
 // ------------------------------------------------------------------------------------------------
+#ifndef OZ_FRONT_UNROLL
+#define OZ_FRONT_UNROLL 1
+#endif
 struct OzFrontArgs {
     const void* Z; long ldz, q, strideZ;
     const double* X; long ldx, n, strideX;
@@ -127,6 +130,7 @@ __device__ __forceinline__ void oz_front_item(const OzFrontArgs& a, OzFrontSmem<
     constexpr int DPB = OzFrontSmem<DP, MJ>::DPB, NB = DPB / 8;   // GEMM 2 column blocks
     constexpr int LDA = OzFrontSmem<DP, MJ>::LDA, LDB = OzFrontSmem<DP, MJ>::LDB;
     constexpr int NT = 32 * NW;                          // threads of the CTA
+    constexpr int UNIT_UNROLL = OZ_FRONT_UNROLL;
     constexpr int PASSES = 4 * OZ_BK / NT;               // staging: 4 threads per training point, NT / 4 points per pass
     double* XsA = sm.XsA; double* XsB = sm.XsB; double* ex = sm.ex; double* as = sm.as;
     const double* exp_tab = sm.exp_tab;
@@ -212,7 +216,7 @@ __device__ __forceinline__ void oz_front_item(const OzFrontArgs& a, OzFrontSmem<
         __syncthreads();
         if (kb + 1 < kb1) prefetch(kb + 1);              // in flight during the compute below
         int8_t* out = a.img + gp * a.strideE + ((long)qt * a.kb_total + kb) * S * OZ_A_SLICE;
-#pragma unroll 1
+#pragma unroll UNIT_UNROLL
         for (int unit = 0; unit < OZ_BK / 16; unit++) {
             const int p0 = unit * 16 + 4 * t;            // this thread's four consecutive training points
             double b1[2][KS];

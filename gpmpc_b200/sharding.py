@@ -40,6 +40,36 @@ def shard_bounds(n: int, world: int, rank: int) -> tuple[int, int]:
     return lo, lo + base + (1 if rank < extra else 0)
 
 
+def weighted_bounds(n: int, weights: Sequence[float], granularity: int = 1) -> list[tuple[int, int]]:
+    """Contiguous blocks [lo, hi) of n items for ranks whose measured speeds are `weights` (items/s, any scale): rank r
+    gets a share proportional to weights[r], cut at multiples of `granularity` (the 128-query tile of the prediction
+    kernels) except for the last block.  Power-capped GPUs of one box hold different clocks on the same kernel
+    (1.17-1.34 GHz at 8 GPUs, profiles/README_r02.md); with equal blocks the step ends when the slowest rank does."""
+    world = len(weights)
+    assert world >= 1 and n >= 0 and granularity >= 1 and all(w > 0 for w in weights)
+    total = float(sum(weights))
+    cuts = [0]
+    acc = 0.0
+    for r in range(world - 1):
+        acc += weights[r]
+        c = int(round(n * acc / total / granularity)) * granularity
+        cuts.append(min(max(c, cuts[-1]), n))
+    cuts.append(n)
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+def measured_weights(items_local: int, seconds_local: float, group=None) -> list[float]:
+    """All-gather of every rank's measured speed (items/s) on its current block: one small collective OUTSIDE the
+    prediction step, e.g. after a warm-up step; feed the result to weighted_bounds."""
+    rank, world = world_info(group)
+    mine = float(items_local) / max(float(seconds_local), 1e-12)
+    if world == 1:
+        return [mine]
+    out = [None] * world
+    dist.all_gather_object(out, mine, group=group)
+    return [float(x) for x in out]
+
+
 def gp_owner(p: int, world: int) -> int:
     """Rank that owns output GP p (round robin)."""
     return p % world
@@ -52,8 +82,10 @@ def owned_gps(n_gps: int, world: int, rank: int) -> list[int]:
 # --------------------------------------------------------------------------------------------------
 # query sharding
 # --------------------------------------------------------------------------------------------------
-def predict_sharded(predict_fn: Callable, Z: torch.Tensor, *, gather: bool = False, group=None):
-    """Each rank predicts its contiguous block of the global query batch Z (Q,d).
+def predict_sharded(predict_fn: Callable, Z: torch.Tensor, *, gather: bool = False, group=None,
+                    bounds: Sequence[tuple[int, int]] | None = None):
+    """Each rank predicts its contiguous block of the global query batch Z (Q,d): equal blocks (shard_bounds), or the
+    blocks `bounds` (one (lo, hi) per rank, e.g. weighted_bounds from measured speeds; must be identical on all ranks).
 
     predict_fn(Z_local) -> tuple of tensors whose query axis is dim 1 for 2-D+ outputs shaped (B,q,...)
     (what engine.predict returns: mean (B,q), var (B,q), jac (B,q,d)).  Returns (lo, hi, outputs).  With
@@ -61,12 +93,14 @@ def predict_sharded(predict_fn: Callable, Z: torch.Tensor, *, gather: bool = Fal
     in the original order; otherwise nothing is communicated.
     """
     rank, world = world_info(group)
-    lo, hi = shard_bounds(Z.shape[0], world, rank)
+    sizes = [shard_bounds(Z.shape[0], world, r) for r in range(world)] if bounds is None else [tuple(b) for b in bounds]
+    assert len(sizes) == world and sizes[0][0] == 0 and sizes[-1][1] == Z.shape[0]
+    assert all(sizes[r][1] == sizes[r + 1][0] for r in range(world - 1)), "blocks must tile the batch in rank order"
+    lo, hi = sizes[rank]
     outs = predict_fn(Z[lo:hi])
     if not gather or world == 1:
         return lo, hi, outs
     gathered = []
-    sizes = [shard_bounds(Z.shape[0], world, r) for r in range(world)]
     qmax = max(h - l for l, h in sizes)
     for t in outs:
         if t is None:

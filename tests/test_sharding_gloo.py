@@ -23,6 +23,22 @@ def test_shard_bounds_cover_everything():
             assert max(sizes) - min(sizes) <= 1
 
 
+def test_weighted_bounds_follow_measured_speeds():
+    # equal speeds -> equal tile-aligned blocks; a slow rank gets proportionally fewer queries; blocks always tile [0, n)
+    assert S.weighted_bounds(1024, [1.0, 1.0], 128) == [(0, 512), (512, 1024)]
+    b = S.weighted_bounds(1048576, [1.34, 1.17, 1.30, 1.25, 1.2, 1.33, 1.28, 1.22], 128)
+    assert b[0][0] == 0 and b[-1][1] == 1048576 and all(b[i][1] == b[i + 1][0] for i in range(7))
+    assert all(l % 128 == 0 for l, _ in b)
+    sizes = [h - l for l, h in b]
+    w = [1.34, 1.17, 1.30, 1.25, 1.2, 1.33, 1.28, 1.22]
+    t = [sz / wi for sz, wi in zip(sizes, w)]
+    assert max(t) / min(t) < 1.002                      # equal finishing times to within a tile
+    for n in (0, 1, 100, 129):                          # degenerate sizes: still a partition, empty blocks allowed
+        bb = S.weighted_bounds(n, [3.0, 1.0, 2.0], 128)
+        assert bb[0][0] == 0 and bb[-1][1] == n and all(bb[i][1] == bb[i + 1][0] and bb[i][0] <= bb[i][1] for i in range(2))
+    assert S.measured_weights(100, 2.0) == [50.0]      # single process: no process group needed
+
+
 def test_gp_ownership_round_robin():
     assert [S.gp_owner(p, 8) for p in range(8)] == list(range(8))
     assert S.owned_gps(3, 2, 0) == [0, 2] and S.owned_gps(3, 2, 1) == [1]
@@ -68,6 +84,17 @@ def _worker(rank, world, port, q_total):
         # --- with gather: everything, original order, on every rank (ragged shards when q_total is odd)
         lo, hi, outs = S.predict_sharded(predict_fn, Z, gather=True)
         assert (lo, hi) == (0, q_total)
+        for a, b in zip(outs, full):
+            assert torch.equal(a, b)
+        # --- speed-weighted blocks (rank 1 three times as fast): same results, same order, one small all-gather outside
+        w = S.measured_weights(10 if rank == 0 else 30, 1.0)
+        assert w == [10.0, 30.0]
+        wb = S.weighted_bounds(q_total, w, 1)
+        lo, hi, outs = S.predict_sharded(predict_fn, Z, bounds=wb)
+        assert (lo, hi) == wb[rank] and wb[0][1] == round(q_total * 0.25)
+        for a, b in zip(outs, full):
+            assert torch.equal(a, b[:, lo:hi])
+        lo, hi, outs = S.predict_sharded(predict_fn, Z, gather=True, bounds=wb)
         for a, b in zip(outs, full):
             assert torch.equal(a, b)
         # --- row-split gradient trace: sum of per-rank row blocks == full trace
