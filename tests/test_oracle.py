@@ -7,6 +7,7 @@ finite differences, analytic known-answer cases, and the committed fixtures in t
 """
 import math
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -308,3 +309,51 @@ def test_stage_linearisation_matches_finite_differences_and_plain_rk4():
     # hover: thrust command (g - b) / a keeps the vertical acceleration at zero
     xh, uh = torch.zeros(12, dtype=torch.float64), torch.tensor([(9.81 - prior[1]) / prior[0], 0, 0, 0], dtype=torch.float64)
     assert float(o.stage_f_disc(xh, uh, prior, zero, dt).abs().max()) < 1e-15
+
+
+# ---- rows a7-a9 against an INDEPENDENT third-party implementation (scikit-learn GPR; tests/golden/make_golden_sklearn.py) ---
+SK = ["sk_d1_n15", "sk_d3_n45", "sk_d16_n300"]
+
+
+def _oracle_log_gradient(X, y, ell, sf2, noise):
+    """d log p(y|X) / d log(sf2, ell_1..d, noise) from the oracle's closed-form raw-parameter gradient."""
+    n = X.shape[0]
+    raw_noise = o.inv_softplus(torch.tensor([noise - o.NOISE_FLOOR], dtype=torch.float64))
+    raw_sf2 = o.inv_softplus(torch.tensor(sf2, dtype=torch.float64))
+    raw_ell = o.inv_softplus(ell.reshape(1, -1))
+    loss, gn, gs, gl = o.loss_and_grad(X, y, raw_noise, raw_sf2, raw_ell)
+    # loss = -lml / n ; d/d theta = (d/d raw) / sigmoid(raw) ; d/d log theta = theta d/d theta
+    d_noise = -n * gn / torch.sigmoid(raw_noise) * noise
+    d_sf2 = -n * gs / torch.sigmoid(raw_sf2) * sf2
+    d_ell = -n * gl / torch.sigmoid(raw_ell) * ell.reshape(1, -1)
+    return -n * float(loss), torch.cat([d_sf2.reshape(1), d_ell.reshape(-1), d_noise.reshape(1)])
+
+
+@pytest.mark.parametrize("name", SK)
+def test_oracle_matches_scikit_learn_gpr(name):
+    """Exact log marginal likelihood, its gradient, posterior mean and predictive variance against scikit-learn's
+    GaussianProcessRegressor (sf2 * RBF(ARD) + White) on the committed fixtures: an implementation that shares no code
+    with the oracle.  gpytorch's ExactMarginalLogLikelihood (gp.py:57) is this lml divided by N."""
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    X, y, Z, ell = (torch.from_numpy(g[k]) for k in ("X", "y", "Z", "ell"))
+    sf2, noise, n = float(g["sf2"]), float(g["noise"]), X.shape[0]
+    lml, grad = _oracle_log_gradient(X, y, ell, sf2, noise)
+    assert abs(lml - float(g["lml"])) < 1e-9 * abs(float(g["lml"]))
+    assert abs(float(o.mll_per_n(X, y, ell, sf2, noise)) * n - float(g["lml"])) < 1e-9 * abs(float(g["lml"]))
+    assert o.rel_err(grad, g["grad_log"]) < 1e-7
+    st = o.fit_state(X, y, ell, sf2, noise)
+    mean, var, _ = o.predict(Z, X, ell, sf2, st["L"], st["alpha"])
+    assert o.rel_err(mean, g["mean"]) < 1e-8
+    assert float(((var + noise) - torch.from_numpy(g["var_y"])).abs().max() / torch.from_numpy(g["var_y"]).abs().min()) < 1e-6
+
+
+def test_sklearn_fixtures_regenerate_when_sklearn_is_present():
+    """The committed sk_*.npz are what scikit-learn computes here (skipped where scikit-learn is not installed)."""
+    pytest.importorskip("sklearn")
+    sys.path.insert(0, GOLD)
+    import make_golden_sklearn as mk
+
+    g = np.load(os.path.join(GOLD, "sk_d3_n45.npz"))
+    lml, grad, mean, var_y = mk.sklearn_gp(g["X"], g["y"], g["Z"], g["ell"], float(g["sf2"]), float(g["noise"]))
+    assert abs(lml - float(g["lml"])) < 1e-10 * abs(lml) and np.abs(grad - g["grad_log"]).max() < 1e-8 * np.abs(grad).max()
+    assert np.abs(mean - g["mean"]).max() < 1e-10 and np.abs(var_y - g["var_y"]).max() < 1e-10
