@@ -114,143 +114,219 @@ static GemmParams gemm_args(const double* A, long lda, const double* B, long ldb
 // ------------------------------------------------------------------------------------------------
 // 128x128 leaf: Cholesky of a diagonal block (one CTA) + inverse of its factor (16 CTAs)
 // ------------------------------------------------------------------------------------------------
-constexpr int P_N = 128, P_LD = 129, P_B = 8, P_NB = P_N / P_B, P_THREADS = 160;
-// shared memory of the Cholesky kernel: diagonal blocks of L (row-major, P_LD) | 1/l_jj | current panel (column-major,
-// permuted)
-constexpr int P_SMEM = (P_N * P_LD + P_N + P_B * P_N) * 8;
-// position of element R = 8 t + c inside a 128-vector read as double2 pairs by 16 consecutive block indices t:
-// pair p = c / 2 of block t sits at doubles [32 p + 2 t, 32 p + 2 t + 1]
-__device__ __forceinline__ int p_perm(int R) { return ((R & 7) >> 1) * 32 + (R >> 3) * 2 + (R & 7 & 1); }
+constexpr int P_N = 128, P_LD = 129, P_B = 8, P_NB = P_N / P_B;
 
-// Thread -> 8x8 block of the lower triangle (136 blocks, 160 threads).  Warps 0-3 (one per SM sub-partition) share
-// the blocks that take part in the rank-8 updates, dealt round-robin so that every step keeps the four warps evenly
-// loaded; warp 4 holds the 16 blocks that never take part in them (block column 0).
-__device__ __forceinline__ void p_map1(int t, int& ty, int& tx) {
-    const int w = t >> 5, l = t & 31;
-    ty = tx = -1;
-    if (w == 4) { if (l < 16) { ty = l; tx = 0; } return; }
-    const int i = l * 4 + w;                  // index into the blocks with tx >= 1, ordered by tx descending
-    if (i >= 120) return;
+// Cholesky of a 128 x 128 leaf, blocked right-looking with block size 8 (16 block steps), rank-8 updates on the FP64
+// tensor pipe (DMMA m8n8k4).  Round 1's leaf kept one 8 x 8 block per THREAD (SIMT DFMAs): a clock64 trace
+// (profiles/pipeline_r02.md) showed 2200 clocks per rank-8 update and 2270 per panel step -- operand-fresh DFMAs issue
+// every ~4 clocks per sub-partition and from block step 8 on most lanes idle -- 47 us per leaf.  Here a
+// WARP owns whole 8 x 8 blocks in the DMMA accumulator layout (lane l holds [l/4][2(l%4)], [l/4][2(l%4)+1]), so the
+// update of a block uses all 32 lanes and every decision is warp-uniform.  Nine warps:
+//   warp 8 (diagonal warp) owns the 16 diagonal blocks.  Step kb: it parks block kb in shared memory, lane 0 factors
+//       it (8 x 8 Cholesky in registers, 1/sqrt by MUFU + two Newton steps), publishes L_kk and 1 / l_jj and ARRIVES
+//       on barrier 1; it then brings its later diagonal blocks up to date with the PREVIOUS panel (lazily: nobody
+//       waits for that), waits for the panel of this step (barrier 2) and updates block kb + 1 first;
+//   warps 0-7 (workers) own the 120 off-diagonal blocks, dealt round-robin in descending block-column order (block
+//       i -> warp i % 8, slot i / 8: the blocks a step touches are a prefix, every warp has at most two panel blocks).
+//       Step kb: park the panel blocks (block column kb) in the panel buffer, wait for L_kk (barrier 1), 16 lanes take
+//       one panel row each and do the forward substitution L_ik = A_ik L_kk^-T (36-deep FMA chain, all rows in
+//       parallel), write it to the panel [block][row][k] (row stride 12 doubles: conflict-free fragment reads) and to
+//       HBM, barrier 2, then A_ic -= L_ik L_ck^T = 2 DMMAs per trailing block, four blocks per basic block.
+// So the serial part of a step is max(diagonal factor, trailing updates) + substitution, not their sum; the panel
+// buffer alternates between two copies because the diagonal warp reads the previous one a step late.
+constexpr int PM_WORKERS = 8, PM_THREADS = 32 * (PM_WORKERS + 1), PM_SLOTS = 16, PM_LD = 12;
+__device__ __forceinline__ void pm_slot_block(int w, int s, int& ty, int& tx) {
+    const int i = (s < 15 ? s : 14) * PM_WORKERS + w;   // < 120, off-diagonal blocks ordered by tx descending (slot 15 unused)
     int m = 0;
-    while ((m + 1) * (m + 2) / 2 <= i) m++;   // tx = 15 - m has m + 1 blocks
-    tx = 15 - m;
-    ty = tx + (i - m * (m + 1) / 2);
+    while ((m + 1) * (m + 2) / 2 <= i) m++;   // tx = 14 - m has m + 1 blocks
+    tx = 14 - m;
+    ty = tx + 1 + (i - m * (m + 1) / 2);
 }
-// Cholesky of a 128 x 128 leaf.  Each thread keeps one 8 x 8 block of the lower triangle in REGISTERS; blocked
-// right-looking with block size 8, so the 128 sequential pivots cost 16 block steps:  step kb: (a) the owner of the
-// diagonal block factors it in registers; (b) the blocks below it become L_ik = A_ik L_kk^-T by forward substitution
-// and are published as the panel; (c) every lower block right of the panel does A_ic -= L_ik L_ck^T (512 FMAs).
-// Two barriers per block step.  The inverse of the factor is a separate kernel (leaf_inv_kernel below).
-__global__ void __launch_bounds__(P_THREADS, 1)
-potf2_kernel(double* __restrict__ A, long lda, int* __restrict__ info, int row_offset) {
-    extern __shared__ __align__(16) double S[];
-    double* dinv = S + P_N * P_LD;                       // [128] 1 / l_jj
-    double* Pn = dinv + P_N;                             // [8][128] panel, Pn[k][perm(R)] = L[R][8 kb + k]
-    const int tid = threadIdx.x;
-    int ty, tx;
-    p_map1(tid, ty, tx);
-    int r0 = ty * 8, c0 = tx * 8;
-    double a[8][8];
-    if (ty >= 0) {
+__device__ __forceinline__ void pm_dmma(double (&c)[2], double a, double b) {
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+        : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+// 1 / sqrt(d) for a normal positive d: MUFU.RSQ64H seed (~2^-22) and two Newton steps y += y/2 (1 - d y^2)
+__device__ __forceinline__ double pm_rsqrt(double d) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;\n" : "=d"(y) : "d"(d));
 #pragma unroll
-        for (int r = 0; r < 8; r++)
-#pragma unroll
-            for (int c = 0; c < 8; c += 2) {
-                const double2 v = *reinterpret_cast<const double2*>(A + (long)(r0 + r) * lda + c0 + c);
-                a[r][c] = v.x;
-                a[r][c + 1] = v.y;
-            }
+    for (int it = 0; it < 2; it++) {
+        const double e = fma(-d * y, y, 1.0);
+        y = fma(0.5 * y, e, y);
     }
+    return y;
+}
+__device__ __forceinline__ void pm_bar_sync(int id) { asm volatile("bar.sync %0, %1;\n" ::"r"(id), "n"(PM_THREADS) : "memory"); }
+__device__ __forceinline__ void pm_bar_arrive(int id) { asm volatile("bar.arrive %0, %1;\n" ::"r"(id), "n"(PM_THREADS) : "memory"); }
 
-    // ---- phase 1: Cholesky (lower) ----
+__global__ void __launch_bounds__(PM_THREADS, 1)
+potf2_mma_kernel(double* __restrict__ A, long lda, int* __restrict__ info, int row_offset) {
+    __shared__ __align__(16) double Pn2[2][P_NB * 8 * PM_LD]; // panel (two buffers, by step parity): [block][row][k]
+    __shared__ __align__(16) double Dg[8 * PM_LD];            // the diagonal block, then its factor L_kk
+    __shared__ double Rv[8];                                  // 1 / l_jj of the current diagonal block
+    __shared__ __align__(16) double Cd[P_NB * 8 * PM_LD];     // the 16 diagonal blocks (diagonal warp only)
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int fr = lane >> 2, fq = lane & 3;                  // fragment row, position in the quad
+    const int fo = fr * PM_LD + fq;                           // fragment element offset inside a panel block
+    if (warp == PM_WORKERS) {
+        // ================= diagonal warp: its 16 blocks live in shared memory (run-time block index) =================
+        for (int j = 0; j < P_NB; j++)
+            *reinterpret_cast<double2*>(Cd + j * 8 * PM_LD + fr * PM_LD + 2 * fq) =
+                *reinterpret_cast<const double2*>(A + (long)(j * 8 + fr) * lda + j * 8 + 2 * fq);
+        __syncwarp();
+        auto update = [&](int j, const double* Pp) {          // C_jj -= L_jk L_jk^T with the panel Pp
+            double* cj = Cd + j * 8 * PM_LD + fr * PM_LD + 2 * fq;
+            const double* pr = Pp + j * 8 * PM_LD + fo;
+            const double v0 = pr[0], v1 = pr[4];
+            const double2 cv = *reinterpret_cast<const double2*>(cj);
+            double d[2] = {cv.x, cv.y};
+            pm_dmma(d, -v0, v0);
+            pm_dmma(d, -v1, v1);
+            *reinterpret_cast<double2*>(cj) = make_double2(d[0], d[1]);
+        };
 #pragma unroll 1
-    for (int kb = 0; kb < P_NB; kb++) {
-        if (ty == kb && tx == kb) {
-            // (a) 8 x 8 Cholesky in registers; 1/sqrt(d) by MUFU seed + Newton, l_jj = d / sqrt(d) corrected once
+        for (int kb = 0; kb < P_NB; kb++) {
+            double* Ck = Cd + kb * 8 * PM_LD;
+            if (lane == 0) {
+                double f[8][8];
 #pragma unroll
-            for (int j = 0; j < 8; j++) {
-                double d = a[j][j];
-                if (!(d > 0.0) || isinf(d)) {            // also catches NaN
-                    atomicCAS(info, 0, row_offset + kb * 8 + j + 1);
-                    d = 1.0;
-                }
-                const double rinv = rsqrt(d);
-                double rt = d * rinv;
-                rt = fma(fma(-rt, rt, d), 0.5 * rinv, rt);
-                a[j][j] = rt;
-                dinv[kb * 8 + j] = rinv;
+                for (int r = 0; r < 8; r++)
 #pragma unroll
-                for (int r = j + 1; r < 8; r++) a[r][j] *= rinv;
+                    for (int cc = 0; cc <= r; cc++) f[r][cc] = Ck[r * PM_LD + cc];
 #pragma unroll
-                for (int c = j + 1; c < 8; c++)
+                for (int j = 0; j < 8; j++) {
+                    double d = f[j][j];
+                    if (!(d >= 1e-290) || isinf(d)) {        // not positive (also NaN), or too small to invert
+                        atomicCAS(info, 0, row_offset + kb * 8 + j + 1);
+                        d = 1.0;
+                    }
+                    const double rinv = pm_rsqrt(d);
+                    double rt = d * rinv;
+                    rt = fma(fma(-rt, rt, d), 0.5 * rinv, rt);
+                    f[j][j] = rt;
+                    Rv[j] = rinv;
 #pragma unroll
-                    for (int r = c; r < 8; r++) a[r][c] = fma(-a[r][j], a[c][j], a[r][c]);
-            }
+                    for (int r = j + 1; r < 8; r++) f[r][j] *= rinv;
 #pragma unroll
-            for (int r = 0; r < 8; r++)
+                    for (int cc = j + 1; cc < 8; cc++)
 #pragma unroll
-                for (int c = 0; c < 8; c++) {
-                    const double v = c <= r ? a[r][c] : 0.0;
-                    S[(r0 + r) * P_LD + c0 + c] = v;
-                    if (c <= r) A[(long)(r0 + r) * lda + c0 + c] = v;
-                }
-        }
-        __syncthreads();
-        const bool panel = tx == kb && ty > kb;
-        if (panel) {
-            // (b) L_ik = A_ik L_kk^-T, column by column: l[r][c] = (a[r][c] - sum_{m<c} l[r][m] L_kk[c][m]) / L_kk[c][c]
-            // (the diagonal factor is fetched up front so that only the FMA chain is on the critical path)
-            const double* Lk = S + (kb * 8) * P_LD + kb * 8;
-            double lk[8][8], di[8];
-#pragma unroll
-            for (int c = 0; c < 8; c++) {
-                di[c] = dinv[kb * 8 + c];
-#pragma unroll
-                for (int m = 0; m < c; m++) lk[c][m] = Lk[c * P_LD + m];
-            }
-#pragma unroll
-            for (int c = 0; c < 8; c++) {
-#pragma unroll
-                for (int m = 0; m < c; m++)
-#pragma unroll
-                    for (int r = 0; r < 8; r++) a[r][c] = fma(-a[r][m], lk[c][m], a[r][c]);
-#pragma unroll
-                for (int r = 0; r < 8; r++) a[r][c] *= di[c];
-            }
-            const int pr = (r0 >> 3) * 2;        // p_perm(r0 + r) = (r >> 1) * 32 + pr + (r & 1)
-#pragma unroll
-            for (int r = 0; r < 8; r += 2)
-#pragma unroll
-                for (int c = 0; c < 8; c++)
-                    *reinterpret_cast<double2*>(Pn + c * P_N + (r >> 1) * 32 + pr) = make_double2(a[r][c], a[r + 1][c]);
-        }
-        __syncthreads();
-        if (panel) {
-            // off the critical path: the finished block goes back to global memory
-#pragma unroll
-            for (int r = 0; r < 8; r++)
-#pragma unroll
-                for (int c = 0; c < 8; c++) A[(long)(r0 + r) * lda + c0 + c] = a[r][c];
-        }
-        if (tx > kb && ty >= tx) {
-            // (c) trailing update of the lower blocks with the published panel
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                double lr[8], lc[8];
-#pragma unroll
-                for (int p2 = 0; p2 < 4; p2++) {
-                    const double2 v = *reinterpret_cast<const double2*>(Pn + k * P_N + p2 * 32 + ty * 2);
-                    lr[2 * p2] = v.x; lr[2 * p2 + 1] = v.y;
-                    const double2 w = *reinterpret_cast<const double2*>(Pn + k * P_N + p2 * 32 + tx * 2);
-                    lc[2 * p2] = w.x; lc[2 * p2 + 1] = w.y;
+                        for (int r = cc; r < 8; r++) f[r][cc] = fma(-f[r][j], f[cc][j], f[r][cc]);
                 }
 #pragma unroll
                 for (int r = 0; r < 8; r++)
 #pragma unroll
-                    for (int c = 0; c < 8; c++) a[r][c] = fma(-lr[r], lc[c], a[r][c]);
+                    for (int cc = 0; cc < 8; cc++) Dg[r * PM_LD + cc] = cc <= r ? f[r][cc] : 0.0;
+            }
+            __syncwarp();
+            __threadfence_block();
+            pm_bar_arrive(1);                                  // L_kk and 1 / l_jj are published
+            // the factored block goes back to global memory (lower triangle only, as before)
+            {
+                const double2 v = *reinterpret_cast<const double2*>(Dg + fr * PM_LD + 2 * fq);
+                double* dst = A + (long)(kb * 8 + fr) * lda + kb * 8 + 2 * fq;
+                if (2 * fq <= fr) dst[0] = v.x;
+                if (2 * fq + 1 <= fr) dst[1] = v.y;
+            }
+            pm_bar_sync(2);                                    // the panel of step kb is final
+            // block kb + 1 is the next one to be factored: this warp updates it itself, right away (the workers
+            // bring the later diagonal blocks up to date during their trailing updates)
+            if (kb + 1 < P_NB) update(kb + 1, Pn2[kb & 1]);
+            __syncwarp();
+        }
+        return;
+    }
+    double c[PM_SLOTS][2];
+    int sty[PM_SLOTS], stx[PM_SLOTS];
+#pragma unroll
+    for (int s = 0; s < PM_SLOTS; s++) {
+        pm_slot_block(warp, s, sty[s], stx[s]);
+        const double2 v = *reinterpret_cast<const double2*>(A + (long)(sty[s] * 8 + fr) * lda + stx[s] * 8 + 2 * fq);
+        c[s][0] = v.x; c[s][1] = v.y;
+    }
+    // ================= workers =================
+#pragma unroll 1
+    for (int kb = 0; kb < P_NB; kb++) {
+        double* Pn = Pn2[kb & 1];
+        // ---- (b) panel: this warp's (at most two) blocks of block column kb go to the panel buffer as they are ----
+        int pty0 = -1, pty1 = -1;
+#pragma unroll
+        for (int s = 0; s < 15; s++) {
+            if (stx[s] != kb) continue;
+            *reinterpret_cast<double2*>(Pn + (sty[s] * 8 + fr) * PM_LD + 2 * fq) = make_double2(c[s][0], c[s][1]);
+            if (pty0 < 0) pty0 = sty[s]; else pty1 = sty[s];
+        }
+        __syncwarp();
+        pm_bar_sync(1);                                        // L_kk and 1 / l_jj are published
+        {
+            // one row per lane: l[c] = (a[c] - sum_{m<c} l[m] L_kk[c][m]) / L_kk[c][c]
+            const int pty = (lane >> 3) == 0 ? pty0 : ((lane >> 3) == 1 ? pty1 : -1);
+            if (pty >= 0) {
+                double* row = Pn + (pty * 8 + (lane & 7)) * PM_LD;
+                double l[8];
+#pragma unroll
+                for (int cc = 0; cc < 8; cc += 2) {
+                    const double2 v = *reinterpret_cast<const double2*>(row + cc);
+                    l[cc] = v.x; l[cc + 1] = v.y;
+                }
+#pragma unroll
+                for (int cc = 0; cc < 8; cc++) {
+#pragma unroll
+                    for (int m = 0; m < cc; m++) l[cc] = fma(-l[m], Dg[cc * PM_LD + m], l[cc]);
+                    l[cc] *= Rv[cc];
+                }
+                double* gdst = A + (long)(pty * 8 + (lane & 7)) * lda + kb * 8;
+#pragma unroll
+                for (int cc = 0; cc < 8; cc += 2) {
+                    *reinterpret_cast<double2*>(row + cc) = make_double2(l[cc], l[cc + 1]);
+                    *reinterpret_cast<double2*>(gdst + cc) = make_double2(l[cc], l[cc + 1]);
+                }
             }
         }
-        // no barrier here: the panel is rewritten only after the next step's first barrier
+        pm_bar_sync(2);                                        // the panel of step kb is final
+        // ---- (c) trailing update: A_ic -= L_ik L_ck^T; the active slots are the prefix s < nact ----
+        {
+            const int nblk = (14 - kb) * (15 - kb) / 2;       // off-diagonal blocks with tx > kb
+            const int nact = nblk > warp ? (nblk - warp + PM_WORKERS - 1) / PM_WORKERS : 0;
+            {
+                // diagonal blocks j >= kb + 2 (shared memory; j % 8 == this warp): C_jj -= L_jk L_jk^T
+                const int j0 = warp + (warp >= ((kb + 2) & 7) ? 0 : 8) + ((kb + 2) & ~7);   // first j >= kb + 2 with j % 8 == warp
+                const bool on0 = j0 < P_NB, on1 = j0 + 8 < P_NB;
+                const int ja = on0 ? j0 : 0, jb = on1 ? j0 + 8 : 0;
+                double* ca = Cd + ja * 8 * PM_LD + fr * PM_LD + 2 * fq;
+                double* cb = Cd + jb * 8 * PM_LD + fr * PM_LD + 2 * fq;
+                const double a0 = on0 ? Pn[ja * 8 * PM_LD + fo] : 0.0, a1 = on0 ? Pn[ja * 8 * PM_LD + fo + 4] : 0.0;
+                const double b0 = on1 ? Pn[jb * 8 * PM_LD + fo] : 0.0, b1 = on1 ? Pn[jb * 8 * PM_LD + fo + 4] : 0.0;
+                if (on0) {                                     // warp-uniform
+                    const double2 va = *reinterpret_cast<const double2*>(ca);
+                    const double2 vb = *reinterpret_cast<const double2*>(cb);
+                    double da[2] = {va.x, va.y}, db[2] = {vb.x, vb.y};
+                    pm_dmma(da, -a0, a0);
+                    pm_dmma(db, -b0, b0);
+                    pm_dmma(da, -a1, a1);
+                    pm_dmma(db, -b1, b1);
+                    *reinterpret_cast<double2*>(ca) = make_double2(da[0], da[1]);
+                    if (on1) *reinterpret_cast<double2*>(cb) = make_double2(db[0], db[1]);
+                }
+            }
+#pragma unroll
+            for (int g4 = 0; g4 < 16; g4 += 4) {
+                if (g4 >= nact) break;
+                double fa[4][2], fb[4][2];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const bool on = g4 + u < nact;
+                    const double* pr = Pn + sty[g4 + u] * 8 * PM_LD + fo;
+                    const double* pc = Pn + stx[g4 + u] * 8 * PM_LD + fo;
+                    fa[u][0] = on ? -pr[0] : 0.0; fa[u][1] = on ? -pr[4] : 0.0;
+                    fb[u][0] = on ? pc[0] : 0.0;  fb[u][1] = on ? pc[4] : 0.0;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) pm_dmma(c[g4 + u], fa[u][0], fb[u][0]);
+#pragma unroll
+                for (int u = 0; u < 4; u++) pm_dmma(c[g4 + u], fa[u][1], fb[u][1]);
+            }
+        }
     }
 }
 
@@ -342,11 +418,10 @@ static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_of
     static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
     bool& attr_done = attr_dev[current_device()];
     if (!attr_done) {
-        GPK_CUDA(cudaFuncSetAttribute(potf2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM));
         GPK_CUDA(cudaFuncSetAttribute(leaf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PI_SMEM));
         attr_done = true;
     }
-    potf2_kernel<<<1, P_THREADS, P_SMEM, st>>>(A, lda, info, row_offset);
+    potf2_mma_kernel<<<1, PM_THREADS, 0, st>>>(A, lda, info, row_offset);
     GPK_LAUNCHED();
     leaf_inv_kernel<<<P_NB, PI_THREADS, PI_SMEM, st>>>(A, lda, Dinv);
     GPK_LAUNCHED();
