@@ -194,13 +194,15 @@ potf2_mma_kernel(double* __restrict__ A, long lda, int* __restrict__ info, int r
                 for (int r = 0; r < 8; r++)
 #pragma unroll
                     for (int cc = 0; cc <= r; cc++) f[r][cc] = Ck[r * PM_LD + cc];
+                // 1-based index of the first bad pivot, branch-free: the whole factorisation stays one basic block, so
+                // the next pivot's MUFU issues as soon as its operand is ready
+                int bad = 0;
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
                     double d = f[j][j];
-                    if (!(d >= 1e-290) || isinf(d)) {        // not positive (also NaN), or too small to invert
-                        atomicCAS(info, 0, row_offset + kb * 8 + j + 1);
-                        d = 1.0;
-                    }
+                    const bool ok = d >= 1e-290 && d <= 1.0e300;   // not positive (also NaN), too small to invert, or inf
+                    bad = (!ok && bad == 0) ? j + 1 : bad;
+                    d = ok ? d : 1.0;
                     const double rinv = pm_rsqrt(d);
                     double rt = d * rinv;
                     rt = fma(fma(-rt, rt, d), 0.5 * rinv, rt);
@@ -214,9 +216,10 @@ potf2_mma_kernel(double* __restrict__ A, long lda, int* __restrict__ info, int r
                         for (int r = cc; r < 8; r++) f[r][cc] = fma(-f[r][j], f[cc][j], f[r][cc]);
                 }
 #pragma unroll
-                for (int r = 0; r < 8; r++)
+                for (int r = 0; r < 8; r++)                    // lower triangle only: nobody reads above the diagonal
 #pragma unroll
-                    for (int cc = 0; cc < 8; cc++) Dg[r * PM_LD + cc] = cc <= r ? f[r][cc] : 0.0;
+                    for (int cc = 0; cc <= r; cc++) Dg[r * PM_LD + cc] = f[r][cc];
+                if (bad) atomicCAS(info, 0, row_offset + kb * 8 + bad);
             }
             __syncwarp();
             __threadfence_block();
