@@ -7,7 +7,8 @@
  * (first non-positive pivot, 1-based; 0 = ok).  Scratch is caller-provided and no compute entry allocates or
  * synchronises in steady state.  The exceptions, all one-time per device and all avoidable by calling gpk_init first:
  * the 8 KB exp table of the prediction front end (cudaMalloc + copy + one stream synchronisation), the library-owned
- * side stream + event pool of gpk_potrf_trtri, and -- not covered by gpk_init -- the item list of an int8 fit GEMM
+ * side stream + event pool of gpk_potrf_trtri (and the side stream + five events of gpk_predict_i8's optional
+ * pipeline, created only when GPK_OZ_PIPELINE enables it), and -- not covered by gpk_init -- the item list of an int8 fit GEMM
  * the first time its SHAPE is seen on a device (cudaMalloc + copy + one stream synchronisation; a fit of one size
  * sees about ten shapes, all in its first iteration).  gpk_shutdown frees all of it.  Per-device state is not
  * thread-safe: one host thread (or process) per GPU, calls on one stream at a time (SURVEY.md 8b "Threading").
