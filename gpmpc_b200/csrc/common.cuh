@@ -45,6 +45,27 @@ inline int current_device() {
     return d < 0 || d >= 64 ? 0 : d;
 }
 
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------
+// The fit is a chain of ~170 (N = 2048) to ~1800 (N = 16384) small dependent kernels; between two of them the GPU
+// idles for ~2-3 us (grid completion -> launch of the next grid).  Kernels launched with launch_pdl may be SCHEDULED
+// as soon as every CTA of the previous kernel in the stream has called pdl_launch_dependents() (or exited); they must
+// call pdl_wait() before touching anything the previous kernel wrote -- it returns when that kernel has completed
+// and its writes are visible.  Without the launch attribute both calls are no-ops.  GPK_PDL=0 turns the attribute off.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---- small device helpers -----------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

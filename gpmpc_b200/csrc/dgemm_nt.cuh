@@ -128,6 +128,8 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
 #pragma unroll
         for (int j = 0; j < FN; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
 
+    pdl_wait();                                          // the operands may come from the previous kernel in the stream
+
 #pragma unroll
     for (int s = 0; s < G_STAGES - 1; s++) {
         if (s < nk) load_stage(s, s);
@@ -161,6 +163,8 @@ __device__ __forceinline__ void dgemm_nt_body(const GemmParams& p) {
         cp_async_commit();
     }
     cp_async_wait<0>();
+    pdl_launch_dependents();                             // the next kernel's CTAs may be scheduled during the epilogue (an
+                                                         // earlier trigger, at the top, measured no better)
 
     if constexpr (EPI == 0) {
         if (p.c_inplace) __syncthreads();                // every warp has read its A rows before C (= A) is written

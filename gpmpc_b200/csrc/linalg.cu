@@ -89,13 +89,13 @@ int launch_dgemm_nt(GemmParams p, int epilogue, int batch, cudaStream_t st) {
     if (epilogue == 1)
         var_colsq_kernel<<<grid, G_THREADS, smem, st>>>(p);
     else if (bm == 128)
-        dgemm_nt_kernel<<<grid, G_THREADS, smem, st>>>(p);
+        GPK_CUDA(launch_pdl(dgemm_nt_kernel, grid, dim3(G_THREADS), smem, st, p));
     else if (bm == 64)
-        dgemm_nt64_kernel<<<grid, 128, smem, st>>>(p);
+        GPK_CUDA(launch_pdl(dgemm_nt64_kernel, grid, dim3(128), smem, st, p));
     else if (bn == 32)
-        dgemm_nt32_kernel<<<grid, 128, smem, st>>>(p);
+        GPK_CUDA(launch_pdl(dgemm_nt32_kernel, grid, dim3(128), smem, st, p));
     else
-        dgemm_nt16x128_kernel<<<grid, 128, smem, st>>>(p);
+        GPK_CUDA(launch_pdl(dgemm_nt16x128_kernel, grid, dim3(128), smem, st, p));
     GPK_LAUNCHED();
     return 0;
 }
@@ -169,6 +169,7 @@ potf2_mma_kernel(double* __restrict__ A, long lda, int* __restrict__ info, int r
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int fr = lane >> 2, fq = lane & 3;                  // fragment row, position in the quad
     const int fo = fr * PM_LD + fq;                           // fragment element offset inside a panel block
+    pdl_wait();
     if (warp == PM_WORKERS) {
         // ================= diagonal warp: its 16 blocks live in shared memory (run-time block index) =================
         for (int j = 0; j < P_NB; j++)
@@ -349,6 +350,7 @@ leaf_inv_kernel(const double* __restrict__ L, long ldl, double* __restrict__ Din
     const int tid = threadIdx.x, k = blockIdx.x;
     const int g = tid >> 6, e = tid & 63, r = e >> 3, c = e & 7;
     const int row_lo = k * 8;
+    pdl_wait();
     // rows >= 8k of L (columns 8k .. row) into shared memory
     for (int idx = tid; idx < (P_N - row_lo) * (P_N / 2); idx += PI_THREADS) {
         const int row = row_lo + idx / (P_N / 2), cp = (idx % (P_N / 2)) * 2;
@@ -424,9 +426,9 @@ static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_of
         GPK_CUDA(cudaFuncSetAttribute(leaf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PI_SMEM));
         attr_done = true;
     }
-    potf2_mma_kernel<<<1, PM_THREADS, 0, st>>>(A, lda, info, row_offset);
+    GPK_CUDA(launch_pdl(potf2_mma_kernel, dim3(1), dim3(PM_THREADS), 0, st, A, lda, info, row_offset));
     GPK_LAUNCHED();
-    leaf_inv_kernel<<<P_NB, PI_THREADS, PI_SMEM, st>>>(A, lda, Dinv);
+    GPK_CUDA(launch_pdl(leaf_inv_kernel, dim3(P_NB), dim3(PI_THREADS), PI_SMEM, st, (const double*)A, lda, Dinv));
     GPK_LAUNCHED();
     return 0;
 }
@@ -439,6 +441,7 @@ __global__ void transpose_kernel(const double* __restrict__ src, long lds, doubl
                                  int cols) {
     __shared__ double tile[32][33];
     const int bx = blockIdx.x * 32, by = blockIdx.y * 32;
+    pdl_wait();
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
         const int r = by + i, c = bx + threadIdx.x;
         if (r < rows && c < cols) tile[i][threadIdx.x] = src[(long)r * lds + c];
@@ -452,7 +455,7 @@ __global__ void transpose_kernel(const double* __restrict__ src, long lds, doubl
 
 static int launch_transpose(const double* src, long lds, double* dst, long ldd, long rows, long cols, cudaStream_t st) {
     dim3 grid((unsigned)((cols + 31) / 32), (unsigned)((rows + 31) / 32));
-    transpose_kernel<<<grid, dim3(32, 8), 0, st>>>(src, lds, dst, ldd, (int)rows, (int)cols);
+    GPK_CUDA(launch_pdl(transpose_kernel, grid, dim3(32, 8), 0, st, src, lds, dst, ldd, (int)rows, (int)cols));
     GPK_LAUNCHED();
     return 0;
 }
@@ -672,6 +675,11 @@ static int potrf_trtri_rec(const RecBoth& r, long off, long n) {
 }
 
 }  // namespace gpk
+
+bool gpk::pdl_enabled() {
+    static const bool on = !(getenv("GPK_PDL") && atoi(getenv("GPK_PDL")) == 0);
+    return on;
+}
 
 // ================================================================================================
 // C ABI
