@@ -245,15 +245,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * 8, 1) ozg_
         const uint32_t tbase = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(half * 32);
         uint32_t tph = 0, par = 0;
         // 8 recombined columns -> C (row-major): 64 contiguous bytes per thread
-        auto emit8 = [&](const double (&r8)[8], double* cp, const double* sb, double sa, double bfac, bool readc) {
+        // the old C values of a chunk (read-modify-write) are fetched BEFORE the wait for the accumulators, so that the
+        // HBM / L2 latency of that read is not part of the epilogue the tensor pipe waits for (6 digits: one TMEM buffer)
+        double cold[4][8];
+        auto emit8 = [&](const double (&r8)[8], const double (&c8)[8], double* cp, const double* sb, double sa, double bfac, bool readc) {
             double o[8];
             if (readc) {
 #pragma unroll
-                for (int v = 0; v < 4; v++) {
-                    const double2 x = *reinterpret_cast<const double2*>(cp + 2 * v);
-                    o[2 * v] = x.x * bfac;
-                    o[2 * v + 1] = x.y * bfac;
-                }
+                for (int v = 0; v < 8; v++) o[v] = c8[v] * bfac;
             } else {
 #pragma unroll
                 for (int v = 0; v < 8; v++) o[v] = 0.0;
@@ -298,7 +297,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * 8, 1) ozg_
                 double r8[8];
 #pragma unroll
                 for (int j = 0; j < 8; j++) r8[j] = oz_recombine<S>(vv, j);
-                emit8(r8, cp + c * 8, sb + c * 8, sa, bfac, readc);
+                emit8(r8, cold[c], cp + c * 8, sb + c * 8, sa, bfac, readc);
             }
         };
         for (int item = pair_id; item < a.total_items; item += n_pairs) {
@@ -316,6 +315,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * 8, 1) ozg_
                 const double* sb = a.scaleB + (long)chunk * a.rowsB + gcol;
                 const double bfac = first ? a.beta : 1.0;
                 const bool readc = !(first && a.beta == 0.0);
+                if (readc) {
+#pragma unroll
+                    for (int c = 0; c < 4; c++)
+#pragma unroll
+                        for (int v = 0; v < 4; v++) {
+                            const double2 x = *reinterpret_cast<const double2*>(cp + c * 8 + 2 * v);
+                            cold[c][2 * v] = x.x;
+                            cold[c][2 * v + 1] = x.y;
+                        }
+                }
                 mbar_wait(&tmem_full_bar, tph);
                 tph ^= 1;
                 tc_fence_after();
@@ -340,7 +349,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * 8, 1) ozg_
                         double r8[8];
 #pragma unroll
                         for (int j = 0; j < 8; j++) r8[j] = oz_recombine<S>(v[c & 1], j);
-                        emit8(r8, cp + c * 8, sb + c * 8, sa, bfac, readc);
+                        emit8(r8, cold[c], cp + c * 8, sb + c * 8, sa, bfac, readc);
                     }
                 }
                 first = false;
