@@ -58,16 +58,20 @@ def weighted_bounds(n: int, weights: Sequence[float], granularity: int = 1) -> l
     return [(cuts[r], cuts[r + 1]) for r in range(world)]
 
 
-def measured_weights(items_local: int, seconds_local: float, group=None) -> list[float]:
+def measured_weights(items_local: int, seconds_local: float, group=None, clamp: float = 0.15) -> list[float]:
     """All-gather of every rank's measured speed (items/s) on its current block: one small collective OUTSIDE the
-    prediction step, e.g. after a warm-up step; feed the result to weighted_bounds."""
+    prediction step, e.g. after a warm-up step; feed the result to weighted_bounds.  Speeds are clamped to within
+    `clamp` of their median (the clocks of one box differ by ~15 %; a larger deviation is a hiccup of the measurement,
+    which must not skew the blocks of every later step)."""
     rank, world = world_info(group)
     mine = float(items_local) / max(float(seconds_local), 1e-12)
     if world == 1:
         return [mine]
     out = [None] * world
     dist.all_gather_object(out, mine, group=group)
-    return [float(x) for x in out]
+    w = [float(x) for x in out]
+    med = sorted(w)[len(w) // 2]
+    return [min(max(x, med * (1.0 - clamp)), med * (1.0 + clamp)) for x in w]
 
 
 def gp_owner(p: int, world: int) -> int:

@@ -87,8 +87,9 @@ def _worker(rank, world, port, q_total):
         for a, b in zip(outs, full):
             assert torch.equal(a, b)
         # --- speed-weighted blocks (rank 1 three times as fast): same results, same order, one small all-gather outside
-        w = S.measured_weights(10 if rank == 0 else 30, 1.0)
+        w = S.measured_weights(10 if rank == 0 else 30, 1.0, clamp=10.0)
         assert w == [10.0, 30.0]
+        assert S.measured_weights(10 if rank == 0 else 30, 1.0) == [25.5, 30.0]      # default: within 15 % of the median
         wb = S.weighted_bounds(q_total, w, 1)
         lo, hi, outs = S.predict_sharded(predict_fn, Z, bounds=wb)
         assert (lo, hi) == wb[rank] and wb[0][1] == round(q_total * 0.25)
