@@ -419,16 +419,115 @@ leaf_inv_kernel(const double* __restrict__ L, long ldl, double* __restrict__ Din
     }
 }
 
-static int launch_potf2(double* A, long lda, double* Dinv, int* info, int row_offset, cudaStream_t st) {
+// B (m x 128, in place) <- B L^-T for a factored 128 x 128 leaf L: the TRSM leaf of the Cholesky recursion, by blocked
+// substitution on the FP64 tensor pipe.  It needs only L itself, so the 128 x 128 inverse of the leaf (leaf_inv_kernel,
+// 19 us) is no longer on the factorisation's critical path -- it moves to the inverse factor's side stream.
+// One warp owns 8 rows of B as 16 accumulator fragments (8 x 8 blocks, lane l holds [l/4][2(l%4)], [l/4][2(l%4)+1]);
+// right-looking over the 16 block columns: X_m = R_m L_mm^-T (2 DMMAs against the 8 x 8 inverse of the diagonal block,
+// computed per CTA by 128 threads, one column each), then R_k -= X_m L_km^T for every k > m (2 DMMAs per block, B
+// fragments straight from the shared-memory copy of L, row stride 132 doubles: conflict-free).  Fully unrolled:
+// 272 DMMAs per warp, ~150 clocks of latency per block column.
+constexpr int TS_WARPS = 4, TS_THREADS = 32 * TS_WARPS, TS_LD = 132;
+constexpr int TS_SMEM = (P_N * TS_LD + P_NB * 8 * PM_LD) * 8;
+__global__ void __launch_bounds__(TS_THREADS, 1)
+trsm128_kernel(double* __restrict__ B, long ldb, int m, const double* __restrict__ L, long ldl) {
+    extern __shared__ __align__(16) double tsm[];
+    double* Ls = tsm;                                     // [128][TS_LD], lower triangle of L
+    double* Li = tsm + P_N * TS_LD;                       // [16][8][PM_LD] inverses of the diagonal 8 x 8 blocks
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int fr = lane >> 2, fq = lane & 3;
+    pdl_wait();
+    for (int idx = tid; idx < P_N * (P_N / 2); idx += TS_THREADS) {
+        const int row = idx / (P_N / 2), cp = (idx % (P_N / 2)) * 2;
+        if (cp <= row) cp_async16(Ls + row * TS_LD + cp, L + (long)row * ldl + cp);   // all copies in flight at once
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncthreads();
+    {
+        // column cc of the inverse of diagonal block j:  x_cc = 1 / l_cc,  x_i = -(sum_{cc <= q < i} l_iq x_q) / l_ii
+        const int j = tid >> 3, cc = tid & 7;
+        const double* Lj = Ls + (j * 8) * TS_LD + j * 8;
+        double x[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            double acc = 0.0;
+#pragma unroll
+            for (int q = 0; q < i; q++) acc = fma(Lj[i * TS_LD + q], x[q], acc);
+            const double di = 1.0 / Lj[i * TS_LD + i];
+            x[i] = i < cc ? 0.0 : (i == cc ? di : -acc * di);
+            Li[(j * 8 + i) * PM_LD + cc] = x[i];
+        }
+    }
+    __syncthreads();
+    const long r0 = ((long)blockIdx.x * TS_WARPS + warp) * 8;
+    if (r0 >= m) return;
+    double* Bw = B + (r0 + fr) * ldb + 2 * fq;
+    double c[P_NB][2];
+#pragma unroll
+    for (int k = 0; k < P_NB; k++) {
+        const double2 v = *reinterpret_cast<const double2*>(Bw + 8 * k);
+        c[k][0] = v.x; c[k][1] = v.y;
+    }
+    const int src0 = (lane & ~3) + (fq >> 1), src1 = src0 + 2;
+    const bool odd = fq & 1;
+#pragma unroll
+    for (int mb = 0; mb < P_NB; mb++) {
+        // accumulator layout -> A fragments of R_m, then X_m = R_m L_mm^-T
+        double a0, a1;
+        {
+            const double x00 = __shfl_sync(0xffffffffu, c[mb][0], src0), x01 = __shfl_sync(0xffffffffu, c[mb][1], src0);
+            const double x10 = __shfl_sync(0xffffffffu, c[mb][0], src1), x11 = __shfl_sync(0xffffffffu, c[mb][1], src1);
+            a0 = odd ? x01 : x00; a1 = odd ? x11 : x10;
+        }
+        double x[2] = {0.0, 0.0};
+        pm_dmma(x, a0, Li[(mb * 8 + fr) * PM_LD + fq]);
+        pm_dmma(x, a1, Li[(mb * 8 + fr) * PM_LD + 4 + fq]);
+        c[mb][0] = x[0]; c[mb][1] = x[1];
+        if (mb + 1 < P_NB) {
+            const double x00 = __shfl_sync(0xffffffffu, x[0], src0), x01 = __shfl_sync(0xffffffffu, x[1], src0);
+            const double x10 = __shfl_sync(0xffffffffu, x[0], src1), x11 = __shfl_sync(0xffffffffu, x[1], src1);
+            a0 = -(odd ? x01 : x00); a1 = -(odd ? x11 : x10);
+#pragma unroll
+            for (int k = mb + 1; k < P_NB; k++) {
+                const double* lk = Ls + (k * 8 + fr) * TS_LD + mb * 8 + fq;
+                pm_dmma(c[k], a0, lk[0]);
+                pm_dmma(c[k], a1, lk[4]);
+            }
+        }
+    }
+    pdl_launch_dependents();
+#pragma unroll
+    for (int k = 0; k < P_NB; k++) *reinterpret_cast<double2*>(Bw + 8 * k) = make_double2(c[k][0], c[k][1]);
+}
+
+static int launch_trsm128(double* B, long ldb, long m, const double* L, long ldl, cudaStream_t st) {
+    static bool attr_dev[64] = {};
+    bool& attr_done = attr_dev[current_device()];
+    if (!attr_done) {
+        GPK_CUDA(cudaFuncSetAttribute(trsm128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM));
+        attr_done = true;
+    }
+    const unsigned grid = (unsigned)((m + 8 * TS_WARPS - 1) / (8 * TS_WARPS));
+    GPK_CUDA(launch_pdl(trsm128_kernel, dim3(grid), dim3(TS_THREADS), TS_SMEM, st, B, ldb, (int)m, L, ldl));
+    GPK_LAUNCHED();
+    return 0;
+}
+
+// the leaf's factorisation, and (separately: it is off the factorisation's critical path) the inverse of its factor
+static int launch_potf2(double* A, long lda, int* info, int row_offset, cudaStream_t st) {
+    GPK_CUDA(launch_pdl(potf2_mma_kernel, dim3(1), dim3(PM_THREADS), 0, st, A, lda, info, row_offset));
+    GPK_LAUNCHED();
+    return 0;
+}
+static int launch_leaf_inv(const double* A, long lda, double* Dinv, cudaStream_t st) {
     static bool attr_dev[64] = {};      // cudaFuncSetAttribute is per device
     bool& attr_done = attr_dev[current_device()];
     if (!attr_done) {
         GPK_CUDA(cudaFuncSetAttribute(leaf_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PI_SMEM));
         attr_done = true;
     }
-    GPK_CUDA(launch_pdl(potf2_mma_kernel, dim3(1), dim3(PM_THREADS), 0, st, A, lda, info, row_offset));
-    GPK_LAUNCHED();
-    GPK_CUDA(launch_pdl(leaf_inv_kernel, dim3(P_NB), dim3(PI_THREADS), PI_SMEM, st, (const double*)A, lda, Dinv));
+    GPK_CUDA(launch_pdl(leaf_inv_kernel, dim3(P_NB), dim3(PI_THREADS), PI_SMEM, st, A, lda, Dinv));
     GPK_LAUNCHED();
     return 0;
 }
@@ -535,11 +634,8 @@ static long split(long n) { return (n / TILE / 2) * TILE; }   // n >= 256, multi
 // B (m x n at rows r0.., cols c0..) <- B * L^-T, L = A[c0:c0+n, c0:c0+n]
 static int trsm_rec(const Rec& r, long r0, long m, long c0, long n) {
     double* Bp = r.A + r0 * r.lda + c0;
-    if (n == TILE) {
-        const double* Di = r.Dinv + (c0 / TILE) * TILE * TILE;
-        // in place: one CTA owns all 128 columns of its rows and has consumed them before its epilogue
-        return launch_dgemm_nt(gemm_args(Bp, r.lda, Di, TILE, Bp, r.lda, m, TILE, TILE, 1.0, 0.0, 0, 0), 0, 1, r.st);
-    }
+    if (n == TILE)    // in place, by substitution with the factored leaf itself (its inverse is not needed here)
+        return launch_trsm128(Bp, r.lda, m, r.A + c0 * r.lda + c0, r.lda, r.st);
     const long n1 = split(n), n2 = n - n1;
     GPK_TRY(trsm_rec(r, r0, m, c0, n1));
     // B2 -= B1 * Lb^T,  Lb = A[c0+n1 : c0+n, c0 : c0+n1]
@@ -549,8 +645,10 @@ static int trsm_rec(const Rec& r, long r0, long m, long c0, long n) {
 }
 
 static int potrf_rec(const Rec& r, long off, long n) {
-    if (n == TILE)
-        return launch_potf2(r.A + off * r.lda + off, r.lda, r.Dinv + (off / TILE) * TILE * TILE, r.info, (int)off, r.st);
+    if (n == TILE) {
+        GPK_TRY(launch_potf2(r.A + off * r.lda + off, r.lda, r.info, (int)off, r.st));
+        return launch_leaf_inv(r.A + off * r.lda + off, r.lda, r.Dinv + (off / TILE) * TILE * TILE, r.st);
+    }
     const long n1 = split(n), n2 = n - n1;
     GPK_TRY(potrf_rec(r, off, n1));
     GPK_TRY(trsm_rec(r, off + n1, n2, off, n1));
@@ -644,10 +742,12 @@ static int potrf_trtri_rec(const RecBoth& r, long off, long n) {
     cudaEvent_t ev;
     if (n == TILE) {
         ozg_set_partition(1);
-        GPK_TRY(launch_potf2(r.f.A + off * r.f.lda + off, r.f.lda, r.f.Dinv + (off / TILE) * TILE * TILE, r.f.info, (int)off, r.f.st));
+        GPK_TRY(launch_potf2(r.f.A + off * r.f.lda + off, r.f.lda, r.f.info, (int)off, r.f.st));
         GPK_TRY(r.fs->get(&ev));
         GPK_CUDA(cudaEventRecord(ev, r.f.st));
         GPK_CUDA(cudaStreamWaitEvent(r.v.st, ev, 0));
+        // the leaf's inverse only feeds the inverse factor: side stream (the TRSM leaves substitute with L itself)
+        GPK_TRY(launch_leaf_inv(r.f.A + off * r.f.lda + off, r.f.lda, r.f.Dinv + (off / TILE) * TILE * TILE, r.v.st));
         ozg_set_partition(2);
         return trtri_rec(r.v, off, TILE);                       // leaf: copy + transpose of the emitted inverse
     }
