@@ -565,6 +565,16 @@ def measure_roofline(gb, Z, ctx, steps):
            "peak_source": (f"2 x MEASURED_PEAKS.json {'bf16_tflops_sustained (sustained' if sustained else 'bf16_tflops (burst'}"
                            f", of measured): {ms:.2f} ms per launch, {steps + 2} launches back to back" if bf16 else
                            f"2 x {FALLBACK_BF16_TFLOPS} TFLOP/s bf16 (of fallback)")}
+    # what bounds the kernel besides the tensor pipe (profiles/pipeline_r02.md): operand fetches from shared memory
+    g = sum(range(1, S + 1))                              # digit groups multiplied per k-step: columns = 64 g
+    a_reads = S + (1 if 64 * S > 256 else 0)              # the widest instruction is split in two: its A tile is read twice
+    smem_bytes_per_kstep = a_reads * 4096 + 64 * g * 32
+    out["shared_memory_bound"] = {
+        "bytes_per_clk_at_full_tensor_rate": smem_bytes_per_kstep / (64 * g / 2.0), "sm_bytes_per_clk": 128,
+        "note": "per 32-byte k-step a CTA's tcgen05.mma read the E digit tiles (4 KB each) and the concatenated W digit columns "
+                "(32 B each) from shared memory in the N/2 clocks the tensor pipe needs: the kernel tops out near "
+                "128 / that figure of tensor-pipe-active (ncu: 89.7 % at config 3), and a co-resident kernel that needs "
+                "shared memory starves (measured)"}
     if peaks.get("bf16_tflops") and peaks.get("bf16_tflops_sustained"):
         out["frac_of_burst_peak"] = achieved / (2.0 * peaks["bf16_tflops"])
         out["frac_of_sustained_peak"] = achieved / (2.0 * peaks["bf16_tflops_sustained"])
