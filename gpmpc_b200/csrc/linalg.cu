@@ -273,11 +273,20 @@ potf2_mma_kernel(double* __restrict__ A, long lda, int* __restrict__ info, int r
                     const double2 v = *reinterpret_cast<const double2*>(row + cc);
                     l[cc] = v.x; l[cc + 1] = v.y;
                 }
+                // right-looking: as soon as l[m] is final it leaves every later column, so the serial chain is one FMA and
+                // one multiply per column (the factor's entries are fetched up front)
+                double lk[8][8], rv[8];
 #pragma unroll
                 for (int cc = 0; cc < 8; cc++) {
+                    rv[cc] = Rv[cc];
 #pragma unroll
-                    for (int m = 0; m < cc; m++) l[cc] = fma(-l[m], Dg[cc * PM_LD + m], l[cc]);
-                    l[cc] *= Rv[cc];
+                    for (int m = 0; m < cc; m++) lk[cc][m] = Dg[cc * PM_LD + m];
+                }
+#pragma unroll
+                for (int m = 0; m < 8; m++) {
+                    l[m] *= rv[m];
+#pragma unroll
+                    for (int cc = m + 1; cc < 8; cc++) l[cc] = fma(-l[m], lk[cc][m], l[cc]);
                 }
                 double* gdst = A + (long)(pty * 8 + (lane & 7)) * lda + kb * 8;
 #pragma unroll
