@@ -497,12 +497,12 @@ trsm128_kernel(double* __restrict__ B, long ldb, int m, const double* __restrict
             const double x00 = __shfl_sync(0xffffffffu, x[0], src0), x01 = __shfl_sync(0xffffffffu, x[1], src0);
             const double x10 = __shfl_sync(0xffffffffu, x[0], src1), x11 = __shfl_sync(0xffffffffu, x[1], src1);
             a0 = -(odd ? x01 : x00); a1 = -(odd ? x11 : x10);
+            // consecutive DMMAs share their A fragment (operand reuse), and the two updates of a block are 15 - mb
+            // instructions apart instead of back to back
 #pragma unroll
-            for (int k = mb + 1; k < P_NB; k++) {
-                const double* lk = Ls + (k * 8 + fr) * TS_LD + mb * 8 + fq;
-                pm_dmma(c[k], a0, lk[0]);
-                pm_dmma(c[k], a1, lk[4]);
-            }
+            for (int k = mb + 1; k < P_NB; k++) pm_dmma(c[k], a0, Ls[(k * 8 + fr) * TS_LD + mb * 8 + fq]);
+#pragma unroll
+            for (int k = mb + 1; k < P_NB; k++) pm_dmma(c[k], a1, Ls[(k * 8 + fr) * TS_LD + mb * 8 + 4 + fq]);
         }
     }
     pdl_launch_dependents();
