@@ -372,7 +372,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * 8, 1) ozg_
 struct OzgWorkspace { void* ptr = nullptr; long bytes = 0; int digits = 0; };
 static OzgWorkspace g_ozg_ws[64];
 static long g_ozg_min_dim = 1024;          // smallest M, N for which the int8 path is used
-static double g_ozg_min_work = 2e9;
+static double g_ozg_min_work = 5e8;          // useful multiply-adds; round 2: 2e9 -> 5e8 (every 1024-sized GEMM with one triangular
+                                             // operand or a lower-only result: N = 2048 iteration 1.27 -> 1.22 ms, 4096 3.38 -> 3.27 ms)
 
 static int g_ozg_gm = 8, g_ozg_gn = 9, g_ozg_pairs = 0;
 static void ozg_env() {
@@ -546,10 +547,11 @@ int ozg_try(const GemmParams& p, int batch, cudaStream_t st) {
     }
     if (ws.ptr == nullptr || ws.digits == 0 || batch != 1) return 0;
     if (p.M < g_ozg_min_dim || p.N < g_ozg_min_dim || p.K < 1024) return 0;
-    // below ~1.2e10 useful multiply-adds the slicing passes and the 74-pair tile quantisation eat the gain
-    // (tools/ozgemm_check.py: 2048 x 2048 x 4096 full 0.50 vs 1.22 ms DMMA; 2048^3 upper/lower 0.15 vs 0.12 ms)
+    // below the threshold the slicing passes and the 74-pair tile quantisation eat the gain (tools/ozgemm_check.py:
+    // 1024^3 triangular 0.049 vs 0.063 ms DMMA; 2048 x 2048 x 4096 full 0.33 vs 1.22 ms; GPK_OZG_MIN_WORK overrides)
     const double work = (double)p.M * p.N * p.K * (p.a_tri ? 0.5 : 1.0) * (p.c_lower ? 0.5 : 1.0);
-    if (work < g_ozg_min_work) return 0;
+    static const double env_min_work = getenv("GPK_OZG_MIN_WORK") ? atof(getenv("GPK_OZG_MIN_WORK")) : -1.0;   // tuning
+    if (work < (env_min_work > 0.0 ? env_min_work : g_ozg_min_work)) return 0;
     if (!ozg_shape_ok(p) || ozg_need_bytes(p, ws.digits) > ws.bytes) return 0;
     const int r = ozg_dispatch(p, ws.digits, static_cast<uint8_t*>(ws.ptr), st);
     return r == 0 ? 1 : r;
