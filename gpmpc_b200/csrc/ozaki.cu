@@ -870,7 +870,7 @@ static OzPlan oz_plan(long tiles_total, int batch, long npad, int S, long tcap) 
     double L = 3.0 * (2048.0 / (double)npad) * (2048.0 / (double)npad);
     double co_slow = 4.5;
     // Default OFF: measured on B200 (profiles/pipeline_r02.md) the co-resident front CTAs start with the contraction
-    // but are starved until it ends -- oz_var_kernel's tensor-core operand fetches take ~114 of the SM's 128 B/clk of
+    // but are starved until it ends -- oz_var_kernel's tensor-core operand fetches take ~115 of the SM's 128 B/clk of
     // shared-memory bandwidth, which the front end's fragment loads need too -- so the pipelined step is slower
     // (config 2: 0.77 vs 0.72 ms) or equal (config 3).  The path stays for experiments and is covered by tests.
     int mode = 0;                                        // 0 = never pipeline, 1 = by the model, 2 = always (tests)
